@@ -1,0 +1,400 @@
+// C ABI (include/fastbn_b200.h) over the planner + kernels. No CPU fallback anywhere: without a usable CUDA device
+// fbn_plan_create fails with FBN_ERR_NO_DEVICE.
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include <cuda_runtime.h>
+
+#include "../../include/fastbn_b200.h"
+#include "plan.h"
+
+namespace fbn {
+size_t fused_smem_bytes(const DevPlan &P);
+cudaError_t fused_prepare(const DevPlan &P, int *blocks_per_sm);
+cudaError_t fused_launch(const DevPlan &P, int grid, double *scratch, int64_t n_cases, const int64_t *ev_off, int64_t ev_base,
+                         const int32_t *ev_vars, const int32_t *ev_vals, int32_t *labels, double *post, cudaStream_t st);
+cudaError_t score_launch(int64_t n_cases, int n_vars, int sum_dims, const VarInfo *vars, const double *post, const double *golden,
+                         const int32_t *labels, const int32_t *truths, double *out_case, double *out4, cudaStream_t st);
+}  // namespace fbn
+
+static thread_local std::string g_err;
+static int fail(int code, const std::string &msg) {
+    g_err = msg;
+    return code;
+}
+#define CK(call)                                                                                       \
+    do {                                                                                               \
+        cudaError_t e__ = (call);                                                                      \
+        if (e__ != cudaSuccess)                                                                        \
+            return fail(FBN_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e__));            \
+    } while (0)
+
+namespace {
+constexpr int kNBuf = 3;            // pipeline depth of fbn_run
+struct ChunkBuf {                   // device + pinned staging for one in-flight chunk
+    int64_t *d_off = nullptr;
+    int32_t *d_vars = nullptr, *d_vals = nullptr, *d_labels = nullptr;
+    double *d_post = nullptr;
+    int64_t *h_off = nullptr;       // pinned staging (rebased copies / pageable callers)
+    int32_t *h_vars = nullptr, *h_vals = nullptr, *h_labels = nullptr;
+    double *h_post = nullptr;
+    int64_t cap_cases = 0, cap_ev = 0;
+    bool staged_out = false;
+    cudaEvent_t in_done = nullptr, k_done = nullptr, out_done = nullptr;
+};
+}  // namespace
+
+struct fbn_plan {
+    fbn::HostPlan hp;
+    fbn::DevPlan dp;
+    int device = 0;
+    int n_sms = 0, blocks_per_sm = 0, grid = 0;
+    std::vector<void *> dev_allocs;
+    double *scratch = nullptr;
+    int64_t scratch_bytes = 0, plan_bytes = 0;
+    cudaStream_t s_in = nullptr, s_k = nullptr, s_out = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    ChunkBuf buf[kNBuf];
+    double *score_case = nullptr;
+    int64_t score_cap = 0;
+    double *score_out4 = nullptr;
+};
+
+extern "C" const char *fbn_last_error(void) { return g_err.c_str(); }
+
+extern "C" int fbn_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+template <class T>
+static int upload(fbn_plan *p, const std::vector<T> &v, const T **out) {
+    void *d = nullptr;
+    size_t bytes = std::max<size_t>(v.size(), 1) * sizeof(T);
+    CK(cudaMalloc(&d, bytes));
+    p->dev_allocs.push_back(d);
+    if (!v.empty()) CK(cudaMemcpy(d, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+    p->plan_bytes += (int64_t)bytes;
+    *out = (const T *)d;
+    return FBN_OK;
+}
+
+static int pick_team(const fbn_tree_desc *t) {
+    // scratch rows per tile ~ clique entries; keep (resident tiles x tile bytes) within a few tens of GB and give
+    // big tables more warps per tile. 1 warp per tile for ALARM/HEPAR2-size trees.
+    double entries = 0;
+    int64_t pos = 0;
+    for (int c = 0; c < t->n_cliques; ++c) {
+        double sz = 1;
+        for (int i = 0; i < t->table_nvars[c]; ++i) sz *= t->var_dims[t->table_vars[pos + i]];
+        pos += t->table_nvars[c];
+        entries += sz;
+    }
+    if (entries <= 8192) return 1;
+    if (entries <= 32768) return 2;
+    if (entries <= 131072) return 4;
+    if (entries <= 1048576) return 8;
+    if (entries <= 8388608) return 16;
+    return 32;
+}
+
+extern "C" int fbn_plan_create(const fbn_tree_desc *tree, const fbn_plan_options *opt, fbn_plan **out) {
+    if (!tree || !out) return fail(FBN_ERR_INVALID, "null argument");
+    *out = nullptr;
+    int ndev = fbn_device_count();
+    if (ndev <= 0) return fail(FBN_ERR_NO_DEVICE, "no CUDA device: fastbn_b200 has no CPU fallback");
+    int dev = opt && opt->device >= 0 ? opt->device : -1;
+    if (dev < 0) CK(cudaGetDevice(&dev));
+    if (dev >= ndev) return fail(FBN_ERR_INVALID, "device ordinal out of range");
+    CK(cudaSetDevice(dev));
+    if (!tree->table_nvars || !tree->table_vars || !tree->var_dims) return fail(FBN_ERR_INVALID, "null array in fbn_tree_desc");
+    for (int v = 0; v < tree->n_vars; ++v)
+        if (tree->var_dims[v] <= 0) return fail(FBN_ERR_INVALID, "variable with non-positive domain size");
+    {
+        int64_t pos = 0;
+        for (int i = 0; i < tree->n_cliques + tree->n_separators; ++i) {
+            for (int k = 0; k < tree->table_nvars[i]; ++k)
+                if (tree->table_vars[pos + k] < 0 || tree->table_vars[pos + k] >= tree->n_vars)
+                    return fail(FBN_ERR_INVALID, "table variable out of range");
+            pos += tree->table_nvars[i];
+        }
+    }
+    int team = opt && opt->team_warps > 0 ? opt->team_warps : pick_team(tree);
+
+    fbn_plan *p = new fbn_plan();
+    p->device = dev;
+    std::string err = fbn::build_plan(*tree, team, p->hp);
+    if (!err.empty()) {
+        delete p;
+        return fail(FBN_ERR_INVALID, err);
+    }
+    const fbn::HostPlan &h = p->hp;
+    fbn::DevPlan &d = p->dp;
+    int rc;
+#define UP(field) if ((rc = upload(p, h.field, &d.field)) != FBN_OK) { fbn_plan_destroy(p); return rc; }
+    UP(pot) UP(lam16) UP(idx32) UP(cops) UP(pops) UP(items) UP(fins) UP(phases) UP(vars)
+#undef UP
+    d.n_phases = (int32_t)h.phases.size();
+    d.n_vars = h.n_vars; d.sum_dims = h.sum_dims; d.query_var = h.query_var;
+    d.tile_rows = h.tile_rows; d.mg_row0 = h.mg_row0;
+    d.max_normslots = h.max_normslots; d.max_pslots = h.max_pslots; d.team = h.team;
+
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, dev));
+    p->n_sms = prop.multiProcessorCount;
+    if (fbn::fused_smem_bytes(d) > (size_t)prop.sharedMemPerBlockOptin) {
+        fbn_plan_destroy(p);
+        return fail(FBN_ERR_INVALID, "tree needs more shared memory per tile than the device has");
+    }
+    cudaError_t ce = fbn::fused_prepare(d, &p->blocks_per_sm);
+    if (ce != cudaSuccess) {
+        fbn_plan_destroy(p);
+        return fail(FBN_ERR_CUDA, std::string("kernel setup failed (is this an sm_100 device?): ") + cudaGetErrorString(ce));
+    }
+    if (p->blocks_per_sm < 1) p->blocks_per_sm = 1;
+    int64_t tile_bytes = (int64_t)h.tile_rows * fbn::kLanes * 8;
+    int64_t resident = (int64_t)p->n_sms * p->blocks_per_sm;
+    size_t free_b = 0, total_b = 0;
+    CK(cudaMemGetInfo(&free_b, &total_b));
+    int64_t budget = (int64_t)(free_b * 0.45);  // leave room for the caller's evidence / posterior buffers
+    if (resident * tile_bytes > budget) resident = std::max<int64_t>(1, budget / tile_bytes);
+    if (opt && opt->max_resident > 0) resident = std::min<int64_t>(resident, opt->max_resident);
+    if (resident >= p->n_sms) resident = resident / p->n_sms * p->n_sms;  // whole waves over the SMs
+    p->grid = (int)resident;
+    p->scratch_bytes = resident * tile_bytes;
+    ce = cudaMalloc((void **)&p->scratch, (size_t)p->scratch_bytes);
+    if (ce != cudaSuccess) {
+        fbn_plan_destroy(p);
+        return fail(FBN_ERR_NOMEM, "cannot allocate tile scratch");
+    }
+    CK(cudaMemset(p->scratch, 0, (size_t)p->scratch_bytes));
+    CK(cudaStreamCreateWithFlags(&p->s_in, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&p->s_k, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&p->s_out, cudaStreamNonBlocking));
+    CK(cudaEventCreate(&p->ev0));
+    CK(cudaEventCreate(&p->ev1));
+    CK(cudaMalloc((void **)&p->score_out4, 4 * sizeof(double)));
+    *out = p;
+    return FBN_OK;
+}
+
+static void free_chunk(ChunkBuf &b) {
+    cudaFree(b.d_off); cudaFree(b.d_vars); cudaFree(b.d_vals); cudaFree(b.d_labels); cudaFree(b.d_post);
+    cudaFreeHost(b.h_off); cudaFreeHost(b.h_vars); cudaFreeHost(b.h_vals); cudaFreeHost(b.h_labels); cudaFreeHost(b.h_post);
+    if (b.in_done) cudaEventDestroy(b.in_done);
+    if (b.k_done) cudaEventDestroy(b.k_done);
+    if (b.out_done) cudaEventDestroy(b.out_done);
+    b = ChunkBuf();
+}
+
+extern "C" void fbn_plan_destroy(fbn_plan *p) {
+    if (!p) return;
+    cudaSetDevice(p->device);
+    cudaDeviceSynchronize();
+    for (void *d : p->dev_allocs) cudaFree(d);
+    cudaFree(p->scratch);
+    cudaFree(p->score_case);
+    cudaFree(p->score_out4);
+    for (auto &b : p->buf) free_chunk(b);
+    if (p->s_in) cudaStreamDestroy(p->s_in);
+    if (p->s_k) cudaStreamDestroy(p->s_k);
+    if (p->s_out) cudaStreamDestroy(p->s_out);
+    if (p->ev0) cudaEventDestroy(p->ev0);
+    if (p->ev1) cudaEventDestroy(p->ev1);
+    cudaGetLastError();
+    delete p;
+}
+
+extern "C" int fbn_plan_get_info(const fbn_plan *p, fbn_plan_info *o) {
+    if (!p || !o) return fail(FBN_ERR_INVALID, "null argument");
+    const fbn::HostPlan &h = p->hp;
+    memset(o, 0, sizeof(*o));
+    o->n_vars = h.n_vars; o->n_cliques = h.n_cliques; o->n_separators = h.n_seps; o->sum_dims = h.sum_dims;
+    o->n_levels = h.n_levels; o->team_warps = h.team; o->resident_tiles = p->grid; o->n_phases = (int32_t)h.phases.size();
+    o->clique_entries = h.clique_entries; o->separator_entries = h.sep_entries; o->parent_entries = h.parent_entries;
+    o->marginal_entries = h.marginal_entries; o->scratch_bytes = p->scratch_bytes; o->plan_bytes = p->plan_bytes;
+    o->alg_bytes_per_case = h.alg_bytes_per_case; o->kernel_bytes_per_case = h.kernel_bytes_per_case;
+    return FBN_OK;
+}
+
+extern "C" int fbn_run_device(fbn_plan *p, int64_t n_cases, const int64_t *ev_offsets, const int32_t *ev_vars,
+                              const int32_t *ev_vals, int32_t *labels_out, double *posteriors_out, void *stream,
+                              fbn_stats *stats) {
+    if (!p) return fail(FBN_ERR_INVALID, "null plan");
+    if (n_cases < 0 || (n_cases > 0 && !ev_offsets)) return fail(FBN_ERR_INVALID, "bad n_cases / ev_offsets");
+    CK(cudaSetDevice(p->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    if (stats) CK(cudaEventRecord(p->ev0, st));
+    CK(fbn::fused_launch(p->dp, p->grid, p->scratch, n_cases, ev_offsets, 0, ev_vars, ev_vals, labels_out, posteriors_out, st));
+    if (stats) {
+        CK(cudaEventRecord(p->ev1, st));
+        CK(cudaEventSynchronize(p->ev1));
+        float ms = 0;
+        CK(cudaEventElapsedTime(&ms, p->ev0, p->ev1));
+        memset(stats, 0, sizeof(*stats));
+        stats->kernel_ms = ms;
+        stats->total_ms = ms;
+        stats->n_launches = n_cases > 0 ? 1 : 0;
+    }
+    return FBN_OK;
+}
+
+static bool is_pinned(const void *ptr) {
+    if (!ptr) return true;
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, ptr) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return a.type == cudaMemoryTypeHost;
+}
+
+static int ensure_chunk(ChunkBuf &b, int64_t cases, int64_t ev, int sum_dims, bool want_post, bool stage_in, bool stage_out) {
+    if (!b.in_done) {
+        CK(cudaEventCreateWithFlags(&b.in_done, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&b.k_done, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&b.out_done, cudaEventDisableTiming));
+    }
+    if (cases > b.cap_cases) {
+        cudaFree(b.d_off); cudaFree(b.d_labels); cudaFree(b.d_post);
+        cudaFreeHost(b.h_off); cudaFreeHost(b.h_labels); cudaFreeHost(b.h_post);
+        b.h_off = nullptr; b.h_labels = nullptr; b.h_post = nullptr; b.d_post = nullptr;
+        CK(cudaMalloc((void **)&b.d_off, (size_t)(cases + 1) * 8));
+        CK(cudaMalloc((void **)&b.d_labels, (size_t)cases * 4));
+        b.cap_cases = cases;
+    }
+    if (want_post && !b.d_post) CK(cudaMalloc((void **)&b.d_post, (size_t)b.cap_cases * sum_dims * 8));
+    if (ev > b.cap_ev) {
+        cudaFree(b.d_vars); cudaFree(b.d_vals); cudaFreeHost(b.h_vars); cudaFreeHost(b.h_vals);
+        b.h_vars = nullptr; b.h_vals = nullptr;
+        CK(cudaMalloc((void **)&b.d_vars, (size_t)ev * 4));
+        CK(cudaMalloc((void **)&b.d_vals, (size_t)ev * 4));
+        b.cap_ev = ev;
+    }
+    if (stage_in) {
+        if (!b.h_off) CK(cudaMallocHost((void **)&b.h_off, (size_t)(b.cap_cases + 1) * 8));
+        if (!b.h_vars) { CK(cudaMallocHost((void **)&b.h_vars, (size_t)b.cap_ev * 4)); CK(cudaMallocHost((void **)&b.h_vals, (size_t)b.cap_ev * 4)); }
+    }
+    if (stage_out) {
+        if (!b.h_labels) CK(cudaMallocHost((void **)&b.h_labels, (size_t)b.cap_cases * 4));
+        if (want_post && !b.h_post) CK(cudaMallocHost((void **)&b.h_post, (size_t)b.cap_cases * sum_dims * 8));
+    }
+    return FBN_OK;
+}
+
+extern "C" int fbn_run(fbn_plan *p, int64_t n_cases, const int64_t *ev_offsets, const int32_t *ev_vars,
+                       const int32_t *ev_vals, int32_t *labels_out, double *posteriors_out, fbn_stats *stats) {
+    if (!p) return fail(FBN_ERR_INVALID, "null plan");
+    if (n_cases < 0 || (n_cases > 0 && (!ev_offsets || !labels_out))) return fail(FBN_ERR_INVALID, "bad arguments");
+    auto t0 = std::chrono::steady_clock::now();
+    CK(cudaSetDevice(p->device));
+    if (stats) memset(stats, 0, sizeof(*stats));
+    if (n_cases == 0) return FBN_OK;
+    for (int64_t i = 0; i < n_cases; ++i)
+        if (ev_offsets[i + 1] < ev_offsets[i]) return fail(FBN_ERR_INVALID, "ev_offsets must be non-decreasing");
+    if (ev_offsets[n_cases] > ev_offsets[0] && (!ev_vars || !ev_vals)) return fail(FBN_ERR_INVALID, "null evidence arrays");
+    const int sd = p->hp.sum_dims;
+    const bool want_post = posteriors_out != nullptr;
+    // chunking: ~128 MB of posteriors per chunk, at least one full wave of resident tiles
+    int64_t chunk = (int64_t)(128.0 * 1048576.0 / (8.0 * sd));
+    chunk = std::max<int64_t>(chunk, (int64_t)p->grid * fbn::kLanes);
+    chunk = std::min<int64_t>(chunk, std::max<int64_t>(fbn::kLanes, (int64_t)(1024.0 * 1048576.0 / (8.0 * sd))));
+    chunk = (chunk + fbn::kLanes - 1) / fbn::kLanes * fbn::kLanes;
+    chunk = std::min<int64_t>(chunk, (n_cases + fbn::kLanes - 1) / fbn::kLanes * fbn::kLanes);
+    const int64_t n_chunks = (n_cases + chunk - 1) / chunk;
+    int64_t max_ev = 1;
+    for (int64_t c = 0; c < n_chunks; ++c) {
+        int64_t c0 = c * chunk, c1 = std::min(n_cases, c0 + chunk);
+        max_ev = std::max(max_ev, ev_offsets[c1] - ev_offsets[c0]);
+    }
+    const bool stage_in = !(is_pinned(ev_offsets) && is_pinned(ev_vars) && is_pinned(ev_vals));
+    const bool stage_out = !(is_pinned(labels_out) && is_pinned(posteriors_out));
+    struct Pending { int64_t c0 = 0, n = 0; bool active = false; } pend[kNBuf];
+    auto drain = [&](int bi) -> int {  // wait for the chunk that last used buffer bi and hand its results to the caller
+        if (!pend[bi].active) return FBN_OK;
+        ChunkBuf &b = p->buf[bi];
+        CK(cudaEventSynchronize(b.out_done));
+        if (stage_out) {
+            memcpy(labels_out + pend[bi].c0, b.h_labels, (size_t)pend[bi].n * 4);
+            if (want_post) memcpy(posteriors_out + pend[bi].c0 * sd, b.h_post, (size_t)pend[bi].n * sd * 8);
+        }
+        pend[bi].active = false;
+        return FBN_OK;
+    };
+    CK(cudaEventRecord(p->ev0, p->s_k));
+    int rc;
+    for (int64_t c = 0; c < n_chunks; ++c) {
+        const int bi = (int)(c % kNBuf);
+        ChunkBuf &b = p->buf[bi];
+        if ((rc = drain(bi)) != FBN_OK) return rc;
+        const int64_t c0 = c * chunk, n = std::min(n_cases, c0 + chunk) - c0;
+        const int64_t e0 = ev_offsets[c0], ne = ev_offsets[c0 + n] - e0;
+        if ((rc = ensure_chunk(b, chunk, max_ev, sd, want_post, stage_in, stage_out)) != FBN_OK) return rc;
+        const int64_t *src_off = ev_offsets + c0;
+        const int32_t *src_vars = ev_vars + e0, *src_vals = ev_vals + e0;
+        if (stage_in) {
+            memcpy(b.h_off, src_off, (size_t)(n + 1) * 8);
+            if (ne) { memcpy(b.h_vars, src_vars, (size_t)ne * 4); memcpy(b.h_vals, src_vals, (size_t)ne * 4); }
+            src_off = b.h_off; src_vars = b.h_vars; src_vals = b.h_vals;
+        }
+        CK(cudaMemcpyAsync(b.d_off, src_off, (size_t)(n + 1) * 8, cudaMemcpyHostToDevice, p->s_in));
+        if (ne) {
+            CK(cudaMemcpyAsync(b.d_vars, src_vars, (size_t)ne * 4, cudaMemcpyHostToDevice, p->s_in));
+            CK(cudaMemcpyAsync(b.d_vals, src_vals, (size_t)ne * 4, cudaMemcpyHostToDevice, p->s_in));
+        }
+        CK(cudaEventRecord(b.in_done, p->s_in));
+        CK(cudaStreamWaitEvent(p->s_k, b.in_done, 0));
+        CK(fbn::fused_launch(p->dp, p->grid, p->scratch, n, b.d_off, e0, b.d_vars, b.d_vals, b.d_labels,
+                             want_post ? b.d_post : nullptr, p->s_k));
+        CK(cudaEventRecord(b.k_done, p->s_k));
+        CK(cudaStreamWaitEvent(p->s_out, b.k_done, 0));
+        CK(cudaMemcpyAsync(stage_out ? b.h_labels : labels_out + c0, b.d_labels, (size_t)n * 4, cudaMemcpyDeviceToHost, p->s_out));
+        if (want_post)
+            CK(cudaMemcpyAsync(stage_out ? b.h_post : posteriors_out + c0 * sd, b.d_post, (size_t)n * sd * 8, cudaMemcpyDeviceToHost, p->s_out));
+        CK(cudaEventRecord(b.out_done, p->s_out));
+        pend[bi].c0 = c0; pend[bi].n = n; pend[bi].active = true;
+        if (stats) {
+            stats->n_launches += 1;
+            stats->h2d_bytes += (n + 1) * 8 + ne * 8;
+            stats->d2h_bytes += n * 4 + (want_post ? n * (int64_t)sd * 8 : 0);
+        }
+    }
+    CK(cudaEventRecord(p->ev1, p->s_k));
+    for (int bi = 0; bi < kNBuf; ++bi)
+        if ((rc = drain(bi)) != FBN_OK) return rc;
+    CK(cudaStreamSynchronize(p->s_k));
+    CK(cudaStreamSynchronize(p->s_in));
+    if (stats) {
+        float ms = 0;
+        CK(cudaEventElapsedTime(&ms, p->ev0, p->ev1));
+        stats->kernel_ms = ms;  // span of the compute stream (kernels + waits on their inputs)
+        stats->total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    }
+    return FBN_OK;
+}
+
+extern "C" int fbn_score_device(fbn_plan *p, int64_t n_cases, const double *posteriors, const int32_t *labels,
+                                const double *golden, const int32_t *truths, double *out4_host, void *stream) {
+    if (!p || !out4_host || n_cases < 0) return fail(FBN_ERR_INVALID, "bad arguments");
+    if (n_cases > 0 && (!posteriors || !labels || !golden || !truths)) return fail(FBN_ERR_INVALID, "null device array");
+    CK(cudaSetDevice(p->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n_cases > p->score_cap) {
+        cudaFree(p->score_case);
+        p->score_case = nullptr;
+        CK(cudaMalloc((void **)&p->score_case, (size_t)n_cases * 16));
+        p->score_cap = n_cases;
+    }
+    CK(fbn::score_launch(n_cases, p->hp.n_vars, p->hp.sum_dims, p->dp.vars, posteriors, golden, labels, truths,
+                         p->score_case, p->score_out4, st));
+    CK(cudaMemcpyAsync(out4_host, p->score_out4, 32, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    return FBN_OK;
+}

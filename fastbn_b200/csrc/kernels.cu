@@ -1,0 +1,296 @@
+// sm_100a kernels of the junction-tree hot path. One persistent kernel runs whole test cases:
+//   evidence -> Collect (deepest level first) -> Distribute -> per-variable marginals -> normalise + argmax.
+// Thread mapping: lane = test case inside a 32-case tile, warp = one column of one table. All table indices, evidence
+// masks (32-bit lambda words, one bit per case) and loop bounds are warp-uniform; all scratch accesses are coalesced
+// 256-byte rows and lane-private, so no shuffles or atomics are needed on the data path.
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "plan.h"
+
+namespace fbn {
+
+__device__ __forceinline__ double *row_ptr(double *S, int32_t row) { return S + (int64_t)row * kLanes; }
+
+struct Smem {
+    uint32_t *lam;    // [sum_dims]  bit l set <=> state allowed for case l of the tile
+    uint32_t *obs;    // [n_vars]    bit l set <=> variable observed in case l
+    double *normacc;  // [max_normslots][TEAM][32]
+    double *part;     // [max_pslots][32]
+};
+
+// COLLECT item: column `col` of clique op, rows [r0,r1).
+//   C[e] = pristine[e] * mask(e) * prod_k ( child message_k[map_k(e)] / norm_k ),  mup[col] = sum_r C[r,col]
+template <int TEAM>
+__device__ __forceinline__ void collect_item(const DevPlan &P, const Item &I, double *S, const Smem &sm, int lane, int warp) {
+    const CollectOp *__restrict__ op = P.cops + I.op;
+    const int nrest = op->nrest, ncolv = op->ncolv, nchild = op->nchild, cols = op->cols, j = I.col;
+    const uint16_t *__restrict__ cl16 = P.lam16 + op->collam_off + (int64_t)j * ncolv;
+    uint32_t cm = 0xffffffffu;
+    for (int i = 0; i < ncolv; ++i) cm &= sm.lam[__ldg(cl16 + i)];
+    double scale = 1.0;
+    const int32_t *__restrict__ invrows = P.idx32 + op->invrow_off;
+    for (int k = 0; k < nchild; ++k) scale *= *row_ptr(S, __ldg(invrows + k));
+    const int32_t *__restrict__ cpart = P.idx32 + op->colpart_off + (int64_t)j * nchild;
+    const int32_t *__restrict__ rpart = P.idx32 + op->rowpart_off;
+    const uint16_t *__restrict__ rl16 = P.lam16 + op->rowlam_off;
+    const double *__restrict__ pot = P.pot + op->pot_off;
+    double *cl = row_ptr(S, op->cl_row);
+    double acc = 0.0;
+    for (int r = I.r0; r < I.r1; ++r) {
+        uint32_t m = cm;
+        const uint16_t *rl = rl16 + (int64_t)r * nrest;
+        for (int i = 0; i < nrest; ++i) m &= sm.lam[__ldg(rl + i)];
+        const int64_t e = (int64_t)r * cols + j;
+        double v = 0.0;
+        if (m != 0u) {  // warp-uniform: skip the gathers when every case of the tile contradicts this entry
+            v = __ldg(pot + e) * scale;
+            const int32_t *rp = rpart + (int64_t)r * nchild;
+            for (int k = 0; k < nchild; ++k) v *= *row_ptr(S, __ldg(rp + k) + __ldg(cpart + k));
+            v = ((m >> lane) & 1u) ? v : 0.0;
+        }
+        cl[e * kLanes] = v;
+        acc += v;
+    }
+    if (I.pslot < 0) *row_ptr(S, op->mup_row + j) = acc;
+    else sm.part[I.pslot * kLanes + lane] = acc;
+    sm.normacc[(op->normslot * TEAM + warp) * kLanes + lane] += acc;
+}
+
+// PULL item: out = sum_r src[base + rest_r] * fac[basecol + restcol_r]
+__device__ __forceinline__ void pull_item(const DevPlan &P, const Item &I, double *S, const Smem &sm, int lane) {
+    const PullOp *__restrict__ op = P.pops + I.op;
+    const int q = I.col;
+    const int2 b = __ldg(reinterpret_cast<const int2 *>(P.idx32 + op->tbase_off) + q);
+    const double *src = row_ptr(S, op->src_row + b.x);
+    const double *fac = row_ptr(S, op->fac_row + b.y);
+    const int2 *__restrict__ tr = reinterpret_cast<const int2 *>(P.idx32 + op->trest_off);
+    double acc = 0.0;
+#pragma unroll 4
+    for (int r = I.r0; r < I.r1; ++r) {
+        const int2 t = __ldg(tr + r);
+        acc += src[(int64_t)t.x * kLanes] * fac[(int64_t)t.y * kLanes];
+    }
+    if (I.pslot >= 0) {
+        sm.part[I.pslot * kLanes + lane] = acc;
+    } else if (op->kind == 1) {
+        const double m = *row_ptr(S, op->mup_row + q);
+        *row_ptr(S, op->dst_row + q) = (m == 0.0) ? 0.0 : acc / m;  // TableDivision 0-guard, PotentialTable.cpp:718-734
+    } else {
+        *row_ptr(S, op->dst_row + q) = acc;
+    }
+}
+
+template <int TEAM>
+__device__ __forceinline__ void fin_item(const FinItem &F, double *S, const Smem &sm, int lane) {
+    double s = 0.0;
+    if (F.type == FIN_NORM) {
+        for (int w = 0; w < TEAM; ++w) s += sm.normacc[(F.slot0 * TEAM + w) * kLanes + lane];
+        *row_ptr(S, F.dst_row) = 1.0 / s;
+        return;
+    }
+    for (int i = 0; i < F.nslots; ++i) s += sm.part[(F.slot0 + i) * kLanes + lane];
+    if (F.type == FIN_D) {
+        const double m = *row_ptr(S, F.aux_row);
+        s = (m == 0.0) ? 0.0 : s / m;
+    }
+    *row_ptr(S, F.dst_row) = s;
+}
+
+template <int TEAM>
+__global__ void __launch_bounds__(TEAM * 32) jt_fused_kernel(const DevPlan P, double *__restrict__ scratch, int64_t n_cases,
+                                                            const int64_t *__restrict__ ev_off, int64_t ev_base,
+                                                            const int32_t *__restrict__ ev_vars,
+                                                            const int32_t *__restrict__ ev_vals, int32_t *__restrict__ labels,
+                                                            double *__restrict__ post, int64_t n_tiles) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    Smem sm;
+    sm.lam = reinterpret_cast<uint32_t *>(smem_raw);
+    sm.obs = sm.lam + P.sum_dims;
+    size_t o = ((size_t)(P.sum_dims + P.n_vars) * 4 + 15) & ~(size_t)15;
+    sm.normacc = reinterpret_cast<double *>(smem_raw + o);
+    sm.part = sm.normacc + (size_t)P.max_normslots * TEAM * kLanes;
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    double *S = scratch + (int64_t)blockIdx.x * P.tile_rows * kLanes + lane;  // lane-private column of this CTA's tile
+
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        // ---- evidence -> lambda bit words (LoadDiscreteEvidence, src/JunctionTree.cpp:316-383, mask form :386-457)
+        if (TEAM > 1) __syncthreads();
+        for (int i = threadIdx.x; i < P.sum_dims + P.n_vars; i += TEAM * 32) sm.lam[i] = i < P.sum_dims ? 0xffffffffu : 0u;
+        if (TEAM > 1) __syncthreads(); else __syncwarp();
+        const int64_t cs = tile * kLanes + lane;
+        const bool valid = cs < n_cases;
+        if (valid) {
+            const int64_t k1 = ev_off[cs + 1] - ev_base;
+            for (int64_t k = ev_off[cs] - ev_base + warp; k < k1; k += TEAM) {
+                const int v = ev_vars[k], val = ev_vals[k];
+                if (v < 0 || v >= P.n_vars) continue;  // src/JunctionTree.cpp:326-331
+                const VarInfo vi = P.vars[v];
+                atomicOr(&sm.obs[v], 1u << lane);
+                for (int d = 0; d < vi.dim; ++d)
+                    if (d != val) atomicAnd(&sm.lam[vi.off + d], ~(1u << lane));
+            }
+        }
+        if (TEAM > 1) __syncthreads(); else __syncwarp();
+
+        for (int ph = 0; ph < P.n_phases; ++ph) {
+            const Phase p = P.phases[ph];
+            if (p.kind == 0) {
+                for (int s = 0; s < p.n_normslots; ++s) sm.normacc[(s * TEAM + warp) * kLanes + lane] = 0.0;
+                for (int it = p.item_begin + warp; it < p.item_end; it += TEAM) {
+                    const Item I = P.items[it];
+                    collect_item<TEAM>(P, I, S, sm, lane, warp);
+                }
+            } else {
+                for (int it = p.item_begin + warp; it < p.item_end; it += TEAM) {
+                    const Item I = P.items[it];
+                    pull_item(P, I, S, sm, lane);
+                }
+            }
+            if (p.fin_end > p.fin_begin) {
+                if (TEAM > 1) __syncthreads();
+                for (int f = p.fin_begin + warp; f < p.fin_end; f += TEAM) fin_item<TEAM>(P.fins[f], S, sm, lane);
+            }
+            if (TEAM > 1) __syncthreads();
+        }
+
+        // ---- posteriors + label (GetProbabilitiesOneNode :1392-1454, Inference::ArgMax Inference.cpp:92-102)
+        for (int v = warp; v < P.n_vars; v += TEAM) {
+            const VarInfo vi = P.vars[v];
+            const bool observed = (sm.obs[v] >> lane) & 1u;
+            const double *mg = row_ptr(S, P.mg_row0 + vi.off);
+            double sum = 0.0;
+            for (int d = 0; d < vi.dim; ++d) sum += mg[d * kLanes];
+            double best = 0.0;
+            int arg = -1;
+            for (int d = 0; d < vi.dim; ++d) {
+                const double pr = observed ? 0.0 : mg[d * kLanes] / sum;
+                if (valid && post) post[cs * P.sum_dims + vi.off + d] = pr;
+                if (pr > best) { best = pr; arg = d; }
+            }
+            if (v == P.query_var && valid && labels) labels[cs] = arg;
+        }
+    }
+}
+
+// ---- scoring against golden posteriors (Inference::CalculateMSE / CalculateHellingerDistance / Round / Accuracy,
+//      src/Inference.cpp:46-61,153-206). One warp per case; out_case[c] = {mse, hd}.
+__device__ __forceinline__ double round7(double number) {  // Round(number, 7), src/Inference.cpp:195-206
+    long long ip = (long long)number;
+    number -= (double)ip;
+    for (int i = 0; i < 7; ++i) number *= 10;
+    number = (double)(long long)(number + 0.5);
+    for (int i = 0; i < 7; ++i) number /= 10;
+    return (double)ip + number;
+}
+
+__global__ void score_cases_kernel(int64_t n_cases, int n_vars, int sum_dims, const VarInfo *__restrict__ vars,
+                                   const double *__restrict__ post, const double *__restrict__ golden,
+                                   double *__restrict__ out_case) {
+    const int lane = threadIdx.x & 31;
+    const int64_t c = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (c >= n_cases) return;
+    const double *p = post + c * sum_dims, *g = golden + c * sum_dims;
+    double e_mse = 0.0, e_hd = 0.0;
+    int num = 0;
+    for (int v = lane; v < n_vars; v += 32) {
+        const VarInfo vi = vars[v];
+        if (g[vi.off] > 0) {
+            num += vi.dim;
+            for (int d = 0; d < vi.dim; ++d) {
+                const double a = round7(p[vi.off + d]), b = g[vi.off + d];
+                e_mse += (a - b) * (a - b);
+                const double h = sqrt(a) - sqrt(b);
+                e_hd += h * h;
+            }
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        e_mse += __shfl_xor_sync(0xffffffffu, e_mse, o);
+        e_hd += __shfl_xor_sync(0xffffffffu, e_hd, o);
+        num += __shfl_xor_sync(0xffffffffu, num, o);
+    }
+    if (lane == 0) {
+        out_case[2 * c] = sqrt(e_mse / num);
+        out_case[2 * c + 1] = sqrt(e_hd / num);
+    }
+}
+
+// deterministic single-block reduction: out4 = {n_correct, n_total, sum_mse, sum_hd}
+__global__ void score_reduce_kernel(int64_t n_cases, const double *__restrict__ out_case, const int32_t *__restrict__ labels,
+                                    const int32_t *__restrict__ truths, double *__restrict__ out4) {
+    __shared__ double s[3][1024];
+    double a = 0, b = 0, c = 0;
+    for (int64_t i = threadIdx.x; i < n_cases; i += blockDim.x) {
+        a += out_case[2 * i];
+        b += out_case[2 * i + 1];
+        c += (labels[i] == truths[i]) ? 1.0 : 0.0;
+    }
+    s[0][threadIdx.x] = a; s[1][threadIdx.x] = b; s[2][threadIdx.x] = c;
+    __syncthreads();
+    for (int o = blockDim.x / 2; o > 0; o >>= 1) {
+        if ((int)threadIdx.x < o)
+            for (int k = 0; k < 3; ++k) s[k][threadIdx.x] += s[k][threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) { out4[0] = s[2][0]; out4[1] = (double)n_cases; out4[2] = s[0][0]; out4[3] = s[1][0]; }
+}
+
+// ---- launch helpers (called from capi.cu) ------------------------------------------------------------------------
+size_t fused_smem_bytes(const DevPlan &P) {
+    size_t o = ((size_t)(P.sum_dims + P.n_vars) * 4 + 15) & ~(size_t)15;
+    return o + ((size_t)P.max_normslots * P.team + (size_t)P.max_pslots) * kLanes * sizeof(double);
+}
+
+template <int TEAM>
+static cudaError_t prep(const DevPlan &P, int *blocks_per_sm) {
+    size_t smem = fused_smem_bytes(P);
+    cudaError_t e = cudaFuncSetAttribute(jt_fused_kernel<TEAM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, jt_fused_kernel<TEAM>, TEAM * 32, smem);
+}
+
+cudaError_t fused_prepare(const DevPlan &P, int *blocks_per_sm) {
+    switch (P.team) {
+        case 1: return prep<1>(P, blocks_per_sm);
+        case 2: return prep<2>(P, blocks_per_sm);
+        case 4: return prep<4>(P, blocks_per_sm);
+        case 8: return prep<8>(P, blocks_per_sm);
+        case 16: return prep<16>(P, blocks_per_sm);
+        case 32: return prep<32>(P, blocks_per_sm);
+    }
+    return cudaErrorInvalidValue;
+}
+
+cudaError_t fused_launch(const DevPlan &P, int grid, double *scratch, int64_t n_cases, const int64_t *ev_off, int64_t ev_base,
+                         const int32_t *ev_vars, const int32_t *ev_vals, int32_t *labels, double *post, cudaStream_t st) {
+    const int64_t n_tiles = (n_cases + kLanes - 1) / kLanes;
+    if (n_tiles == 0) return cudaSuccess;
+    if (grid > n_tiles) grid = (int)n_tiles;
+    size_t smem = fused_smem_bytes(P);
+#define FBN_LAUNCH(T) jt_fused_kernel<T><<<grid, T * 32, smem, st>>>(P, scratch, n_cases, ev_off, ev_base, ev_vars, ev_vals, labels, post, n_tiles)
+    switch (P.team) {
+        case 1: FBN_LAUNCH(1); break;
+        case 2: FBN_LAUNCH(2); break;
+        case 4: FBN_LAUNCH(4); break;
+        case 8: FBN_LAUNCH(8); break;
+        case 16: FBN_LAUNCH(16); break;
+        case 32: FBN_LAUNCH(32); break;
+        default: return cudaErrorInvalidValue;
+    }
+#undef FBN_LAUNCH
+    return cudaGetLastError();
+}
+
+cudaError_t score_launch(int64_t n_cases, int n_vars, int sum_dims, const VarInfo *vars, const double *post, const double *golden,
+                         const int32_t *labels, const int32_t *truths, double *out_case, double *out4, cudaStream_t st) {
+    if (n_cases > 0) {
+        const int wpb = 8;
+        score_cases_kernel<<<(unsigned)((n_cases + wpb - 1) / wpb), wpb * 32, 0, st>>>(n_cases, n_vars, sum_dims, vars, post, golden, out_case);
+    }
+    score_reduce_kernel<<<1, 1024, 0, st>>>(n_cases, out_case, labels, truths, out4);
+    return cudaGetLastError();
+}
+
+}  // namespace fbn

@@ -1,0 +1,416 @@
+// Host-side planner: flat reference tree (fbn_tree_desc) -> per-tree constant arrays + warp work items.
+// Replaces, once per tree, what the reference recomputes for every level of every case in the "pre" phases
+// of src/JunctionTree.cpp:586-639 and :834-880 (index maps by GetConfigValueByTableIndex /
+// GetTableIndexByConfigValue, src/PotentialTableBase.cpp:547-566).
+#include "plan.h"
+
+#include <algorithm>
+#include <cstdio>
+#include <numeric>
+#include <string>
+
+#include "../../include/fastbn_b200.h"
+
+namespace fbn {
+namespace {
+
+struct Table {
+    std::vector<int> vars, dims, stride;
+    int64_t size = 1;
+    int find(int v) const {
+        for (size_t i = 0; i < vars.size(); ++i)
+            if (vars[i] == v) return (int)i;
+        return -1;
+    }
+};
+
+// cum_levels of the reference: stride[n-1] = 1, stride[i] = stride[i+1]*dims[i+1] (PotentialTableBase.cpp:599-607)
+bool finish_table(Table &t, const int32_t *var_dims, int n_vars, std::string &err) {
+    size_t n = t.vars.size();
+    t.dims.resize(n);
+    t.stride.resize(n);
+    t.size = 1;
+    for (size_t i = 0; i < n; ++i) {
+        if (t.vars[i] < 0 || t.vars[i] >= n_vars) {
+            err = "table variable out of range";
+            return false;
+        }
+        for (size_t k = 0; k < i; ++k)
+            if (t.vars[k] == t.vars[i]) {
+                err = "duplicate variable in a table";
+                return false;
+            }
+        t.dims[i] = var_dims[t.vars[i]];
+    }
+    for (size_t i = n; i-- > 0;) {
+        t.stride[i] = (int)t.size;
+        t.size *= t.dims[i];
+        if (t.size > (int64_t)1 << 30) {
+            err = "table exceeds 2^30 entries (the reference itself is limited to int32 table sizes)";
+            return false;
+        }
+    }
+    return true;
+}
+
+// For every configuration of `sub` (a list of positions into tab.vars, row-major in the given order) the partial
+// entry index sum digit*stride. Enumerated with an odometer, no div/mod.
+std::vector<int32_t> enumerate_offsets(const Table &tab, const std::vector<int> &pos) {
+    int64_t n = 1;
+    for (int p : pos) n *= tab.dims[p];
+    std::vector<int32_t> out((size_t)n);
+    std::vector<int> dig(pos.size(), 0);
+    int32_t cur = 0;
+    for (int64_t i = 0; i < n; ++i) {
+        out[(size_t)i] = cur;
+        for (size_t k = pos.size(); k-- > 0;) {
+            int p = pos[k];
+            if (++dig[k] < tab.dims[p]) {
+                cur += tab.stride[p];
+                break;
+            }
+            cur -= (tab.dims[p] - 1) * tab.stride[p];
+            dig[k] = 0;
+        }
+    }
+    return out;
+}
+
+// digits of every configuration of `pos` (row-major), flattened n x pos.size()
+std::vector<int> enumerate_digits(const Table &tab, const std::vector<int> &pos) {
+    int64_t n = 1;
+    for (int p : pos) n *= tab.dims[p];
+    std::vector<int> out((size_t)n * pos.size());
+    std::vector<int> dig(pos.size(), 0);
+    for (int64_t i = 0; i < n; ++i) {
+        for (size_t k = 0; k < pos.size(); ++k) out[(size_t)i * pos.size() + k] = dig[k];
+        for (size_t k = pos.size(); k-- > 0;) {
+            if (++dig[k] < tab.dims[pos[k]]) break;
+            dig[k] = 0;
+        }
+    }
+    return out;
+}
+
+}  // namespace
+
+std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P) {
+    std::string err;
+    const int nv = t.n_vars, nc = t.n_cliques, ns = t.n_separators;
+    if (nv <= 0 || nc <= 0 || ns != nc - 1) return "need n_vars > 0, n_cliques > 0 and n_separators == n_cliques - 1";
+    if (!t.var_dims || !t.table_nvars || !t.table_vars || !t.clique_potentials || (ns > 0 && (!t.sep_parent || !t.sep_child)))
+        return "null array in fbn_tree_desc";
+    if (t.root < 0 || t.root >= nc) return "root out of range";
+    if (t.query_var < 0 || t.query_var >= nv) return "query_var out of range";
+    if (team < 1 || team > 32 || (team & (team - 1))) return "team_warps must be a power of two in [1,32]";
+    P = HostPlan();
+    P.n_vars = nv; P.n_cliques = nc; P.n_seps = ns; P.query_var = t.query_var; P.team = team;
+    P.vars.resize(nv);
+    int64_t sd = 0;
+    for (int v = 0; v < nv; ++v) {
+        if (t.var_dims[v] <= 0) return "variable with non-positive domain size";
+        P.vars[v].off = (int32_t)sd;
+        P.vars[v].dim = t.var_dims[v];
+        sd += t.var_dims[v];
+    }
+    if (sd > 65535) return "sum of domain sizes exceeds 65535 (lambda index is 16 bit)";
+    P.sum_dims = (int32_t)sd;
+
+    // ---- tables ----
+    std::vector<Table> clq(nc), sep(ns);
+    {
+        int64_t pos = 0;
+        for (int i = 0; i < nc + ns; ++i) {
+            Table &tb = i < nc ? clq[i] : sep[i - nc];
+            if (t.table_nvars[i] <= 0) return "empty table";
+            tb.vars.assign(t.table_vars + pos, t.table_vars + pos + t.table_nvars[i]);
+            pos += t.table_nvars[i];
+            if (!finish_table(tb, t.var_dims, nv, err)) return err;
+        }
+    }
+    std::vector<int64_t> pot_off(nc + 1, 0);
+    for (int c = 0; c < nc; ++c) pot_off[c + 1] = pot_off[c] + clq[c].size;
+    P.clique_entries = pot_off[nc];
+
+    // ---- topology (MarkLevel, src/JunctionTree.cpp:137-181) ----
+    std::vector<int> up_sep(nc, -1), depth(nc, -1);
+    std::vector<std::vector<int>> kids(nc);
+    for (int s = 0; s < ns; ++s) {
+        int p = t.sep_parent[s], c = t.sep_child[s];
+        if (p < 0 || p >= nc || c < 0 || c >= nc || p == c) return "separator endpoints out of range";
+        if (up_sep[c] != -1) return "clique with two upstream separators";
+        up_sep[c] = s;
+        kids[p].push_back(s);
+    }
+    if (up_sep[t.root] != -1) return "root has an upstream separator";
+    int maxdepth = 0;
+    {
+        std::vector<int> q{t.root};
+        depth[t.root] = 0;
+        for (size_t h = 0; h < q.size(); ++h)
+            for (int s : kids[q[h]]) {
+                int c = t.sep_child[s];
+                if (depth[c] != -1) return "cycle in the tree";
+                depth[c] = depth[q[h]] + 1;
+                maxdepth = std::max(maxdepth, depth[c]);
+                q.push_back(c);
+            }
+        if ((int)q.size() != nc) return "tree is not connected";
+    }
+    P.n_levels = 2 * maxdepth + 1;
+    // separator scope checks + ReorganizeTableStorage invariant (src/JunctionTree.cpp:235-281)
+    for (int s = 0; s < ns; ++s) {
+        const Table &S = sep[s], &C = clq[t.sep_child[s]], &Pa = clq[t.sep_parent[s]];
+        if (S.vars.size() > C.vars.size()) return "separator larger than its child clique";
+        size_t base = C.vars.size() - S.vars.size();
+        for (size_t i = 0; i < S.vars.size(); ++i) {
+            if (C.vars[base + i] != S.vars[i]) return "child clique does not end with its upstream separator's variables";
+            if (Pa.find(S.vars[i]) < 0) return "separator variable missing from parent clique";
+        }
+    }
+
+    // ---- scratch row regions ----
+    std::vector<int64_t> sep_off(ns + 1, 0);
+    for (int s = 0; s < ns; ++s) sep_off[s + 1] = sep_off[s] + sep[s].size;
+    P.sep_entries = sep_off[ns];
+    int64_t rows_total = P.clique_entries + 2 * (P.sep_entries + 1) + nc + sd;
+    if (rows_total > ((int64_t)1 << 30)) return "tree too large: more than 2^30 scratch rows per tile";
+    P.cl_row0 = 0;
+    P.mup_row0 = (int32_t)P.clique_entries;
+    P.dn_row0 = P.mup_row0 + (int32_t)P.sep_entries + 1;
+    P.inv_row0 = P.dn_row0 + (int32_t)P.sep_entries + 1;
+    P.mg_row0 = P.inv_row0 + nc;
+    P.tile_rows = (int32_t)rows_total;
+    auto cl_row = [&](int c) { return (int32_t)pot_off[c]; };
+    auto mup_row = [&](int c) { return c == t.root ? P.mup_row0 + (int32_t)P.sep_entries : P.mup_row0 + (int32_t)sep_off[up_sep[c]]; };
+    auto fac_row = [&](int c) { return c == t.root ? P.inv_row0 + c : P.dn_row0 + (int32_t)sep_off[up_sep[c]]; };
+    auto ncols = [&](int c) { return c == t.root ? (int64_t)1 : sep[up_sep[c]].size; };
+
+    P.pot.assign(t.clique_potentials, t.clique_potentials + pot_off[nc]);
+
+    // ---- collect ops ----
+    P.cops.resize(nc);
+    for (int c = 0; c < nc; ++c) {
+        const Table &C = clq[c];
+        CollectOp &op = P.cops[c];
+        op = CollectOp();
+        op.pot_off = pot_off[c];
+        op.ncolv = c == t.root ? 0 : (int32_t)sep[up_sep[c]].vars.size();
+        op.nrest = (int32_t)C.vars.size() - op.ncolv;
+        op.cols = (int32_t)ncols(c);
+        op.rows = (int32_t)(C.size / op.cols);
+        op.cl_row = cl_row(c);
+        op.mup_row = mup_row(c);
+        op.inv_row = P.inv_row0 + c;
+        op.nchild = (int32_t)kids[c].size();
+        std::vector<int> rpos(op.nrest), cpos(op.ncolv);
+        std::iota(rpos.begin(), rpos.end(), 0);
+        std::iota(cpos.begin(), cpos.end(), op.nrest);
+        // lambda-bit indices (evidence mask): var offset + digit
+        op.rowlam_off = (int64_t)P.lam16.size();
+        {
+            std::vector<int> dg = enumerate_digits(C, rpos);
+            for (int64_t r = 0; r < op.rows; ++r)
+                for (int i = 0; i < op.nrest; ++i)
+                    P.lam16.push_back((uint16_t)(P.vars[C.vars[rpos[i]]].off + dg[(size_t)r * op.nrest + i]));
+        }
+        op.collam_off = (int64_t)P.lam16.size();
+        {
+            std::vector<int> dg = enumerate_digits(C, cpos);
+            for (int64_t j = 0; j < op.cols; ++j)
+                for (int i = 0; i < op.ncolv; ++i)
+                    P.lam16.push_back((uint16_t)(P.vars[C.vars[cpos[i]]].off + dg[(size_t)j * op.ncolv + i]));
+        }
+        // child message index maps, split into row part + column part (TableExtensionMain, PotentialTable.cpp:603-613)
+        std::vector<std::vector<int32_t>> rp(op.nchild), cp(op.nchild);
+        for (int k = 0; k < op.nchild; ++k) {
+            int s = kids[c][k];
+            Table V = C;  // same shape, strides of the separator (0 for variables outside it)
+            for (size_t i = 0; i < V.vars.size(); ++i) {
+                int ps = sep[s].find(V.vars[i]);
+                V.stride[i] = ps < 0 ? 0 : sep[s].stride[ps];
+            }
+            rp[k] = enumerate_offsets(V, rpos);
+            cp[k] = enumerate_offsets(V, cpos);
+            int32_t base = P.mup_row0 + (int32_t)sep_off[s];
+            for (auto &x : rp[k]) x += base;
+        }
+        op.rowpart_off = (int64_t)P.idx32.size();
+        for (int64_t r = 0; r < op.rows; ++r)
+            for (int k = 0; k < op.nchild; ++k) P.idx32.push_back(rp[k][(size_t)r]);
+        op.colpart_off = (int64_t)P.idx32.size();
+        for (int64_t j = 0; j < op.cols; ++j)
+            for (int k = 0; k < op.nchild; ++k) P.idx32.push_back(cp[k][(size_t)j]);
+        op.invrow_off = (int64_t)P.idx32.size();
+        for (int k = 0; k < op.nchild; ++k) P.idx32.push_back(P.inv_row0 + t.sep_child[kids[c][k]]);
+    }
+
+    // ---- pull ops: distribute (one per non-root clique) + marginals (one per variable) ----
+    auto make_pull = [&](const Table &X, const std::vector<int> &tpos, int64_t xcols, bool col_is_idx) {
+        PullOp op = PullOp();
+        std::vector<int> rest;
+        for (int i = 0; i < (int)X.vars.size(); ++i)
+            if (std::find(tpos.begin(), tpos.end(), i) == tpos.end()) rest.push_back(i);
+        std::vector<int32_t> tb = enumerate_offsets(X, tpos), tr = enumerate_offsets(X, rest);
+        op.nT = (int32_t)tb.size();
+        op.nR = (int32_t)tr.size();
+        if (P.idx32.size() & 1) P.idx32.push_back(0);  // int2 alignment
+        op.tbase_off = (int64_t)P.idx32.size();
+        for (int32_t x : tb) { P.idx32.push_back(x); P.idx32.push_back(col_is_idx ? x : (int32_t)(x % xcols)); }
+        op.trest_off = (int64_t)P.idx32.size();
+        for (int32_t x : tr) { P.idx32.push_back(x); P.idx32.push_back(col_is_idx ? x : (int32_t)(x % xcols)); }
+        return op;
+    };
+    std::vector<int> dist_op(nc, -1);
+    for (int c = 0; c < nc; ++c) {
+        if (c == t.root) continue;
+        int s = up_sep[c], p = t.sep_parent[s];
+        std::vector<int> tpos;
+        for (int v : sep[s].vars) tpos.push_back(clq[p].find(v));
+        PullOp op = make_pull(clq[p], tpos, ncols(p), false);
+        op.kind = 1;
+        op.src_row = cl_row(p);
+        op.fac_row = fac_row(p);
+        op.mup_row = mup_row(c);
+        op.dst_row = P.dn_row0 + (int32_t)sep_off[s];
+        dist_op[c] = (int)P.pops.size();
+        P.pops.push_back(op);
+        P.parent_entries += clq[p].size;
+    }
+    // marginal source: the smallest table (separator preferred on ties) containing the variable; any calibrated
+    // table gives the same marginal (the reference takes the smallest clique, src/JunctionTree.cpp:1417-1434)
+    std::vector<int> marg_op(nv, -1), marg_avail(nv, 0);
+    P.marg_source.assign(nv, -1);
+    double ref_marg_entries = 0;
+    for (int v = 0; v < nv; ++v) {
+        int best = -1;
+        int64_t best_size = INT64_MAX;
+        for (int s = 0; s < ns; ++s)
+            if (sep[s].find(v) >= 0 && sep[s].size < best_size) { best = nc + s; best_size = sep[s].size; }
+        for (int c = 0; c < nc; ++c)
+            if (clq[c].find(v) >= 0 && clq[c].size < best_size) { best = c; best_size = clq[c].size; }
+        if (best < 0) return "variable " + std::to_string(v) + " does not appear in any clique";
+        {   // reference rule, for the algorithmic-bytes figure only
+            size_t mn = SIZE_MAX; int64_t sz = 0;
+            for (int c = 0; c < nc; ++c)
+                if (clq[c].vars.size() < mn && clq[c].find(v) >= 0) { mn = clq[c].vars.size(); sz = clq[c].size; }
+            ref_marg_entries += (double)sz;
+        }
+        P.marg_source[v] = best;
+        PullOp op;
+        if (best >= nc) {
+            int s = best - nc, c = t.sep_child[s];
+            op = make_pull(sep[s], {sep[s].find(v)}, 1, true);
+            op.src_row = P.mup_row0 + (int32_t)sep_off[s];
+            op.fac_row = P.dn_row0 + (int32_t)sep_off[s];
+            marg_avail[v] = depth[c];
+        } else {
+            int c = best;
+            op = make_pull(clq[c], {clq[c].find(v)}, ncols(c), false);
+            op.src_row = cl_row(c);
+            op.fac_row = fac_row(c);
+            marg_avail[v] = depth[c];
+        }
+        op.kind = 2;
+        op.mup_row = 0;
+        op.dst_row = P.mg_row0 + P.vars[v].off;
+        marg_op[v] = (int)P.pops.size();
+        P.pops.push_back(op);
+        P.marginal_entries += best_size;
+    }
+
+    // ---- phases, warp work items, split-column partial slots ----
+    // A column (collect) / target entry (pull) is one item unless its row range is long and the phase has too few
+    // columns to keep `team` warps busy; then the rows are cut into chunks whose partial sums meet in shared memory.
+    const int kMaxPslots = 192;
+    auto emit_phase = [&](int kind, const std::vector<int> &ops) {
+        Phase ph = Phase();
+        ph.kind = kind;
+        ph.item_begin = (int32_t)P.items.size();
+        ph.fin_begin = (int32_t)P.fins.size();
+        int64_t work = 0;
+        for (int o : ops) work += kind == 0 ? (int64_t)P.cops[o].rows * P.cops[o].cols : (int64_t)P.pops[o].nT * P.pops[o].nR;
+        int64_t target = std::max<int64_t>(32, work / (4 * (int64_t)team));
+        int pslots = 0, normslots = 0;
+        for (int pass = 0; pass < 8; ++pass) {  // coarsen the split until the partial slots fit
+            pslots = 0;
+            for (int o : ops) {
+                int64_t rows = kind == 0 ? P.cops[o].rows : P.pops[o].nR, cols = kind == 0 ? P.cops[o].cols : P.pops[o].nT;
+                int64_t chunks = team == 1 ? 1 : (rows + target - 1) / target;
+                if (chunks > 1) pslots += (int)(chunks * cols);
+            }
+            if (pslots <= kMaxPslots) break;
+            target *= 4;
+        }
+        if (pslots > kMaxPslots) target = INT64_MAX / 4;
+        pslots = 0;
+        for (int o : ops) {
+            int64_t rows = kind == 0 ? P.cops[o].rows : P.pops[o].nR, cols = kind == 0 ? P.cops[o].cols : P.pops[o].nT;
+            int64_t chunks = team == 1 ? 1 : std::min<int64_t>(rows, (rows + target - 1) / target);
+            int64_t per = (rows + chunks - 1) / chunks;
+            chunks = (rows + per - 1) / per;
+            if (kind == 0) P.cops[o].normslot = normslots++;
+            for (int64_t j = 0; j < cols; ++j) {
+                if (chunks > 1) {
+                    FinItem f = FinItem();
+                    if (kind == 0) { f.type = FIN_MUP; f.dst_row = P.cops[o].mup_row + (int32_t)j; }
+                    else if (P.pops[o].kind == 1) { f.type = FIN_D; f.dst_row = P.pops[o].dst_row + (int32_t)j; f.aux_row = P.pops[o].mup_row + (int32_t)j; }
+                    else { f.type = FIN_MARG; f.dst_row = P.pops[o].dst_row + (int32_t)j; }
+                    f.slot0 = pslots;
+                    f.nslots = (int32_t)chunks;
+                    P.fins.push_back(f);
+                }
+                for (int64_t ch = 0; ch < chunks; ++ch) {
+                    Item it = Item();
+                    it.op = o;
+                    it.col = (int32_t)j;
+                    it.r0 = (int32_t)(ch * per);
+                    it.r1 = (int32_t)std::min<int64_t>(rows, (ch + 1) * per);
+                    it.pslot = chunks > 1 ? pslots++ : -1;
+                    P.items.push_back(it);
+                }
+            }
+            if (kind == 0) {
+                FinItem f = FinItem();
+                f.type = FIN_NORM;
+                f.dst_row = P.cops[o].inv_row;
+                f.slot0 = P.cops[o].normslot;
+                f.nslots = 1;
+                P.fins.push_back(f);
+            }
+        }
+        ph.item_end = (int32_t)P.items.size();
+        ph.fin_end = (int32_t)P.fins.size();
+        ph.n_normslots = normslots;
+        P.max_normslots = std::max(P.max_normslots, normslots);
+        P.max_pslots = std::max(P.max_pslots, pslots);
+        P.phases.push_back(ph);
+    };
+    for (int d = maxdepth; d >= 0; --d) {  // Collect: deepest cliques first (src/JunctionTree.cpp:1240-1306)
+        std::vector<int> ops;
+        for (int c = 0; c < nc; ++c)
+            if (depth[c] == d) ops.push_back(c);
+        emit_phase(0, ops);
+    }
+    for (int d = 1; d <= maxdepth + 1; ++d) {  // Distribute (src/JunctionTree.cpp:1308-1333) + marginals as soon as ready
+        std::vector<int> ops;
+        for (int c = 0; c < nc; ++c)
+            if (depth[c] == d) ops.push_back(dist_op[c]);
+        for (int v = 0; v < nv; ++v)
+            if (marg_avail[v] == d - 1) ops.push_back(marg_op[v]);
+        if (!ops.empty()) emit_phase(1, ops);
+    }
+
+    // ---- byte accounting ----
+    // B = 8(Tc+Ts) + sum_edges(24|child| + 24|parent| + 32|sep|) + sum_vars 8|marginal clique| + 8 sum_dims
+    double child_entries = (double)(P.clique_entries - clq[t.root].size);
+    P.alg_bytes_per_case = 8.0 * (double)(P.clique_entries + P.sep_entries) + 24.0 * child_entries +
+                           24.0 * (double)P.parent_entries + 32.0 * (double)P.sep_entries + 8.0 * ref_marg_entries + 8.0 * (double)sd;
+    // what the fused kernel must move per case: clique write (collect) + parent reads (distribute) + marginal reads
+    // + separator up/down rows written once and read once + posterior/label output
+    P.kernel_bytes_per_case = 8.0 * (double)(P.clique_entries + P.parent_entries + P.marginal_entries) +
+                              32.0 * (double)P.sep_entries + 8.0 * (double)sd + 4.0;
+    return "";
+}
+
+}  // namespace fbn

@@ -1,0 +1,134 @@
+// Flattened junction-tree plan shared by the host-side planner (plan.cpp) and the sm_100a kernels (kernels.cu).
+//
+// Data layout in HBM ("scratch"): one TILE = 32 test cases, interleaved. A tile owns `tile_rows` ROWS of
+// 32 doubles (256 B, lane = case), so every access a warp makes is one fully coalesced 256-byte row no matter how
+// irregular the table index map is, and all index arithmetic is warp-uniform. Row regions of a tile:
+//   [cl_row0 ..)   one row per clique-table entry           (reference: Clique::p_table.potentials)
+//   [mup_row0 ..)  one row per separator entry, up message   (reference: Separator::p_table after Collect)
+//   [dn_row0 ..)   one row per separator entry, down ratio   (reference: Separator::p_table after Distribute / old)
+//   [inv_row0 ..)  one row per clique: 1 / (sum of the clique after Collect)  (reference: Normalize(), PotentialTableBase.cpp:433-445)
+//   [mg_row0 ..)   one row per (variable, state): unnormalised marginal
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+namespace fbn {
+
+constexpr int kLanes = 32;  // cases per tile == warp width
+
+// --- device-visible op descriptors -------------------------------------------------------------------------------
+// COLLECT of clique C (fuses reference steps: reset from backup [JunctionTree.cpp:302-311], evidence masking
+// [LoadEvidenceToNodes :386-457], clique *= child messages [CliqueLevelCollection :829-941], column sums into the
+// upstream separator [SeparatorLevelCollectionOptimized :1056-1148]).
+// The clique table is viewed as rows x cols, cols = |upstream separator| (trailing variables), root: cols = 1.
+struct CollectOp {
+    int64_t pot_off;      // into pot[]: pristine potentials (rows*cols doubles, per-tree constant)
+    int64_t rowlam_off;   // into lam16[]: rows*nrest lambda-bit indices of the leading (non-separator) variables
+    int64_t collam_off;   // into lam16[]: cols*ncolv lambda-bit indices of the trailing (separator) variables
+    int64_t rowpart_off;  // into idx32[]: rows*nchild  (absolute scratch row of child k's message, row part)
+    int64_t colpart_off;  // into idx32[]: cols*nchild  (column part)
+    int64_t invrow_off;   // into idx32[]: nchild absolute scratch rows holding 1/norm of each child clique
+    int32_t cl_row;       // scratch row of entry 0 of this clique
+    int32_t mup_row;      // scratch row of entry 0 of this clique's upward message (root: dummy row)
+    int32_t inv_row;      // scratch row receiving 1/sum(clique)
+    int32_t rows, cols;
+    int32_t nrest, ncolv;
+    int32_t nchild;
+    int32_t normslot;     // index of this op among the collect ops of its phase
+    int32_t pad;
+};
+
+// PULL: out[q] = sum_r src[tbase[q].x + trest[r].x] * fac[tbase[q].y + trest[r].y]
+//  kind 1 (distribute, reference SeparatorLevelDistribution :700-816 + CliqueLevelDistributionOptimized :1150-1238):
+//          src = parent clique, fac = parent's down ratio; dn[q] = mup[q]==0 ? 0 : out[q]/mup[q]
+//  kind 2 (marginal of one variable, reference GetProbabilitiesOneNode :1392-1454): mg[q] = out[q]
+struct PullOp {
+    int64_t tbase_off;  // into idx32[] (int2 pairs): nT pairs
+    int64_t trest_off;  // into idx32[] (int2 pairs): nR pairs
+    int32_t src_row;
+    int32_t fac_row;
+    int32_t mup_row;    // kind 1 only
+    int32_t dst_row;
+    int32_t nT, nR;
+    int32_t kind;
+    int32_t pad;
+};
+
+// One unit of warp work: column `col` of op `op`, rows [r0, r1). pslot >= 0: the row range of this column is split
+// over several items and this item's partial sum goes to shared partial slot pslot (combined by a FinItem).
+struct Item {
+    int32_t op, col, r0, r1, pslot, pad0, pad1, pad2;
+};
+
+enum FinType : int32_t { FIN_MUP = 0, FIN_NORM = 1, FIN_D = 2, FIN_MARG = 3 };
+struct FinItem {
+    int32_t type;
+    int32_t dst_row;   // FIN_MUP: mup row; FIN_NORM: inv row; FIN_D: dn row; FIN_MARG: mg row
+    int32_t aux_row;   // FIN_D: mup row (divisor)
+    int32_t slot0;     // first partial slot (FIN_NORM: normslot)
+    int32_t nslots;    // number of partial slots
+    int32_t pad0, pad1, pad2;
+};
+
+struct Phase {
+    int32_t kind;  // 0 = collect items, 1 = pull items
+    int32_t item_begin, item_end;
+    int32_t fin_begin, fin_end;
+    int32_t n_normslots;
+    int32_t pad0, pad1;
+};
+
+struct VarInfo {
+    int32_t off;  // prefix sum of dims
+    int32_t dim;
+};
+
+// Kernel parameter block (device pointers)
+struct DevPlan {
+    const double *pot;
+    const uint16_t *lam16;
+    const int32_t *idx32;
+    const CollectOp *cops;
+    const PullOp *pops;
+    const Item *items;
+    const FinItem *fins;
+    const Phase *phases;
+    const VarInfo *vars;
+    int32_t n_phases;
+    int32_t n_vars, sum_dims, query_var;
+    int32_t tile_rows;   // rows per tile
+    int32_t mg_row0;
+    int32_t max_normslots, max_pslots;
+    int32_t team;        // warps per tile
+};
+
+// --- host-side plan ----------------------------------------------------------------------------------------------
+struct HostPlan {
+    std::vector<double> pot;
+    std::vector<uint16_t> lam16;
+    std::vector<int32_t> idx32;
+    std::vector<CollectOp> cops;
+    std::vector<PullOp> pops;
+    std::vector<Item> items;
+    std::vector<FinItem> fins;
+    std::vector<Phase> phases;
+    std::vector<VarInfo> vars;
+    int32_t n_vars = 0, n_cliques = 0, n_seps = 0, sum_dims = 0, query_var = 0;
+    int32_t n_levels = 0;
+    int32_t tile_rows = 0, cl_row0 = 0, mup_row0 = 0, dn_row0 = 0, inv_row0 = 0, mg_row0 = 0;
+    int32_t max_normslots = 0, max_pslots = 0;
+    int32_t team = 1;
+    int64_t clique_entries = 0, sep_entries = 0, parent_entries = 0, marginal_entries = 0;
+    // per-variable marginal source, for tests: table index (clique c, or n_cliques + s)
+    std::vector<int32_t> marg_source;
+    double alg_bytes_per_case = 0, kernel_bytes_per_case = 0;
+};
+
+}  // namespace fbn
+
+struct fbn_tree_desc;
+namespace fbn {
+// Validates the tree and builds the host plan for `team` warps per tile. Returns empty string on success.
+std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &out);
+}

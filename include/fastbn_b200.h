@@ -1,0 +1,129 @@
+/*
+ * fastbn_b200 — C ABI of the B200-native junction-tree inference hot path.
+ *
+ * The reference (Tonanguyxiro/FastBN) has no FFI layer: its boundary for this path is the C++ class API
+ *   JunctionTree(Network*, Dataset*, bool)            include/JunctionTree.h:40
+ *   virtual double EvaluateAccuracy(string, int)      include/Inference.h:44, src/JunctionTree.cpp:57-129
+ * and everything below replaces what happens INSIDE JunctionTree::PredictUseJTInfer (src/JunctionTree.cpp:1473-1534)
+ * for a whole batch of test cases at once. A maintainer of the reference binds these entry points from
+ * JunctionTree.cpp; our own host-side mirror (fastbn_b200/host/) does exactly that.
+ *
+ * Plain C types only; every pointer is caller-owned; nothing is retained after a call returns except the plan.
+ * All functions return 0 on success, non-zero on error; fbn_last_error() gives the message (thread-local).
+ * There is no CPU fallback: fbn_plan_create fails with FBN_ERR_NO_DEVICE when no sm_100 device is usable.
+ */
+#ifndef FASTBN_B200_H
+#define FASTBN_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FBN_OK 0
+#define FBN_ERR_INVALID 1   /* malformed tree / arguments */
+#define FBN_ERR_NO_DEVICE 2 /* no CUDA device (the product path never falls back to the CPU) */
+#define FBN_ERR_CUDA 3      /* a CUDA runtime call failed */
+#define FBN_ERR_NOMEM 4
+
+/*
+ * Flat, immutable description of a calibrated-to-be junction tree, i.e. of the reference's
+ * JunctionTreeStructure + JunctionTree state right after the JunctionTree ctor (src/JunctionTree.cpp:3-46):
+ *  - tables [0, n_cliques) are tree->vector_clique_ptr_container[i]->p_table, tables
+ *    [n_cliques, n_cliques+n_separators) are tree->vector_separator_ptr_container[i]->p_table;
+ *  - table_vars is PotentialTableBase::vec_related_variables in STORAGE order (first = most significant digit,
+ *    src/PotentialTableBase.cpp:599-607) — for a non-root clique the variables of its upstream separator are the
+ *    trailing ones, in separator order (JunctionTree::ReorganizeTableStorage, src/JunctionTree.cpp:235-281);
+ *  - clique_potentials are PotentialTableBase::potentials of every clique, concatenated in clique order
+ *    (separator tables are all-ones in the reference and are not passed);
+ *  - sep_parent / sep_child are Separator::ptr_upstream_clique / ptr_downstream_cliques[0] as clique indices;
+ *  - root is jt_root; query_var is Inference::query_index.
+ */
+typedef struct fbn_tree_desc {
+    int32_t n_vars;
+    const int32_t *var_dims;          /* [n_vars] DiscreteNode::GetDomainSize */
+    int32_t n_cliques;
+    int32_t n_separators;             /* == n_cliques - 1 for a tree, fewer for a forest is NOT supported */
+    const int32_t *table_nvars;       /* [n_cliques + n_separators] */
+    const int32_t *table_vars;        /* concatenated, sum(table_nvars) entries */
+    const double *clique_potentials;  /* concatenated, sum over cliques of prod(dims) entries */
+    const int32_t *sep_parent;        /* [n_separators] */
+    const int32_t *sep_child;         /* [n_separators] */
+    int32_t root;
+    int32_t query_var;
+} fbn_tree_desc;
+
+typedef struct fbn_plan fbn_plan; /* opaque: device-resident flattened tree + schedule */
+
+typedef struct fbn_plan_options {
+    int32_t device;        /* CUDA device ordinal; -1 = current device */
+    int32_t team_warps;    /* warps cooperating on one 32-case tile; 0 = choose from the tree size */
+    int32_t max_resident;  /* cap on resident tiles (scratch = max_resident x tile bytes); 0 = choose */
+    int32_t reserved[5];
+} fbn_plan_options;
+
+typedef struct fbn_plan_info {
+    int32_t n_vars, n_cliques, n_separators, sum_dims;
+    int32_t n_levels;            /* == reference max_level (cliques and separators alternate) */
+    int32_t team_warps;          /* chosen threads-per-tile / 32 */
+    int32_t resident_tiles;      /* tiles in flight (grid size) */
+    int32_t n_phases;
+    int64_t clique_entries;      /* sum |clique| */
+    int64_t separator_entries;   /* sum |separator| */
+    int64_t parent_entries;      /* sum over edges of |parent clique| */
+    int64_t marginal_entries;    /* sum over vars of |table the marginal is read from| */
+    int64_t scratch_bytes;       /* device scratch for all resident tiles */
+    int64_t plan_bytes;          /* device bytes of per-tree constants */
+    double alg_bytes_per_case;   /* SURVEY.md 8(d) algorithmic bytes per case (fixed-shape fp64 tables), evidence excluded */
+    double kernel_bytes_per_case;/* bytes the fused kernel itself moves per case (scratch r/w + output) */
+} fbn_plan_info;
+
+typedef struct fbn_stats {
+    double kernel_ms;      /* device time of the inference kernel(s), CUDA events on the launching stream */
+    double total_ms;       /* fbn_run only: wall time of the whole call incl. copies */
+    int64_t n_launches;    /* kernels launched by this call */
+    int64_t h2d_bytes, d2h_bytes;
+} fbn_stats;
+
+const char *fbn_last_error(void);
+int fbn_device_count(void);
+
+/* Build the device plan once per tree (replaces BackUpJunctionTree + the per-level "pre" phases,
+ * src/JunctionTree.cpp:289-300, :586-639, :834-880). opt may be NULL. */
+int fbn_plan_create(const fbn_tree_desc *tree, const fbn_plan_options *opt, fbn_plan **out);
+void fbn_plan_destroy(fbn_plan *plan);
+int fbn_plan_get_info(const fbn_plan *plan, fbn_plan_info *info);
+
+/*
+ * Run n_cases test cases (replaces the loop of src/JunctionTree.cpp:1517-1528 and everything it calls).
+ * Evidence is CSR: case i observes (ev_vars[k], ev_vals[k]) for k in [ev_offsets[i], ev_offsets[i+1]).
+ * Pairs with var >= n_vars or var < 0 are ignored (src/JunctionTree.cpp:326-331).
+ * labels_out[i]      = Inference::ArgMax of the query variable's posterior (src/Inference.cpp:92-102), -1 if none > 0
+ * posteriors_out     = n_cases x sum_dims doubles, row i = probs_one_sample of case i flattened in variable order,
+ *                      zeros for evidence variables (src/JunctionTree.cpp:1392-1406). May be NULL (labels only).
+ * HOST buffers (pageable or pinned); copies are chunked and overlapped with compute. stats may be NULL.
+ */
+int fbn_run(fbn_plan *plan, int64_t n_cases, const int64_t *ev_offsets, const int32_t *ev_vars,
+            const int32_t *ev_vals, int32_t *labels_out, double *posteriors_out, fbn_stats *stats);
+
+/* Same, but every buffer is DEVICE memory on the plan's device and the work is enqueued on `stream`
+ * (a cudaStream_t, NULL = default stream); returns after enqueueing unless stats != NULL (then it synchronises
+ * to fill kernel_ms). */
+int fbn_run_device(fbn_plan *plan, int64_t n_cases, const int64_t *ev_offsets, const int32_t *ev_vars,
+                   const int32_t *ev_vals, int32_t *labels_out, double *posteriors_out, void *stream,
+                   fbn_stats *stats);
+
+/*
+ * On-device scoring against golden posteriors (replaces Inference::CalculateMSE / CalculateHellingerDistance /
+ * Accuracy, src/Inference.cpp:46-61,153-206). golden is n_cases x sum_dims with golden[i][off_v] <= 0 meaning
+ * "skip node v" (src/Inference.cpp:160). out4 = {n_correct, n_total, sum_mse, sum_hd} as doubles, host memory.
+ * All array arguments are device pointers.
+ */
+int fbn_score_device(fbn_plan *plan, int64_t n_cases, const double *posteriors, const int32_t *labels,
+                     const double *golden, const int32_t *truths, double *out4_host, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FASTBN_B200_H */

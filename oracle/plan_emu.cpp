@@ -1,0 +1,109 @@
+// TEST INFRASTRUCTURE ONLY — scalar CPU interpreter of the device plan (fastbn_b200/csrc/plan.h) so that the
+// planner's index maps, phases, split columns and finalisers can be unit-tested in the no-GPU container
+// (`pytest -m "not gpu"`). It mirrors jt_fused_kernel one lane at a time. Never shipped, never timed, never
+// reachable from fastbn_b200/: built into oracle/_build/libplan_emu.so by tests only.
+#include <cstdint>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../fastbn_b200/csrc/plan.h"
+#include "../include/fastbn_b200.h"
+
+using namespace fbn;
+
+static std::string g_err;
+
+extern "C" const char *emu_last_error() { return g_err.c_str(); }
+
+extern "C" int emu_run(const fbn_tree_desc *tree, int team, int64_t n_cases, const int64_t *ev_off, const int32_t *ev_vars,
+                       const int32_t *ev_vals, int32_t *labels, double *post, int64_t *info /* 8 */) {
+    HostPlan P;
+    g_err = build_plan(*tree, team, P);
+    if (!g_err.empty()) return 1;
+    if (info) {
+        info[0] = (int64_t)P.phases.size(); info[1] = (int64_t)P.items.size(); info[2] = (int64_t)P.fins.size();
+        info[3] = P.max_pslots; info[4] = P.max_normslots; info[5] = P.tile_rows; info[6] = P.n_levels; info[7] = P.parent_entries;
+    }
+    std::vector<double> S((size_t)P.tile_rows);
+    std::vector<char> lam((size_t)P.sum_dims), obs((size_t)P.n_vars);
+    std::vector<double> normacc((size_t)std::max(1, P.max_normslots) * team), part((size_t)std::max(1, P.max_pslots));
+    for (int64_t cs = 0; cs < n_cases; ++cs) {
+        std::fill(S.begin(), S.end(), -12345.0);  // poison: reading a row before writing it shows up in the results
+        std::fill(lam.begin(), lam.end(), 1);
+        std::fill(obs.begin(), obs.end(), 0);
+        for (int64_t k = ev_off[cs]; k < ev_off[cs + 1]; ++k) {
+            int v = ev_vars[k], val = ev_vals[k];
+            if (v < 0 || v >= P.n_vars) continue;
+            obs[v] = 1;
+            for (int d = 0; d < P.vars[v].dim; ++d)
+                if (d != val) lam[P.vars[v].off + d] = 0;
+        }
+        for (const Phase &ph : P.phases) {
+            if (ph.kind == 0) std::fill(normacc.begin(), normacc.end(), 0.0);
+            for (int it = ph.item_begin; it < ph.item_end; ++it) {
+                const Item &I = P.items[it];
+                const int warp = (it - ph.item_begin) % team;
+                if (ph.kind == 0) {
+                    const CollectOp &op = P.cops[I.op];
+                    const int j = I.col;
+                    bool cm = true;
+                    for (int i = 0; i < op.ncolv; ++i) cm = cm && lam[P.lam16[op.collam_off + (int64_t)j * op.ncolv + i]];
+                    double scale = 1.0;
+                    for (int k = 0; k < op.nchild; ++k) scale *= S[P.idx32[op.invrow_off + k]];
+                    double acc = 0.0;
+                    for (int r = I.r0; r < I.r1; ++r) {
+                        bool m = cm;
+                        for (int i = 0; i < op.nrest; ++i) m = m && lam[P.lam16[op.rowlam_off + (int64_t)r * op.nrest + i]];
+                        const int64_t e = (int64_t)r * op.cols + j;
+                        double v = P.pot[op.pot_off + e] * scale;
+                        for (int k = 0; k < op.nchild; ++k)
+                            v *= S[P.idx32[op.rowpart_off + (int64_t)r * op.nchild + k] + P.idx32[op.colpart_off + (int64_t)j * op.nchild + k]];
+                        if (!m) v = 0.0;
+                        S[op.cl_row + e] = v;
+                        acc += v;
+                    }
+                    if (I.pslot < 0) S[op.mup_row + j] = acc;
+                    else part[I.pslot] = acc;
+                    normacc[op.normslot * team + warp] += acc;
+                } else {
+                    const PullOp &op = P.pops[I.op];
+                    const int q = I.col;
+                    const int32_t bx = P.idx32[op.tbase_off + 2 * q], by = P.idx32[op.tbase_off + 2 * q + 1];
+                    double acc = 0.0;
+                    for (int r = I.r0; r < I.r1; ++r)
+                        acc += S[op.src_row + bx + P.idx32[op.trest_off + 2 * r]] * S[op.fac_row + by + P.idx32[op.trest_off + 2 * r + 1]];
+                    if (I.pslot >= 0) part[I.pslot] = acc;
+                    else if (op.kind == 1) { double m = S[op.mup_row + q]; S[op.dst_row + q] = m == 0.0 ? 0.0 : acc / m; }
+                    else S[op.dst_row + q] = acc;
+                }
+            }
+            for (int f = ph.fin_begin; f < ph.fin_end; ++f) {
+                const FinItem &F = P.fins[f];
+                double s = 0.0;
+                if (F.type == FIN_NORM) {
+                    for (int w = 0; w < team; ++w) s += normacc[F.slot0 * team + w];
+                    S[F.dst_row] = 1.0 / s;
+                    continue;
+                }
+                for (int i = 0; i < F.nslots; ++i) s += part[F.slot0 + i];
+                if (F.type == FIN_D) { double m = S[F.aux_row]; s = m == 0.0 ? 0.0 : s / m; }
+                S[F.dst_row] = s;
+            }
+        }
+        for (int v = 0; v < P.n_vars; ++v) {
+            const VarInfo vi = P.vars[v];
+            double sum = 0.0;
+            for (int d = 0; d < vi.dim; ++d) sum += S[P.mg_row0 + vi.off + d];
+            double best = 0.0;
+            int arg = -1;
+            for (int d = 0; d < vi.dim; ++d) {
+                double pr = obs[v] ? 0.0 : S[P.mg_row0 + vi.off + d] / sum;
+                if (post) post[cs * P.sum_dims + vi.off + d] = pr;
+                if (pr > best) { best = pr; arg = d; }
+            }
+            if (v == P.query_var && labels) labels[cs] = arg;
+        }
+    }
+    return 0;
+}

@@ -1,0 +1,138 @@
+"""GPU parity tests (run on the B200 with -m gpu): the CUDA path, called through the C ABI, against the committed
+reference fp64 fixtures and against the CPU oracle on fresh seeded cases. Tolerance from BASELINE.json's north_star:
+posteriors max-abs <= 1e-9 in fp64, labels bit-identical."""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, load_golden
+from fastbn_b200 import capi, synth
+from oracle import jtoracle
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-9
+
+
+@pytest.fixture(scope="module")
+def plan(alarm_tree):
+    p = capi.Plan(alarm_tree, device=0)
+    yield p
+    p.close()
+
+
+@pytest.mark.parametrize("name", ["alarm_1k_ref", "alarm_synth_4k_ref", "alarm_edge_ref"])
+def test_matches_reference_fixtures(plan, name):
+    g = load_golden(name)
+    labels, post, st = plan.run(g["ev_off"], g["ev_vars"], g["ev_vals"])
+    assert np.array_equal(np.isnan(post), np.isnan(g["post"]))
+    assert np.nanmax(np.abs(post - g["post"])) <= TOL
+    assert np.array_equal(labels, g["labels"])
+    assert st.n_launches >= 1
+
+
+@pytest.mark.parametrize("team", [1, 2, 4, 8, 16, 32])
+def test_every_team_size(alarm_tree, team):
+    g = load_golden("alarm_1k_ref")
+    p = capi.Plan(alarm_tree, device=0, team_warps=team, max_resident=37)
+    labels, post, _ = p.run(g["ev_off"], g["ev_vars"], g["ev_vals"])
+    p.close()
+    assert np.nanmax(np.abs(post - g["post"])) <= TOL
+    assert np.array_equal(labels, g["labels"])
+
+
+def test_fresh_cases_vs_oracle_ragged(plan, alarm_tree):
+    """ragged evidence (0..20 pairs per case), unsorted, with ignored out-of-range variables; not a multiple of 32"""
+    rng = np.random.default_rng(5)
+    dims = alarm_tree["var_dims"]
+    n = 3001
+    vl, wl = [], []
+    for i in range(n):
+        k = int(rng.integers(0, 21))
+        v = rng.permutation(np.arange(1, 37))[:k].astype(np.int32)
+        w = (rng.integers(0, 1 << 30, k) % dims[v]).astype(np.int32)
+        if i % 97 == 0:
+            v = np.concatenate([v, [37, 1000, -3]]).astype(np.int32)
+            w = np.concatenate([w, [0, 1, 0]]).astype(np.int32)
+        vl.append(v)
+        wl.append(w)
+    off = np.concatenate([[0], np.cumsum([len(v) for v in vl])]).astype(np.int64)
+    ev = np.concatenate(vl)
+    ew = np.concatenate(wl)
+    labels, post, _ = plan.run(off, ev, ew)
+    o = jtoracle.Oracle(alarm_tree)
+    opost, olab = o.run_batch(off, ev, ew)
+    o.close()
+    assert np.max(np.abs(post - opost)) <= TOL
+    assert np.array_equal(labels, olab)
+
+
+def test_empty_batch_and_labels_only(plan):
+    z = np.zeros(1, np.int64)
+    e = np.zeros(0, np.int32)
+    labels, post, _ = plan.run(z, e, e)
+    assert labels.shape == (0,)
+    g = load_golden("alarm_1k_ref")
+    labels, post, _ = plan.run(g["ev_off"], g["ev_vars"], g["ev_vals"], want_post=False)
+    assert post is None and np.array_equal(labels, g["labels"])
+
+
+def test_impossible_evidence_gives_nan_like_reference(plan, alarm_tree):
+    """value >= dim wipes every table: the reference's Normalize divides 0/0 -> NaN (no zero guard)."""
+    off = np.array([0, 1], np.int64)
+    labels, post, _ = plan.run(off, np.array([5], np.int32), np.array([9], np.int32))
+    d = alarm_tree["var_dims"]
+    o5 = int(np.sum(d[:5]))
+    assert np.all(post[0, o5:o5 + d[5]] == 0)  # the evidence variable itself is reported as zeros
+    assert np.all(np.isnan(np.delete(post[0], np.arange(o5, o5 + d[5]))))
+    assert labels[0] == -1
+
+
+def test_device_resident_path_and_scoring(plan, alarm_tree):
+    import torch
+    g = load_golden("alarm_1k_ref")
+    dev = torch.device("cuda:0")
+    off = torch.from_numpy(g["ev_off"]).to(dev)
+    ev = torch.from_numpy(g["ev_vars"]).to(dev)
+    ew = torch.from_numpy(g["ev_vals"]).to(dev)
+    n = 1000
+    labels = torch.empty(n, dtype=torch.int32, device=dev)
+    post = torch.empty((n, 105), dtype=torch.float64, device=dev)
+    torch.cuda.synchronize()
+    st = plan.run_device(n, off.data_ptr(), ev.data_ptr(), ew.data_ptr(), labels.data_ptr(), post.data_ptr())
+    torch.cuda.synchronize()
+    assert st.kernel_ms > 0
+    assert np.max(np.abs(post.cpu().numpy() - g["post"])) <= TOL
+    assert np.array_equal(labels.cpu().numpy(), g["labels"])
+    # on-device MSE / HD / accuracy against the shipped 7-decimal golden file (reference prints 6.50867e-17, 4.6999e-17, 1)
+    from test_oracle import read_pt
+    gold = torch.from_numpy(read_pt(os.path.join(GOLDEN, "alarm", "alarm_1k_pt"), alarm_tree["var_dims"])).to(dev)
+    truths = torch.from_numpy(g["truths"]).to(dev)
+    sc = plan.score_device(n, post.data_ptr(), labels.data_ptr(), gold.data_ptr(), truths.data_ptr())
+    assert sc["n_correct"] == 1000 and sc["n_total"] == 1000
+    assert abs(sc["sum_mse"] / n - 6.50867e-17) < 1e-19
+    assert abs(sc["sum_hd"] / n - 4.6999e-17) < 1e-19
+
+
+def test_large_batch_properties(plan, alarm_tree):
+    """200k synthetic cases (several waves of tiles): rows sum to 1 per non-evidence variable, evidence rows are 0,
+    permuting the cases permutes the results, and the first 2000 match the oracle."""
+    n = 200_000
+    off, ev, ew = synth.uniform_evidence(alarm_tree["var_dims"], n, 7, seed=20260101)
+    labels, post, _ = plan.run(off, ev, ew)
+    d = alarm_tree["var_dims"]
+    voff = np.concatenate([[0], np.cumsum(d)])
+    sums = np.add.reduceat(post, voff[:-1], axis=1)
+    is_ev = np.zeros((n, len(d)), bool)
+    is_ev[np.repeat(np.arange(n), 7), ev] = True
+    assert np.all(np.abs(sums[~is_ev] - 1.0) < 1e-12)
+    assert np.all(sums[is_ev] == 0.0)
+    o = jtoracle.Oracle(alarm_tree)
+    opost, olab = o.run_batch(off[:2001], ev[:2000 * 7], ew[:2000 * 7])
+    o.close()
+    assert np.max(np.abs(post[:2000] - opost)) <= TOL and np.array_equal(labels[:2000], olab)
+    perm = np.random.default_rng(1).permutation(n)
+    ev2 = ev.reshape(n, 7)[perm].reshape(-1)
+    ew2 = ew.reshape(n, 7)[perm].reshape(-1)
+    labels2, post2, _ = plan.run(off, ev2, ew2)
+    assert np.array_equal(post2, post[perm]) and np.array_equal(labels2, labels[perm])

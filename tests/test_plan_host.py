@@ -1,0 +1,66 @@
+"""CPU tests of the host side: the planner (fastbn_b200/csrc/plan.cpp) interpreted by oracle/plan_emu.cpp must
+reproduce the reference's posteriors for every team size, and must reject malformed trees; the C-ABI library must
+load and export every symbol include/fastbn_b200.h declares (no compute without a GPU)."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+import emu
+from conftest import ROOT, load_golden
+from fastbn_b200 import capi
+
+
+@pytest.mark.parametrize("team", [1, 2, 8, 32])
+@pytest.mark.parametrize("name", ["alarm_1k_ref", "alarm_edge_ref"])
+def test_plan_reproduces_reference(alarm_tree, team, name):
+    g = load_golden(name)
+    post, lab, info = emu.run(alarm_tree, team, g["ev_off"], g["ev_vars"], g["ev_vals"])
+    assert np.array_equal(np.isnan(post), np.isnan(g["post"]))
+    assert np.nanmax(np.abs(post - g["post"])) <= 1e-9
+    assert np.array_equal(lab, g["labels"])
+    assert info[6] == 15  # reference prints "maximum level of the junction tree = 15"
+    assert info[7] == 1517  # sum over edges of |parent clique|
+
+
+def test_planner_rejects_malformed_trees(alarm_tree):
+    z = np.zeros(1, np.int64)
+    e = np.zeros(0, np.int32)
+    t = dict(alarm_tree)
+    t["root"] = np.int32(3)  # a non-root clique as root: it has an upstream separator
+    with pytest.raises(ValueError):
+        emu.run(t, 1, z[:1].repeat(2), e, e)
+    t = dict(alarm_tree)
+    tv = t["table_vars"].copy()
+    tv[0], tv[1] = tv[1], tv[0]  # breaks "child ends with its separator's variables" or the scope check
+    t["table_vars"] = tv
+    with pytest.raises(ValueError):
+        emu.run(t, 1, z[:1].repeat(2), e, e)
+    t = dict(alarm_tree)
+    sp = t["sep_child"].copy()
+    sp[0] = sp[1]
+    t["sep_child"] = sp
+    with pytest.raises(ValueError):
+        emu.run(t, 1, z[:1].repeat(2), e, e)
+    with pytest.raises(ValueError):
+        emu.run(alarm_tree, 3, z[:1].repeat(2), e, e)  # team must be a power of two
+
+
+def test_abi_exports_every_declared_symbol():
+    hdr = open(os.path.join(ROOT, "include", "fastbn_b200.h")).read()
+    declared = set(re.findall(r"\b(fbn_[a-z_]+)\s*\(", hdr))
+    assert declared == set(capi.ABI_SYMBOLS)
+    L = capi.load_library()
+    for s in declared:
+        assert hasattr(L, s), s
+
+
+def test_no_cpu_fallback_without_device(alarm_tree):
+    L = capi.load_library()
+    if L.fbn_device_count() > 0:
+        pytest.skip("a CUDA device is present")
+    with pytest.raises(capi.FastBNError) as ei:
+        capi.Plan(alarm_tree)
+    assert "no CUDA device" in str(ei.value)
