@@ -139,12 +139,12 @@ extern "C" int fbn_plan_create(const fbn_tree_desc *tree, const fbn_plan_options
     fbn::DevPlan &d = p->dp;
     int rc;
 #define UP(field) if ((rc = upload(p, h.field, &d.field)) != FBN_OK) { fbn_plan_destroy(p); return rc; }
-    UP(pot) UP(lam16) UP(idx32) UP(cops) UP(pops) UP(items) UP(fins) UP(phases) UP(vars)
+    UP(pot) UP(lam16) UP(idx32) UP(cops) UP(pops) UP(oplist) UP(fins) UP(phases) UP(vars)
 #undef UP
     d.n_phases = (int32_t)h.phases.size();
     d.n_vars = h.n_vars; d.sum_dims = h.sum_dims; d.query_var = h.query_var;
     d.tile_rows = h.tile_rows; d.mg_row0 = h.mg_row0;
-    d.max_normslots = h.max_normslots; d.max_pslots = h.max_pslots; d.team = h.team;
+    d.max_normslots = h.max_normslots; d.max_pslots = h.max_pslots; d.max_mask_words = h.max_mask_words; d.team = h.team;
 
     cudaDeviceProp prop;
     CK(cudaGetDeviceProperties(&prop, dev));

@@ -15,69 +15,125 @@ __device__ __forceinline__ double *row_ptr(double *S, int32_t row) { return S + 
 struct Smem {
     uint32_t *lam;    // [sum_dims]  bit l set <=> state allowed for case l of the tile
     uint32_t *obs;    // [n_vars]    bit l set <=> variable observed in case l
+    uint32_t *mask;   // [max_mask_words] per-phase evidence mask tables: one word per clique row / column
     double *normacc;  // [max_normslots][TEAM][32]
     double *part;     // [max_pslots][32]
 };
 
-// COLLECT item: column `col` of clique op, rows [r0,r1).
-//   C[e] = pristine[e] * mask(e) * prod_k ( child message_k[map_k(e)] / norm_k ),  mup[col] = sum_r C[r,col]
-template <int TEAM>
-__device__ __forceinline__ void collect_item(const DevPlan &P, const Item &I, double *S, const Smem &sm, int lane, int warp) {
-    const CollectOp *__restrict__ op = P.cops + I.op;
-    const int nrest = op->nrest, ncolv = op->ncolv, nchild = op->nchild, cols = op->cols, j = I.col;
-    const uint16_t *__restrict__ cl16 = P.lam16 + op->collam_off + (int64_t)j * ncolv;
-    uint32_t cm = 0xffffffffu;
-    for (int i = 0; i < ncolv; ++i) cm &= sm.lam[__ldg(cl16 + i)];
-    double scale = 1.0;
-    const int32_t *__restrict__ invrows = P.idx32 + op->invrow_off;
-    for (int k = 0; k < nchild; ++k) scale *= *row_ptr(S, __ldg(invrows + k));
-    const int32_t *__restrict__ cpart = P.idx32 + op->colpart_off + (int64_t)j * nchild;
-    const int32_t *__restrict__ rpart = P.idx32 + op->rowpart_off;
-    const uint16_t *__restrict__ rl16 = P.lam16 + op->rowlam_off;
-    const double *__restrict__ pot = P.pot + op->pot_off;
-    double *cl = row_ptr(S, op->cl_row);
+// Inner loop of COLLECT for one column and a row range, NC = number of children (compile-time for 0..3).
+//   C[e] = pristine[e] * mask(e) * prod_k ( child message_k[map_k(e)] / norm_k ),  returns sum_r C[r,col]
+template <int NC, bool TABLES>
+__device__ __forceinline__ double collect_rows(const DevPlan &P, const CollectOp &op, const Smem &sm, double *S, int lane, int j,
+                                               int r0, int r1, double scale) {
+    const int nchild = NC >= 0 ? NC : op.nchild, cols = op.cols;
+    uint32_t cm;
+    if (TABLES) {
+        cm = sm.mask[op.colmask_off + j];
+    } else {
+        const uint16_t *__restrict__ cl16 = P.lam16 + op.collam_off + (int64_t)j * op.ncolv;
+        cm = 0xffffffffu;
+        for (int i = 0; i < op.ncolv; ++i) cm &= sm.lam[__ldg(cl16 + i)];
+    }
+    const int32_t *__restrict__ cpart = P.idx32 + op.colpart_off + (int64_t)j * nchild;
+    int32_t cp[NC > 0 ? NC : 1];
+    if (NC > 0) {
+#pragma unroll
+        for (int k = 0; k < NC; ++k) cp[k] = __ldg(cpart + k);
+    }
+    const int32_t *__restrict__ rp = P.idx32 + op.rowpart_off + (int64_t)r0 * nchild;
+    const uint32_t *rowmask = sm.mask + op.rowmask_off;
+    const double *__restrict__ pot = P.pot + op.pot_off + j;
+    double *cl = row_ptr(S, op.cl_row + j);
     double acc = 0.0;
-    for (int r = I.r0; r < I.r1; ++r) {
+#pragma unroll 2
+    for (int r = r0; r < r1; ++r, rp += nchild) {
         uint32_t m = cm;
-        const uint16_t *rl = rl16 + (int64_t)r * nrest;
-        for (int i = 0; i < nrest; ++i) m &= sm.lam[__ldg(rl + i)];
-        const int64_t e = (int64_t)r * cols + j;
-        double v = 0.0;
-        if (m != 0u) {  // warp-uniform: skip the gathers when every case of the tile contradicts this entry
-            v = __ldg(pot + e) * scale;
-            const int32_t *rp = rpart + (int64_t)r * nchild;
-            for (int k = 0; k < nchild; ++k) v *= *row_ptr(S, __ldg(rp + k) + __ldg(cpart + k));
-            v = ((m >> lane) & 1u) ? v : 0.0;
+        if (TABLES) {
+            m &= rowmask[r];
+        } else {
+            const uint16_t *rl = P.lam16 + op.rowlam_off + (int64_t)r * op.nrest;
+            for (int i = 0; i < op.nrest; ++i) m &= sm.lam[__ldg(rl + i)];
         }
+        const int64_t e = (int64_t)r * cols;
+        double v = __ldg(pot + e) * scale;
+        if (NC > 0) {
+#pragma unroll
+            for (int k = 0; k < NC; ++k) v *= *row_ptr(S, __ldg(rp + k) + cp[k]);
+        } else if (NC < 0) {
+            for (int k = 0; k < nchild; ++k) v *= *row_ptr(S, __ldg(rp + k) + __ldg(cpart + k));
+        }
+        v = ((m >> lane) & 1u) ? v : 0.0;
         cl[e * kLanes] = v;
         acc += v;
     }
-    if (I.pslot < 0) *row_ptr(S, op->mup_row + j) = acc;
-    else sm.part[I.pslot * kLanes + lane] = acc;
-    sm.normacc[(op->normslot * TEAM + warp) * kLanes + lane] += acc;
+    return acc;
 }
 
-// PULL item: out = sum_r src[base + rest_r] * fac[basecol + restcol_r]
-__device__ __forceinline__ void pull_item(const DevPlan &P, const Item &I, double *S, const Smem &sm, int lane) {
-    const PullOp *__restrict__ op = P.pops + I.op;
-    const int q = I.col;
-    const int2 b = __ldg(reinterpret_cast<const int2 *>(P.idx32 + op->tbase_off) + q);
-    const double *src = row_ptr(S, op->src_row + b.x);
-    const double *fac = row_ptr(S, op->fac_row + b.y);
-    const int2 *__restrict__ tr = reinterpret_cast<const int2 *>(P.idx32 + op->trest_off);
-    double acc = 0.0;
-#pragma unroll 4
-    for (int r = I.r0; r < I.r1; ++r) {
-        const int2 t = __ldg(tr + r);
-        acc += src[(int64_t)t.x * kLanes] * fac[(int64_t)t.y * kLanes];
+// COLLECT op: all columns (and row chunks) of one clique that this warp owns.
+template <int TEAM>
+__device__ __forceinline__ void collect_op(const DevPlan &P, const CollectOp &__restrict__ op, double *S, const Smem &sm, int lane, int warp) {
+    double scale = 1.0;
+    const int32_t *__restrict__ invrows = P.idx32 + op.invrow_off;
+    for (int k = 0; k < op.nchild; ++k) scale *= *row_ptr(S, __ldg(invrows + k));
+    const int units = op.cols * op.chunks;
+    const bool tables = op.rowmask_off >= 0;
+    double nacc = 0.0;
+    for (int u = (warp - op.rot) & (TEAM - 1); u < units; u += TEAM) {
+        int j = u, r0 = 0, r1 = op.rows;
+        if (op.chunks > 1) {
+            j = u / op.chunks;
+            r0 = (u - j * op.chunks) * op.rows_per_chunk;
+            r1 = min(op.rows, r0 + op.rows_per_chunk);
+        }
+        double acc;
+        if (tables) {
+            switch (op.nchild) {
+                case 0: acc = collect_rows<0, true>(P, op, sm, S, lane, j, r0, r1, scale); break;
+                case 1: acc = collect_rows<1, true>(P, op, sm, S, lane, j, r0, r1, scale); break;
+                case 2: acc = collect_rows<2, true>(P, op, sm, S, lane, j, r0, r1, scale); break;
+                case 3: acc = collect_rows<3, true>(P, op, sm, S, lane, j, r0, r1, scale); break;
+                default: acc = collect_rows<-1, true>(P, op, sm, S, lane, j, r0, r1, scale); break;
+            }
+        } else {
+            acc = collect_rows<-1, false>(P, op, sm, S, lane, j, r0, r1, scale);
+        }
+        if (op.chunks > 1) sm.part[(op.pslot0 + u) * kLanes + lane] = acc;
+        else *row_ptr(S, op.mup_row + j) = acc;
+        nacc += acc;
     }
-    if (I.pslot >= 0) {
-        sm.part[I.pslot * kLanes + lane] = acc;
-    } else if (op->kind == 1) {
-        const double m = *row_ptr(S, op->mup_row + q);
-        *row_ptr(S, op->dst_row + q) = (m == 0.0) ? 0.0 : acc / m;  // TableDivision 0-guard, PotentialTable.cpp:718-734
-    } else {
-        *row_ptr(S, op->dst_row + q) = acc;
+    sm.normacc[(op.normslot * TEAM + warp) * kLanes + lane] = nacc;
+}
+
+// PULL op: out[q] = sum_r src[base_q + rest_r] * fac[basecol_q + restcol_r]
+template <int TEAM>
+__device__ __forceinline__ void pull_op(const DevPlan &P, const PullOp &__restrict__ op, double *S, const Smem &sm, int lane, int warp) {
+    const int units = op.nT * op.chunks;
+    const int2 *__restrict__ tb = reinterpret_cast<const int2 *>(P.idx32 + op.tbase_off);
+    const int2 *__restrict__ tr = reinterpret_cast<const int2 *>(P.idx32 + op.trest_off);
+    for (int u = (warp - op.rot) & (TEAM - 1); u < units; u += TEAM) {
+        int q = u, r0 = 0, r1 = op.nR;
+        if (op.chunks > 1) {
+            q = u / op.chunks;
+            r0 = (u - q * op.chunks) * op.rows_per_chunk;
+            r1 = min(op.nR, r0 + op.rows_per_chunk);
+        }
+        const int2 b = __ldg(tb + q);
+        const double *src = row_ptr(S, op.src_row + b.x);
+        const double *fac = row_ptr(S, op.fac_row + b.y);
+        double acc = 0.0;
+#pragma unroll 4
+        for (int r = r0; r < r1; ++r) {
+            const int2 t = __ldg(tr + r);
+            acc += src[(int64_t)t.x * kLanes] * fac[(int64_t)t.y * kLanes];
+        }
+        if (op.chunks > 1) {
+            sm.part[(op.pslot0 + u) * kLanes + lane] = acc;
+        } else if (op.kind == 1) {
+            const double m = *row_ptr(S, op.mup_row + q);
+            *row_ptr(S, op.dst_row + q) = (m == 0.0) ? 0.0 : acc / m;  // TableDivision 0-guard, PotentialTable.cpp:718-734
+        } else {
+            *row_ptr(S, op.dst_row + q) = acc;
+        }
     }
 }
 
@@ -98,7 +154,7 @@ __device__ __forceinline__ void fin_item(const FinItem &F, double *S, const Smem
 }
 
 template <int TEAM>
-__global__ void __launch_bounds__(TEAM * 32) jt_fused_kernel(const DevPlan P, double *__restrict__ scratch, int64_t n_cases,
+__global__ void __launch_bounds__(TEAM * 32, 32 / TEAM) jt_fused_kernel(const DevPlan P, double *__restrict__ scratch, int64_t n_cases,
                                                             const int64_t *__restrict__ ev_off, int64_t ev_base,
                                                             const int32_t *__restrict__ ev_vars,
                                                             const int32_t *__restrict__ ev_vals, int32_t *__restrict__ labels,
@@ -108,6 +164,8 @@ __global__ void __launch_bounds__(TEAM * 32) jt_fused_kernel(const DevPlan P, do
     sm.lam = reinterpret_cast<uint32_t *>(smem_raw);
     sm.obs = sm.lam + P.sum_dims;
     size_t o = ((size_t)(P.sum_dims + P.n_vars) * 4 + 15) & ~(size_t)15;
+    sm.mask = reinterpret_cast<uint32_t *>(smem_raw + o);
+    o += ((size_t)P.max_mask_words * 4 + 15) & ~(size_t)15;
     sm.normacc = reinterpret_cast<double *>(smem_raw + o);
     sm.part = sm.normacc + (size_t)P.max_normslots * TEAM * kLanes;
 
@@ -116,7 +174,7 @@ __global__ void __launch_bounds__(TEAM * 32) jt_fused_kernel(const DevPlan P, do
 
     for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         // ---- evidence -> lambda bit words (LoadDiscreteEvidence, src/JunctionTree.cpp:316-383, mask form :386-457)
-        if (TEAM > 1) __syncthreads();
+        if (TEAM > 1) __syncthreads(); else __syncwarp();  // previous tile's readers of lam/obs are done (lanes may diverge)
         for (int i = threadIdx.x; i < P.sum_dims + P.n_vars; i += TEAM * 32) sm.lam[i] = i < P.sum_dims ? 0xffffffffu : 0u;
         if (TEAM > 1) __syncthreads(); else __syncwarp();
         const int64_t cs = tile * kLanes + lane;
@@ -137,22 +195,38 @@ __global__ void __launch_bounds__(TEAM * 32) jt_fused_kernel(const DevPlan P, do
         for (int ph = 0; ph < P.n_phases; ++ph) {
             const Phase p = P.phases[ph];
             if (p.kind == 0) {
-                for (int s = 0; s < p.n_normslots; ++s) sm.normacc[(s * TEAM + warp) * kLanes + lane] = 0.0;
-                for (int it = p.item_begin + warp; it < p.item_end; it += TEAM) {
-                    const Item I = P.items[it];
-                    collect_item<TEAM>(P, I, S, sm, lane, warp);
+                // evidence mask tables of every clique of this phase: lanes work on different rows (warp-uniform data)
+                for (int oi = p.op_begin; oi < p.op_end; ++oi) {
+                    const CollectOp *__restrict__ op = P.cops + P.oplist[oi];
+                    if (op->rowmask_off < 0) continue;
+                    const int nrest = op->nrest, ncolv = op->ncolv, rows = op->rows, cols = op->cols;
+                    const uint16_t *__restrict__ rl16 = P.lam16 + op->rowlam_off;
+                    for (int r = threadIdx.x; r < rows; r += TEAM * 32) {
+                        uint32_t m = 0xffffffffu;
+                        for (int i = 0; i < nrest; ++i) m &= sm.lam[__ldg(rl16 + (int64_t)r * nrest + i)];
+                        sm.mask[op->rowmask_off + r] = m;
+                    }
+                    const uint16_t *__restrict__ cl16 = P.lam16 + op->collam_off;
+                    for (int j = threadIdx.x; j < cols; j += TEAM * 32) {
+                        uint32_t m = 0xffffffffu;
+                        for (int i = 0; i < ncolv; ++i) m &= sm.lam[__ldg(cl16 + (int64_t)j * ncolv + i)];
+                        sm.mask[op->colmask_off + j] = m;
+                    }
+                }
+                if (TEAM > 1) __syncthreads(); else __syncwarp();
+                for (int oi = p.op_begin; oi < p.op_end; ++oi) {
+                    collect_op<TEAM>(P, P.cops[P.oplist[oi]], S, sm, lane, warp);
                 }
             } else {
-                for (int it = p.item_begin + warp; it < p.item_end; it += TEAM) {
-                    const Item I = P.items[it];
-                    pull_item(P, I, S, sm, lane);
+                for (int oi = p.op_begin; oi < p.op_end; ++oi) {
+                    pull_op<TEAM>(P, P.pops[P.oplist[oi]], S, sm, lane, warp);
                 }
             }
             if (p.fin_end > p.fin_begin) {
                 if (TEAM > 1) __syncthreads();
                 for (int f = p.fin_begin + warp; f < p.fin_end; f += TEAM) fin_item<TEAM>(P.fins[f], S, sm, lane);
             }
-            if (TEAM > 1) __syncthreads();
+            if (TEAM > 1) __syncthreads(); else __syncwarp();  // the next phase overwrites the mask tables / partial slots
         }
 
         // ---- posteriors + label (GetProbabilitiesOneNode :1392-1454, Inference::ArgMax Inference.cpp:92-102)
@@ -240,6 +314,7 @@ __global__ void score_reduce_kernel(int64_t n_cases, const double *__restrict__ 
 // ---- launch helpers (called from capi.cu) ------------------------------------------------------------------------
 size_t fused_smem_bytes(const DevPlan &P) {
     size_t o = ((size_t)(P.sum_dims + P.n_vars) * 4 + 15) & ~(size_t)15;
+    o += ((size_t)P.max_mask_words * 4 + 15) & ~(size_t)15;
     return o + ((size_t)P.max_normslots * P.team + (size_t)P.max_pslots) * kLanes * sizeof(double);
 }
 

@@ -6,6 +6,7 @@
 
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <numeric>
 #include <string>
 
@@ -319,57 +320,72 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P) {
         P.marginal_entries += best_size;
     }
 
-    // ---- phases, warp work items, split-column partial slots ----
-    // A column (collect) / target entry (pull) is one item unless its row range is long and the phase has too few
-    // columns to keep `team` warps busy; then the rows are cut into chunks whose partial sums meet in shared memory.
+    // ---- phases, warp work units, split-column partial slots ----
+    // A column (collect) / target entry (pull) is one unit of warp work unless its row range is long and the phase has
+    // too few columns to keep `team` warps busy; then the rows are cut into chunks whose partial sums meet in shared
+    // memory. Evidence-mask tables (one 32-bit word per row and per column of every clique of the phase) are built in
+    // shared memory at the start of a collect phase when they fit.
     const int kMaxPslots = 192;
+    const int kMaxMaskWords = getenv("FBN_NO_TABLES") ? 0 : 6144;
     auto emit_phase = [&](int kind, const std::vector<int> &ops) {
         Phase ph = Phase();
         ph.kind = kind;
-        ph.item_begin = (int32_t)P.items.size();
+        ph.op_begin = (int32_t)P.oplist.size();
         ph.fin_begin = (int32_t)P.fins.size();
         int64_t work = 0;
         for (int o : ops) work += kind == 0 ? (int64_t)P.cops[o].rows * P.cops[o].cols : (int64_t)P.pops[o].nT * P.pops[o].nR;
         int64_t target = std::max<int64_t>(32, work / (4 * (int64_t)team));
-        int pslots = 0, normslots = 0;
-        for (int pass = 0; pass < 8; ++pass) {  // coarsen the split until the partial slots fit
-            pslots = 0;
+        auto chunks_of = [&](int64_t rows, int64_t tgt) {
+            if (team == 1) return (int64_t)1;
+            int64_t ch = std::min<int64_t>(rows, (rows + tgt - 1) / tgt);
+            int64_t per = (rows + ch - 1) / ch;
+            return (rows + per - 1) / per;
+        };
+        for (int pass = 0; pass < 12; ++pass) {  // coarsen the split until the partial slots fit
+            int64_t pslots = 0;
             for (int o : ops) {
                 int64_t rows = kind == 0 ? P.cops[o].rows : P.pops[o].nR, cols = kind == 0 ? P.cops[o].cols : P.pops[o].nT;
-                int64_t chunks = team == 1 ? 1 : (rows + target - 1) / target;
-                if (chunks > 1) pslots += (int)(chunks * cols);
+                int64_t ch = chunks_of(rows, target);
+                if (ch > 1) pslots += ch * cols;
             }
             if (pslots <= kMaxPslots) break;
             target *= 4;
         }
-        if (pslots > kMaxPslots) target = INT64_MAX / 4;
-        pslots = 0;
+        int pslots = 0, normslots = 0, mask_words = 0;
+        int64_t units = 0;
         for (int o : ops) {
             int64_t rows = kind == 0 ? P.cops[o].rows : P.pops[o].nR, cols = kind == 0 ? P.cops[o].cols : P.pops[o].nT;
-            int64_t chunks = team == 1 ? 1 : std::min<int64_t>(rows, (rows + target - 1) / target);
+            int64_t chunks = chunks_of(rows, target);
+            if (chunks > 1 && pslots + chunks * cols > kMaxPslots) chunks = 1;
             int64_t per = (rows + chunks - 1) / chunks;
-            chunks = (rows + per - 1) / per;
-            if (kind == 0) P.cops[o].normslot = normslots++;
-            for (int64_t j = 0; j < cols; ++j) {
-                if (chunks > 1) {
+            int32_t pslot0 = chunks > 1 ? pslots : -1;
+            if (chunks > 1) pslots += (int)(chunks * cols);
+            if (kind == 0) {
+                CollectOp &op = P.cops[o];
+                op.normslot = normslots++;
+                op.chunks = (int32_t)chunks; op.rows_per_chunk = (int32_t)per; op.pslot0 = pslot0; op.rot = (int32_t)(units % team);
+                if (mask_words + rows + cols <= kMaxMaskWords) {
+                    op.rowmask_off = mask_words; op.colmask_off = mask_words + (int32_t)rows;
+                    mask_words += (int32_t)(rows + cols);
+                } else {
+                    op.rowmask_off = op.colmask_off = -1;
+                }
+            } else {
+                PullOp &op = P.pops[o];
+                op.chunks = (int32_t)chunks; op.rows_per_chunk = (int32_t)per; op.pslot0 = pslot0; op.rot = (int32_t)(units % team);
+            }
+            units += chunks * cols;
+            P.oplist.push_back(o);
+            if (chunks > 1)
+                for (int64_t j = 0; j < cols; ++j) {
                     FinItem f = FinItem();
                     if (kind == 0) { f.type = FIN_MUP; f.dst_row = P.cops[o].mup_row + (int32_t)j; }
                     else if (P.pops[o].kind == 1) { f.type = FIN_D; f.dst_row = P.pops[o].dst_row + (int32_t)j; f.aux_row = P.pops[o].mup_row + (int32_t)j; }
                     else { f.type = FIN_MARG; f.dst_row = P.pops[o].dst_row + (int32_t)j; }
-                    f.slot0 = pslots;
+                    f.slot0 = pslot0 + (int32_t)(j * chunks);
                     f.nslots = (int32_t)chunks;
                     P.fins.push_back(f);
                 }
-                for (int64_t ch = 0; ch < chunks; ++ch) {
-                    Item it = Item();
-                    it.op = o;
-                    it.col = (int32_t)j;
-                    it.r0 = (int32_t)(ch * per);
-                    it.r1 = (int32_t)std::min<int64_t>(rows, (ch + 1) * per);
-                    it.pslot = chunks > 1 ? pslots++ : -1;
-                    P.items.push_back(it);
-                }
-            }
             if (kind == 0) {
                 FinItem f = FinItem();
                 f.type = FIN_NORM;
@@ -379,11 +395,14 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P) {
                 P.fins.push_back(f);
             }
         }
-        ph.item_end = (int32_t)P.items.size();
+        P.n_units += units;
+        ph.op_end = (int32_t)P.oplist.size();
         ph.fin_end = (int32_t)P.fins.size();
         ph.n_normslots = normslots;
+        ph.mask_words = mask_words;
         P.max_normslots = std::max(P.max_normslots, normslots);
         P.max_pslots = std::max(P.max_pslots, pslots);
+        P.max_mask_words = std::max(P.max_mask_words, mask_words);
         P.phases.push_back(ph);
     };
     for (int d = maxdepth; d >= 0; --d) {  // Collect: deepest cliques first (src/JunctionTree.cpp:1240-1306)

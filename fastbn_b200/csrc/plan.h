@@ -36,7 +36,13 @@ struct CollectOp {
     int32_t nrest, ncolv;
     int32_t nchild;
     int32_t normslot;     // index of this op among the collect ops of its phase
-    int32_t pad;
+    // work decomposition: unit u in [0, cols*chunks): col = u / chunks, rows [ (u%chunks)*rows_per_chunk, ...)
+    int32_t chunks, rows_per_chunk;
+    int32_t pslot0;       // chunks > 1: partial slot of (col, chunk) = pslot0 + col*chunks + chunk
+    int32_t rot;          // units of earlier ops in the phase, mod team: keeps the round-robin over warps going
+    int32_t rowmask_off;  // shared-memory word offsets of this op's per-tile evidence mask tables (rows / cols words),
+    int32_t colmask_off;  //   -1: tables do not fit, fall back to per-entry mask evaluation
+    int32_t pad0, pad1;
 };
 
 // PULL: out[q] = sum_r src[tbase[q].x + trest[r].x] * fac[tbase[q].y + trest[r].y]
@@ -52,14 +58,10 @@ struct PullOp {
     int32_t dst_row;
     int32_t nT, nR;
     int32_t kind;
+    int32_t chunks, rows_per_chunk, pslot0, rot;  // as in CollectOp (cols = nT, rows = nR)
     int32_t pad;
 };
 
-// One unit of warp work: column `col` of op `op`, rows [r0, r1). pslot >= 0: the row range of this column is split
-// over several items and this item's partial sum goes to shared partial slot pslot (combined by a FinItem).
-struct Item {
-    int32_t op, col, r0, r1, pslot, pad0, pad1, pad2;
-};
 
 enum FinType : int32_t { FIN_MUP = 0, FIN_NORM = 1, FIN_D = 2, FIN_MARG = 3 };
 struct FinItem {
@@ -72,11 +74,12 @@ struct FinItem {
 };
 
 struct Phase {
-    int32_t kind;  // 0 = collect items, 1 = pull items
-    int32_t item_begin, item_end;
+    int32_t kind;  // 0 = collect ops, 1 = pull ops
+    int32_t op_begin, op_end;  // into oplist[] (indices into cops[] / pops[])
     int32_t fin_begin, fin_end;
     int32_t n_normslots;
-    int32_t pad0, pad1;
+    int32_t mask_words;        // shared-memory words of evidence mask tables this phase builds
+    int32_t pad0;
 };
 
 struct VarInfo {
@@ -91,7 +94,7 @@ struct DevPlan {
     const int32_t *idx32;
     const CollectOp *cops;
     const PullOp *pops;
-    const Item *items;
+    const int32_t *oplist;
     const FinItem *fins;
     const Phase *phases;
     const VarInfo *vars;
@@ -99,7 +102,7 @@ struct DevPlan {
     int32_t n_vars, sum_dims, query_var;
     int32_t tile_rows;   // rows per tile
     int32_t mg_row0;
-    int32_t max_normslots, max_pslots;
+    int32_t max_normslots, max_pslots, max_mask_words;
     int32_t team;        // warps per tile
 };
 
@@ -110,15 +113,16 @@ struct HostPlan {
     std::vector<int32_t> idx32;
     std::vector<CollectOp> cops;
     std::vector<PullOp> pops;
-    std::vector<Item> items;
+    std::vector<int32_t> oplist;
     std::vector<FinItem> fins;
     std::vector<Phase> phases;
     std::vector<VarInfo> vars;
     int32_t n_vars = 0, n_cliques = 0, n_seps = 0, sum_dims = 0, query_var = 0;
     int32_t n_levels = 0;
     int32_t tile_rows = 0, cl_row0 = 0, mup_row0 = 0, dn_row0 = 0, inv_row0 = 0, mg_row0 = 0;
-    int32_t max_normslots = 0, max_pslots = 0;
+    int32_t max_normslots = 0, max_pslots = 0, max_mask_words = 0;
     int32_t team = 1;
+    int64_t n_units = 0;  // warp work units per tile (for tests / info)
     int64_t clique_entries = 0, sep_entries = 0, parent_entries = 0, marginal_entries = 0;
     // per-variable marginal source, for tests: table index (clique c, or n_cliques + s)
     std::vector<int32_t> marg_source;

@@ -22,7 +22,7 @@ extern "C" int emu_run(const fbn_tree_desc *tree, int team, int64_t n_cases, con
     g_err = build_plan(*tree, team, P);
     if (!g_err.empty()) return 1;
     if (info) {
-        info[0] = (int64_t)P.phases.size(); info[1] = (int64_t)P.items.size(); info[2] = (int64_t)P.fins.size();
+        info[0] = (int64_t)P.phases.size(); info[1] = P.n_units; info[2] = (int64_t)P.fins.size();
         info[3] = P.max_pslots; info[4] = P.max_normslots; info[5] = P.tile_rows; info[6] = P.n_levels; info[7] = P.parent_entries;
     }
     std::vector<double> S((size_t)P.tile_rows);
@@ -41,41 +41,46 @@ extern "C" int emu_run(const fbn_tree_desc *tree, int team, int64_t n_cases, con
         }
         for (const Phase &ph : P.phases) {
             if (ph.kind == 0) std::fill(normacc.begin(), normacc.end(), 0.0);
-            for (int it = ph.item_begin; it < ph.item_end; ++it) {
-                const Item &I = P.items[it];
-                const int warp = (it - ph.item_begin) % team;
-                if (ph.kind == 0) {
-                    const CollectOp &op = P.cops[I.op];
-                    const int j = I.col;
-                    bool cm = true;
-                    for (int i = 0; i < op.ncolv; ++i) cm = cm && lam[P.lam16[op.collam_off + (int64_t)j * op.ncolv + i]];
-                    double scale = 1.0;
-                    for (int k = 0; k < op.nchild; ++k) scale *= S[P.idx32[op.invrow_off + k]];
-                    double acc = 0.0;
-                    for (int r = I.r0; r < I.r1; ++r) {
-                        bool m = cm;
-                        for (int i = 0; i < op.nrest; ++i) m = m && lam[P.lam16[op.rowlam_off + (int64_t)r * op.nrest + i]];
-                        const int64_t e = (int64_t)r * op.cols + j;
-                        double v = P.pot[op.pot_off + e] * scale;
-                        for (int k = 0; k < op.nchild; ++k)
-                            v *= S[P.idx32[op.rowpart_off + (int64_t)r * op.nchild + k] + P.idx32[op.colpart_off + (int64_t)j * op.nchild + k]];
-                        if (!m) v = 0.0;
-                        S[op.cl_row + e] = v;
-                        acc += v;
+            for (int oi = ph.op_begin; oi < ph.op_end; ++oi) {
+                const int o = P.oplist[oi];
+                const int units = ph.kind == 0 ? P.cops[o].cols * P.cops[o].chunks : P.pops[o].nT * P.pops[o].chunks;
+                for (int u = 0; u < units; ++u) {
+                    if (ph.kind == 0) {
+                        const CollectOp &op = P.cops[o];
+                        const int warp = (op.rot + u) % team;
+                        int j = u, r0 = 0, r1 = op.rows;
+                        if (op.chunks > 1) { j = u / op.chunks; r0 = (u - j * op.chunks) * op.rows_per_chunk; r1 = std::min(op.rows, r0 + op.rows_per_chunk); }
+                        bool cm = true;
+                        for (int i = 0; i < op.ncolv; ++i) cm = cm && lam[P.lam16[op.collam_off + (int64_t)j * op.ncolv + i]];
+                        double scale = 1.0;
+                        for (int k = 0; k < op.nchild; ++k) scale *= S[P.idx32[op.invrow_off + k]];
+                        double acc = 0.0;
+                        for (int r = r0; r < r1; ++r) {
+                            bool m = cm;
+                            for (int i = 0; i < op.nrest; ++i) m = m && lam[P.lam16[op.rowlam_off + (int64_t)r * op.nrest + i]];
+                            const int64_t e = (int64_t)r * op.cols + j;
+                            double v = P.pot[op.pot_off + e] * scale;
+                            for (int k = 0; k < op.nchild; ++k)
+                                v *= S[P.idx32[op.rowpart_off + (int64_t)r * op.nchild + k] + P.idx32[op.colpart_off + (int64_t)j * op.nchild + k]];
+                            if (!m) v = 0.0;
+                            S[op.cl_row + e] = v;
+                            acc += v;
+                        }
+                        if (op.chunks > 1) part[op.pslot0 + u] = acc;
+                        else S[op.mup_row + j] = acc;
+                        normacc[op.normslot * team + warp] += acc;
+                    } else {
+                        const PullOp &op = P.pops[o];
+                        int q = u, r0 = 0, r1 = op.nR;
+                        if (op.chunks > 1) { q = u / op.chunks; r0 = (u - q * op.chunks) * op.rows_per_chunk; r1 = std::min(op.nR, r0 + op.rows_per_chunk); }
+                        const int32_t bx = P.idx32[op.tbase_off + 2 * q], by = P.idx32[op.tbase_off + 2 * q + 1];
+                        double acc = 0.0;
+                        for (int r = r0; r < r1; ++r)
+                            acc += S[op.src_row + bx + P.idx32[op.trest_off + 2 * r]] * S[op.fac_row + by + P.idx32[op.trest_off + 2 * r + 1]];
+                        if (op.chunks > 1) part[op.pslot0 + u] = acc;
+                        else if (op.kind == 1) { double m = S[op.mup_row + q]; S[op.dst_row + q] = m == 0.0 ? 0.0 : acc / m; }
+                        else S[op.dst_row + q] = acc;
                     }
-                    if (I.pslot < 0) S[op.mup_row + j] = acc;
-                    else part[I.pslot] = acc;
-                    normacc[op.normslot * team + warp] += acc;
-                } else {
-                    const PullOp &op = P.pops[I.op];
-                    const int q = I.col;
-                    const int32_t bx = P.idx32[op.tbase_off + 2 * q], by = P.idx32[op.tbase_off + 2 * q + 1];
-                    double acc = 0.0;
-                    for (int r = I.r0; r < I.r1; ++r)
-                        acc += S[op.src_row + bx + P.idx32[op.trest_off + 2 * r]] * S[op.fac_row + by + P.idx32[op.trest_off + 2 * r + 1]];
-                    if (I.pslot >= 0) part[I.pslot] = acc;
-                    else if (op.kind == 1) { double m = S[op.mup_row + q]; S[op.dst_row + q] = m == 0.0 ? 0.0 : acc / m; }
-                    else S[op.dst_row + q] = acc;
                 }
             }
             for (int f = ph.fin_begin; f < ph.fin_end; ++f) {
