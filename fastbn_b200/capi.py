@@ -10,7 +10,7 @@ LIB_PATH = os.path.join(_HERE, "libfastbn_b200.so")
 
 # every symbol include/fastbn_b200.h declares
 ABI_SYMBOLS = ["fbn_last_error", "fbn_device_count", "fbn_plan_create", "fbn_plan_destroy", "fbn_plan_get_info",
-               "fbn_run", "fbn_run_device", "fbn_score_device"]
+               "fbn_run", "fbn_run_device", "fbn_evaluate", "fbn_score_device"]
 
 
 class FastBNError(RuntimeError):
@@ -59,6 +59,7 @@ def load_library():
     L.fbn_plan_get_info.argtypes = [C.c_void_p, C.POINTER(PlanInfo)]
     L.fbn_run.argtypes = [C.c_void_p, C.c_int64] + [C.c_void_p] * 5 + [C.POINTER(Stats)]
     L.fbn_run_device.argtypes = [C.c_void_p, C.c_int64] + [C.c_void_p] * 6 + [C.POINTER(Stats)]
+    L.fbn_evaluate.argtypes = [C.c_void_p, C.c_int64] + [C.c_void_p] * 8 + [C.POINTER(Stats)]
     L.fbn_score_device.argtypes = [C.c_void_p, C.c_int64] + [C.c_void_p] * 6
     _lib = L
     return L
@@ -124,6 +125,22 @@ class Plan:
         st = Stats()
         _check(self.L, self.L.fbn_run(self.h, n, _ptr(ev_off), _ptr(ev_vars), _ptr(ev_vals), _ptr(labels), _ptr(post), C.byref(st)))
         return labels, post, st
+
+    def evaluate(self, ev_off, ev_vars, ev_vals, golden, truths, want_post=False):
+        """fbn_evaluate: inference + MSE/HD/accuracy vs golden posteriors. Returns (labels, posteriors|None, score dict, Stats)."""
+        ev_off = np.ascontiguousarray(ev_off, np.int64)
+        ev_vars = np.ascontiguousarray(ev_vars, np.int32)
+        ev_vals = np.ascontiguousarray(ev_vals, np.int32)
+        golden = np.ascontiguousarray(golden, np.float64)
+        truths = np.ascontiguousarray(truths, np.int32)
+        n = len(ev_off) - 1
+        labels = np.empty(n, np.int32)
+        post = np.empty((n, self.sum_dims), np.float64) if want_post else None
+        out = np.zeros(4, np.float64)
+        st = Stats()
+        _check(self.L, self.L.fbn_evaluate(self.h, n, _ptr(ev_off), _ptr(ev_vars), _ptr(ev_vals), _ptr(golden), _ptr(truths),
+                                           _ptr(labels), _ptr(post), _ptr(out), C.byref(st)))
+        return labels, post, dict(n_correct=int(out[0]), n_total=int(out[1]), sum_mse=float(out[2]), sum_hd=float(out[3])), st
 
     def run_device(self, n_cases, ev_off_ptr, ev_vars_ptr, ev_vals_ptr, labels_ptr, post_ptr, stream=0, timed=True):
         """Device pointers (ints, e.g. torch.Tensor.data_ptr())."""

@@ -16,8 +16,9 @@ size_t fused_smem_bytes(const DevPlan &P);
 cudaError_t fused_prepare(const DevPlan &P, int *blocks_per_sm);
 cudaError_t fused_launch(const DevPlan &P, int grid, double *scratch, int64_t n_cases, const int64_t *ev_off, int64_t ev_base,
                          const int32_t *ev_vars, const int32_t *ev_vals, int32_t *labels, double *post, cudaStream_t st);
-cudaError_t score_launch(int64_t n_cases, int n_vars, int sum_dims, const VarInfo *vars, const double *post, const double *golden,
-                         const int32_t *labels, const int32_t *truths, double *out_case, double *out4, cudaStream_t st);
+cudaError_t score_cases_launch(int64_t n_cases, int n_vars, int sum_dims, const VarInfo *vars, const double *post, const double *golden,
+                               const int32_t *labels, const int32_t *truths, double *out_case, cudaStream_t st);
+cudaError_t score_reduce_launch(int64_t n_cases, const double *out_case, double *out4, cudaStream_t st);
 }  // namespace fbn
 
 static thread_local std::string g_err;
@@ -38,6 +39,8 @@ struct ChunkBuf {                   // device + pinned staging for one in-flight
     int64_t *d_off = nullptr;
     int32_t *d_vars = nullptr, *d_vals = nullptr, *d_labels = nullptr;
     double *d_post = nullptr;
+    double *d_gold = nullptr, *h_gold = nullptr;   // fbn_evaluate only
+    int32_t *d_truth = nullptr, *h_truth = nullptr;
     int64_t *h_off = nullptr;       // pinned staging (rebased copies / pageable callers)
     int32_t *h_vars = nullptr, *h_vals = nullptr, *h_labels = nullptr;
     double *h_post = nullptr;
@@ -187,6 +190,7 @@ extern "C" int fbn_plan_create(const fbn_tree_desc *tree, const fbn_plan_options
 
 static void free_chunk(ChunkBuf &b) {
     cudaFree(b.d_off); cudaFree(b.d_vars); cudaFree(b.d_vals); cudaFree(b.d_labels); cudaFree(b.d_post);
+    cudaFree(b.d_gold); cudaFree(b.d_truth); cudaFreeHost(b.h_gold); cudaFreeHost(b.h_truth);
     cudaFreeHost(b.h_off); cudaFreeHost(b.h_vars); cudaFreeHost(b.h_vals); cudaFreeHost(b.h_labels); cudaFreeHost(b.h_post);
     if (b.in_done) cudaEventDestroy(b.in_done);
     if (b.k_done) cudaEventDestroy(b.k_done);
@@ -256,21 +260,31 @@ static bool is_pinned(const void *ptr) {
     return a.type == cudaMemoryTypeHost;
 }
 
-static int ensure_chunk(ChunkBuf &b, int64_t cases, int64_t ev, int sum_dims, bool want_post, bool stage_in, bool stage_out) {
+static int ensure_chunk(ChunkBuf &b, int64_t cases, int64_t ev, int sum_dims, bool want_post, bool want_post_host, bool stage_in,
+                        bool stage_out, bool want_gold, bool stage_gold) {
     if (!b.in_done) {
         CK(cudaEventCreateWithFlags(&b.in_done, cudaEventDisableTiming));
         CK(cudaEventCreateWithFlags(&b.k_done, cudaEventDisableTiming));
         CK(cudaEventCreateWithFlags(&b.out_done, cudaEventDisableTiming));
     }
     if (cases > b.cap_cases) {
-        cudaFree(b.d_off); cudaFree(b.d_labels); cudaFree(b.d_post);
-        cudaFreeHost(b.h_off); cudaFreeHost(b.h_labels); cudaFreeHost(b.h_post);
+        cudaFree(b.d_off); cudaFree(b.d_labels); cudaFree(b.d_post); cudaFree(b.d_gold); cudaFree(b.d_truth);
+        cudaFreeHost(b.h_off); cudaFreeHost(b.h_labels); cudaFreeHost(b.h_post); cudaFreeHost(b.h_gold); cudaFreeHost(b.h_truth);
         b.h_off = nullptr; b.h_labels = nullptr; b.h_post = nullptr; b.d_post = nullptr;
+        b.d_gold = nullptr; b.h_gold = nullptr; b.d_truth = nullptr; b.h_truth = nullptr;
         CK(cudaMalloc((void **)&b.d_off, (size_t)(cases + 1) * 8));
         CK(cudaMalloc((void **)&b.d_labels, (size_t)cases * 4));
         b.cap_cases = cases;
     }
     if (want_post && !b.d_post) CK(cudaMalloc((void **)&b.d_post, (size_t)b.cap_cases * sum_dims * 8));
+    if (want_gold && !b.d_gold) {
+        CK(cudaMalloc((void **)&b.d_gold, (size_t)b.cap_cases * sum_dims * 8));
+        CK(cudaMalloc((void **)&b.d_truth, (size_t)b.cap_cases * 4));
+    }
+    if (want_gold && stage_gold && !b.h_gold) {
+        CK(cudaMallocHost((void **)&b.h_gold, (size_t)b.cap_cases * sum_dims * 8));
+        CK(cudaMallocHost((void **)&b.h_truth, (size_t)b.cap_cases * 4));
+    }
     if (ev > b.cap_ev) {
         cudaFree(b.d_vars); cudaFree(b.d_vals); cudaFreeHost(b.h_vars); cudaFreeHost(b.h_vals);
         b.h_vars = nullptr; b.h_vals = nullptr;
@@ -284,24 +298,44 @@ static int ensure_chunk(ChunkBuf &b, int64_t cases, int64_t ev, int sum_dims, bo
     }
     if (stage_out) {
         if (!b.h_labels) CK(cudaMallocHost((void **)&b.h_labels, (size_t)b.cap_cases * 4));
-        if (want_post && !b.h_post) CK(cudaMallocHost((void **)&b.h_post, (size_t)b.cap_cases * sum_dims * 8));
+        if (want_post_host && !b.h_post) CK(cudaMallocHost((void **)&b.h_post, (size_t)b.cap_cases * sum_dims * 8));
     }
     return FBN_OK;
 }
 
-extern "C" int fbn_run(fbn_plan *p, int64_t n_cases, const int64_t *ev_offsets, const int32_t *ev_vars,
-                       const int32_t *ev_vals, int32_t *labels_out, double *posteriors_out, fbn_stats *stats) {
+static int ensure_score(fbn_plan *p, int64_t n_cases) {
+    if (n_cases > p->score_cap) {
+        cudaFree(p->score_case);
+        p->score_case = nullptr;
+        p->score_cap = 0;
+        CK(cudaMalloc((void **)&p->score_case, (size_t)n_cases * 24));
+        p->score_cap = n_cases;
+    }
+    return FBN_OK;
+}
+
+// Chunked, triple-buffered pipeline H2D -> fused kernel (-> scoring kernel) -> D2H shared by fbn_run and fbn_evaluate.
+static int run_impl(fbn_plan *p, int64_t n_cases, const int64_t *ev_offsets, const int32_t *ev_vars, const int32_t *ev_vals,
+                    const double *golden, const int32_t *truths, int32_t *labels_out, double *posteriors_out, double *out4,
+                    fbn_stats *stats) {
     if (!p) return fail(FBN_ERR_INVALID, "null plan");
     if (n_cases < 0 || (n_cases > 0 && (!ev_offsets || !labels_out))) return fail(FBN_ERR_INVALID, "bad arguments");
+    const bool want_gold = golden != nullptr;
+    if (want_gold && (!truths || !out4)) return fail(FBN_ERR_INVALID, "fbn_evaluate needs truths and out4");
     auto t0 = std::chrono::steady_clock::now();
     CK(cudaSetDevice(p->device));
     if (stats) memset(stats, 0, sizeof(*stats));
+    if (out4) { out4[0] = out4[1] = out4[2] = out4[3] = 0.0; }
     if (n_cases == 0) return FBN_OK;
     for (int64_t i = 0; i < n_cases; ++i)
         if (ev_offsets[i + 1] < ev_offsets[i]) return fail(FBN_ERR_INVALID, "ev_offsets must be non-decreasing");
     if (ev_offsets[n_cases] > ev_offsets[0] && (!ev_vars || !ev_vals)) return fail(FBN_ERR_INVALID, "null evidence arrays");
     const int sd = p->hp.sum_dims;
-    const bool want_post = posteriors_out != nullptr;
+    const bool want_post_host = posteriors_out != nullptr;
+    const bool want_post = want_post_host || want_gold;  // scoring reads the posteriors on the device
+    int rc;
+    if (want_gold && (rc = ensure_score(p, n_cases)) != FBN_OK) return rc;
+    const bool stage_gold = want_gold && !(is_pinned(golden) && is_pinned(truths));
     // chunking: ~128 MB of posteriors per chunk, at least one full wave of resident tiles
     int64_t chunk = (int64_t)(128.0 * 1048576.0 / (8.0 * sd));
     chunk = std::max<int64_t>(chunk, (int64_t)p->grid * fbn::kLanes);
@@ -323,20 +357,19 @@ extern "C" int fbn_run(fbn_plan *p, int64_t n_cases, const int64_t *ev_offsets, 
         CK(cudaEventSynchronize(b.out_done));
         if (stage_out) {
             memcpy(labels_out + pend[bi].c0, b.h_labels, (size_t)pend[bi].n * 4);
-            if (want_post) memcpy(posteriors_out + pend[bi].c0 * sd, b.h_post, (size_t)pend[bi].n * sd * 8);
+            if (want_post_host) memcpy(posteriors_out + pend[bi].c0 * sd, b.h_post, (size_t)pend[bi].n * sd * 8);
         }
         pend[bi].active = false;
         return FBN_OK;
     };
     CK(cudaEventRecord(p->ev0, p->s_k));
-    int rc;
     for (int64_t c = 0; c < n_chunks; ++c) {
         const int bi = (int)(c % kNBuf);
         ChunkBuf &b = p->buf[bi];
         if ((rc = drain(bi)) != FBN_OK) return rc;
         const int64_t c0 = c * chunk, n = std::min(n_cases, c0 + chunk) - c0;
         const int64_t e0 = ev_offsets[c0], ne = ev_offsets[c0 + n] - e0;
-        if ((rc = ensure_chunk(b, chunk, max_ev, sd, want_post, stage_in, stage_out)) != FBN_OK) return rc;
+        if ((rc = ensure_chunk(b, chunk, max_ev, sd, want_post, want_post_host, stage_in, stage_out, want_gold, stage_gold)) != FBN_OK) return rc;
         const int64_t *src_off = ev_offsets + c0;
         const int32_t *src_vars = ev_vars + e0, *src_vals = ev_vals + e0;
         if (stage_in) {
@@ -349,22 +382,41 @@ extern "C" int fbn_run(fbn_plan *p, int64_t n_cases, const int64_t *ev_offsets, 
             CK(cudaMemcpyAsync(b.d_vars, src_vars, (size_t)ne * 4, cudaMemcpyHostToDevice, p->s_in));
             CK(cudaMemcpyAsync(b.d_vals, src_vals, (size_t)ne * 4, cudaMemcpyHostToDevice, p->s_in));
         }
+        if (want_gold) {
+            const double *src_g = golden + c0 * sd;
+            const int32_t *src_t = truths + c0;
+            if (stage_gold) {
+                memcpy(b.h_gold, src_g, (size_t)n * sd * 8);
+                memcpy(b.h_truth, src_t, (size_t)n * 4);
+                src_g = b.h_gold; src_t = b.h_truth;
+            }
+            CK(cudaMemcpyAsync(b.d_gold, src_g, (size_t)n * sd * 8, cudaMemcpyHostToDevice, p->s_in));
+            CK(cudaMemcpyAsync(b.d_truth, src_t, (size_t)n * 4, cudaMemcpyHostToDevice, p->s_in));
+        }
         CK(cudaEventRecord(b.in_done, p->s_in));
         CK(cudaStreamWaitEvent(p->s_k, b.in_done, 0));
         CK(fbn::fused_launch(p->dp, p->grid, p->scratch, n, b.d_off, e0, b.d_vars, b.d_vals, b.d_labels,
                              want_post ? b.d_post : nullptr, p->s_k));
+        if (want_gold)
+            CK(fbn::score_cases_launch(n, p->hp.n_vars, sd, p->dp.vars, b.d_post, b.d_gold, b.d_labels, b.d_truth,
+                                       p->score_case + 3 * c0, p->s_k));
         CK(cudaEventRecord(b.k_done, p->s_k));
         CK(cudaStreamWaitEvent(p->s_out, b.k_done, 0));
         CK(cudaMemcpyAsync(stage_out ? b.h_labels : labels_out + c0, b.d_labels, (size_t)n * 4, cudaMemcpyDeviceToHost, p->s_out));
-        if (want_post)
+        if (want_post_host)
             CK(cudaMemcpyAsync(stage_out ? b.h_post : posteriors_out + c0 * sd, b.d_post, (size_t)n * sd * 8, cudaMemcpyDeviceToHost, p->s_out));
         CK(cudaEventRecord(b.out_done, p->s_out));
         pend[bi].c0 = c0; pend[bi].n = n; pend[bi].active = true;
         if (stats) {
-            stats->n_launches += 1;
-            stats->h2d_bytes += (n + 1) * 8 + ne * 8;
-            stats->d2h_bytes += n * 4 + (want_post ? n * (int64_t)sd * 8 : 0);
+            stats->n_launches += want_gold ? 2 : 1;
+            stats->h2d_bytes += (n + 1) * 8 + ne * 8 + (want_gold ? n * ((int64_t)sd * 8 + 4) : 0);
+            stats->d2h_bytes += n * 4 + (want_post_host ? n * (int64_t)sd * 8 : 0);
         }
+    }
+    if (want_gold) {
+        CK(fbn::score_reduce_launch(n_cases, p->score_case, p->score_out4, p->s_k));
+        CK(cudaMemcpyAsync(out4, p->score_out4, 32, cudaMemcpyDeviceToHost, p->s_k));
+        if (stats) { stats->n_launches += 1; stats->d2h_bytes += 32; }
     }
     CK(cudaEventRecord(p->ev1, p->s_k));
     for (int bi = 0; bi < kNBuf; ++bi)
@@ -380,20 +432,29 @@ extern "C" int fbn_run(fbn_plan *p, int64_t n_cases, const int64_t *ev_offsets, 
     return FBN_OK;
 }
 
+extern "C" int fbn_run(fbn_plan *p, int64_t n_cases, const int64_t *ev_offsets, const int32_t *ev_vars,
+                       const int32_t *ev_vals, int32_t *labels_out, double *posteriors_out, fbn_stats *stats) {
+    return run_impl(p, n_cases, ev_offsets, ev_vars, ev_vals, nullptr, nullptr, labels_out, posteriors_out, nullptr, stats);
+}
+
+extern "C" int fbn_evaluate(fbn_plan *p, int64_t n_cases, const int64_t *ev_offsets, const int32_t *ev_vars,
+                            const int32_t *ev_vals, const double *golden, const int32_t *truths, int32_t *labels_out,
+                            double *posteriors_out, double *out4, fbn_stats *stats) {
+    if (!golden || !truths || !out4) return fail(FBN_ERR_INVALID, "fbn_evaluate: golden, truths and out4 are required");
+    return run_impl(p, n_cases, ev_offsets, ev_vars, ev_vals, golden, truths, labels_out, posteriors_out, out4, stats);
+}
+
 extern "C" int fbn_score_device(fbn_plan *p, int64_t n_cases, const double *posteriors, const int32_t *labels,
                                 const double *golden, const int32_t *truths, double *out4_host, void *stream) {
     if (!p || !out4_host || n_cases < 0) return fail(FBN_ERR_INVALID, "bad arguments");
     if (n_cases > 0 && (!posteriors || !labels || !golden || !truths)) return fail(FBN_ERR_INVALID, "null device array");
     CK(cudaSetDevice(p->device));
     cudaStream_t st = (cudaStream_t)stream;
-    if (n_cases > p->score_cap) {
-        cudaFree(p->score_case);
-        p->score_case = nullptr;
-        CK(cudaMalloc((void **)&p->score_case, (size_t)n_cases * 16));
-        p->score_cap = n_cases;
-    }
-    CK(fbn::score_launch(n_cases, p->hp.n_vars, p->hp.sum_dims, p->dp.vars, posteriors, golden, labels, truths,
-                         p->score_case, p->score_out4, st));
+    int rc;
+    if ((rc = ensure_score(p, n_cases)) != FBN_OK) return rc;
+    CK(fbn::score_cases_launch(n_cases, p->hp.n_vars, p->hp.sum_dims, p->dp.vars, posteriors, golden, labels, truths,
+                               p->score_case, st));
+    CK(fbn::score_reduce_launch(n_cases, p->score_case, p->score_out4, st));
     CK(cudaMemcpyAsync(out4_host, p->score_out4, 32, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
     return FBN_OK;

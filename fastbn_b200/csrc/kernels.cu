@@ -261,6 +261,7 @@ __device__ __forceinline__ double round7(double number) {  // Round(number, 7), 
 
 __global__ void score_cases_kernel(int64_t n_cases, int n_vars, int sum_dims, const VarInfo *__restrict__ vars,
                                    const double *__restrict__ post, const double *__restrict__ golden,
+                                   const int32_t *__restrict__ labels, const int32_t *__restrict__ truths,
                                    double *__restrict__ out_case) {
     const int lane = threadIdx.x & 31;
     const int64_t c = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -286,20 +287,20 @@ __global__ void score_cases_kernel(int64_t n_cases, int n_vars, int sum_dims, co
         num += __shfl_xor_sync(0xffffffffu, num, o);
     }
     if (lane == 0) {
-        out_case[2 * c] = sqrt(e_mse / num);
-        out_case[2 * c + 1] = sqrt(e_hd / num);
+        out_case[3 * c] = sqrt(e_mse / num);
+        out_case[3 * c + 1] = sqrt(e_hd / num);
+        out_case[3 * c + 2] = (labels[c] == truths[c]) ? 1.0 : 0.0;  // Inference::Accuracy, src/Inference.cpp:46-61
     }
 }
 
 // deterministic single-block reduction: out4 = {n_correct, n_total, sum_mse, sum_hd}
-__global__ void score_reduce_kernel(int64_t n_cases, const double *__restrict__ out_case, const int32_t *__restrict__ labels,
-                                    const int32_t *__restrict__ truths, double *__restrict__ out4) {
+__global__ void score_reduce_kernel(int64_t n_cases, const double *__restrict__ out_case, double *__restrict__ out4) {
     __shared__ double s[3][1024];
     double a = 0, b = 0, c = 0;
     for (int64_t i = threadIdx.x; i < n_cases; i += blockDim.x) {
-        a += out_case[2 * i];
-        b += out_case[2 * i + 1];
-        c += (labels[i] == truths[i]) ? 1.0 : 0.0;
+        a += out_case[3 * i];
+        b += out_case[3 * i + 1];
+        c += out_case[3 * i + 2];
     }
     s[0][threadIdx.x] = a; s[1][threadIdx.x] = b; s[2][threadIdx.x] = c;
     __syncthreads();
@@ -358,13 +359,19 @@ cudaError_t fused_launch(const DevPlan &P, int grid, double *scratch, int64_t n_
     return cudaGetLastError();
 }
 
-cudaError_t score_launch(int64_t n_cases, int n_vars, int sum_dims, const VarInfo *vars, const double *post, const double *golden,
-                         const int32_t *labels, const int32_t *truths, double *out_case, double *out4, cudaStream_t st) {
+// per-case scores of n_cases cases into out_case[3*i..] (i relative to the arrays passed)
+cudaError_t score_cases_launch(int64_t n_cases, int n_vars, int sum_dims, const VarInfo *vars, const double *post, const double *golden,
+                               const int32_t *labels, const int32_t *truths, double *out_case, cudaStream_t st) {
     if (n_cases > 0) {
         const int wpb = 8;
-        score_cases_kernel<<<(unsigned)((n_cases + wpb - 1) / wpb), wpb * 32, 0, st>>>(n_cases, n_vars, sum_dims, vars, post, golden, out_case);
+        score_cases_kernel<<<(unsigned)((n_cases + wpb - 1) / wpb), wpb * 32, 0, st>>>(n_cases, n_vars, sum_dims, vars, post, golden,
+                                                                                      labels, truths, out_case);
     }
-    score_reduce_kernel<<<1, 1024, 0, st>>>(n_cases, out_case, labels, truths, out4);
+    return cudaGetLastError();
+}
+
+cudaError_t score_reduce_launch(int64_t n_cases, const double *out_case, double *out4, cudaStream_t st) {
+    score_reduce_kernel<<<1, 1024, 0, st>>>(n_cases, out_case, out4);
     return cudaGetLastError();
 }
 

@@ -115,6 +115,17 @@ int fbn_run_device(fbn_plan *plan, int64_t n_cases, const int64_t *ev_offsets, c
                    fbn_stats *stats);
 
 /*
+ * fbn_run + scoring in one pipelined call: what JunctionTree::EvaluateAccuracy needs (src/JunctionTree.cpp:57-129:
+ * PredictUseJTInfer for every case, CalculateMSE / CalculateHellingerDistance per case src/Inference.cpp:153-192, Accuracy
+ * src/Inference.cpp:46-61). HOST buffers. golden = n_cases x sum_dims, flattened ground_truth_probability_tables
+ * (src/Inference.cpp:108-146: first entry of an evidence node is -1); truths = ground_truths. posteriors_out may be NULL
+ * (posteriors then never leave the device). out4 = {n_correct, n_total, sum_mse, sum_hd}.
+ */
+int fbn_evaluate(fbn_plan *plan, int64_t n_cases, const int64_t *ev_offsets, const int32_t *ev_vars,
+                 const int32_t *ev_vals, const double *golden, const int32_t *truths, int32_t *labels_out,
+                 double *posteriors_out, double *out4, fbn_stats *stats);
+
+/*
  * On-device scoring against golden posteriors (replaces Inference::CalculateMSE / CalculateHellingerDistance /
  * Accuracy, src/Inference.cpp:46-61,153-206). golden is n_cases x sum_dims with golden[i][off_v] <= 0 meaning
  * "skip node v" (src/Inference.cpp:160). out4 = {n_correct, n_total, sum_mse, sum_hd} as doubles, host memory.

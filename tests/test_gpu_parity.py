@@ -136,3 +136,21 @@ def test_large_batch_properties(plan, alarm_tree):
     ew2 = ew.reshape(n, 7)[perm].reshape(-1)
     labels2, post2, _ = plan.run(off, ev2, ew2)
     assert np.array_equal(post2, post[perm]) and np.array_equal(labels2, labels[perm])
+
+
+@pytest.mark.parametrize("want_post", [False, True])
+def test_evaluate_pipeline_matches_reference_printout(plan, alarm_tree, want_post):
+    """fbn_evaluate (host buffers, inference + scoring pipelined): reference prints accuracy 1, MSE 6.50867e-17, HD 4.6999e-17"""
+    from test_oracle import read_pt
+    g = load_golden("alarm_1k_ref")
+    gold = read_pt(os.path.join(GOLDEN, "alarm", "alarm_1k_pt"), alarm_tree["var_dims"])
+    labels, post, sc, st = plan.evaluate(g["ev_off"], g["ev_vars"], g["ev_vals"], gold, g["truths"], want_post=want_post)
+    assert np.array_equal(labels, g["labels"])
+    assert sc["n_correct"] == 1000 and sc["n_total"] == 1000
+    assert abs(sc["sum_mse"] / 1000 - 6.50867e-17) < 1e-19
+    assert abs(sc["sum_hd"] / 1000 - 4.6999e-17) < 1e-19
+    if want_post:
+        assert np.nanmax(np.abs(post - g["post"])) <= TOL
+    other = np.array([int(l.split(" ")[0]) for l in open(os.path.join(GOLDEN, "alarm", "alarm_1k_p20")).read().strip().split("\n")], np.int32)
+    _, _, sc2, _ = plan.evaluate(g["ev_off"], g["ev_vars"], g["ev_vals"], gold, other)
+    assert sc2["n_correct"] == 513
