@@ -1,0 +1,86 @@
+// BayesianNetwork — CLI drop-in for the reference's `-a 2` path (src/main.cpp:61-83, src/Parameter.cpp:30-66).
+// Same flags (-a -t -f0 -f3 -f4; the others are parsed and ignored), same default files, paths relative to
+// "../dataset/", same stdout lines. Algorithms other than 2 are outside this build and say so.
+// Extensions: -G <n> shards the test cases over n GPUs (or FASTBN_DEVICES=0,1,...); -o <file> writes the posteriors
+// in the reference's potential-table format (relative to ../dataset/ too); -D <dir> replaces the "../dataset/" prefix.
+#include <cstdio>
+#include <cstdlib>
+#include <iostream>
+#include <string>
+
+#include "../fastbn_host.h"
+
+using namespace std;
+
+int main(int argc, char **argv) {
+    int algorithm = 2, num_threads = 1, n_gpus = 0;
+    string net_file = "alarm/alarm.xml", test_set_file = "alarm/testing_alarm_1k_p20", pt_file = "alarm/alarm_1k_pt";
+    string out_pt, prefix = "../dataset/";
+    int i;
+    for (i = 1; (i < argc) && ((argv[i])[0] == '-'); i++) {
+        auto need = [&](const char *) -> const char * {
+            if (i + 1 >= argc) { printf("\n Option %s needs a value!\n", argv[i]); exit(0); }
+            return argv[++i];
+        };
+        switch (argv[i][1]) {
+            case 'h':
+                cout << "Usage: ./BayesianNetwork -a 2 [-t threads] [-f0 bn.xml] [-f3 test cases] [-f4 potential tables] [-G gpus] [-o out_pt] [-D dataset dir]" << endl;
+                exit(0);
+            case 'a': algorithm = atoi(need("a")); break;
+            case 't': num_threads = atoi(need("t")); break;
+            case 'q': case 'm': case 'l': case 'd': case 'g': need("x"); break;  // sampling / PC-stable options: ignored
+            case 'G': n_gpus = atoi(need("G")); break;
+            case 'o': out_pt = need("o"); break;
+            case 'D': prefix = need("D"); if (!prefix.empty() && prefix.back() != '/') prefix += '/'; break;
+            case 'f':
+                switch (argv[i][2]) {
+                    case '0': net_file = need("f0"); break;
+                    case '3': test_set_file = need("f3"); break;
+                    case '4': pt_file = need("f4"); break;
+                    case '1': case '2': need("f"); break;
+                }
+                break;
+            default:
+                printf("\n Unrecognized option %s!\n", argv[i]);
+                exit(0);
+        }
+    }
+    if (algorithm < 0 || algorithm > 11) {
+        cout << "\tError! Please give the right value of -a to specify the functionality/algorithm" << endl;
+        exit(0);
+    }
+    net_file = prefix + net_file;
+    test_set_file = prefix + test_set_file;
+    pt_file = prefix + pt_file;
+    if (algorithm != 2) {
+        cout << "This build (fastbn_b200) only provides -a 2: junction tree (JT) for exact inference" << endl;
+        return 0;
+    }
+    cout << "===============================" << endl;
+    cout << "Algorithm: junction tree (JT) for exact inference, #threads = " << num_threads << endl;
+    cout << "\tBN: " << net_file << endl;
+    cout << "\ttesting set: " << test_set_file << endl;
+    cout << "\treference potential table: " << pt_file << endl;
+    cout << "===============================" << endl;
+
+    Dataset *tester = new Dataset();
+    CustomNetwork *network = new CustomNetwork(true);
+    network->GetNetFromXMLBIFFile(net_file);
+    tester->LoadLIBSVMDataKnownNetwork(test_set_file, network->num_nodes);
+
+    JunctionTree *jt = new JunctionTree(network, tester, false);
+    if (n_gpus > 0) {
+        jt->devices.clear();
+        for (int d = 0; d < n_gpus; ++d) jt->devices.push_back(d);
+    }
+    jt->keep_posteriors = !out_pt.empty();
+    Inference *inference = jt;
+    double accuracy = inference->EvaluateAccuracy(pt_file, num_threads);
+    cout << "accuracy = " << accuracy << endl;
+    if (!out_pt.empty()) jt->WritePotentialTableFile(prefix + out_pt);
+
+    delete inference;
+    delete network;
+    delete tester;
+    return 0;
+}

@@ -35,3 +35,77 @@ def write_libsvm(path, ev_off, ev_vars, ev_vals, labels=None):
             lab = 0 if labels is None else int(labels[i])
             parts = [str(lab)] + ["%d:%d" % (ev_vars[k], ev_vals[k]) for k in range(ev_off[i], ev_off[i + 1])]
             f.write(" ".join(parts) + " \n")
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Synthetic networks of the named shapes (BASELINE.json configs 3-5; recipe of SURVEY.md Appendix B): node i draws
+# 1..max_par parents uniformly from the previous `window` nodes (bounded treewidth), CPT rows are Dirichlet(1) samples
+# printed with 4 decimals in the reference's <TABLE> order (FOR variable most significant, then <GIVEN>s in file order).
+SHAPES = {
+    # name: generator parameters; the seeds were found by tools/make_synth_golden.py --sweep so that the junction tree the
+    # reference (and our host mirror) builds has the named maximum clique size. n_evidence = int(frac * n).
+    # hepar2: 52 cliques, 29 levels, max clique 6 912, sum |clique| 67 286
+    "hepar2": dict(n=70, dims=(2, 3, 4), max_par=6, window=8, par_geom=0.55, seed=20260103, max_clique=6912, evidence=(14, 35),
+                   desc="synthetic HEPAR2-shape BN (70 nodes, card 2-4)"),
+    # pigs: 380 cliques, 75 levels, max clique 3^10, sum |clique| 264 690
+    "pigs": dict(n=441, dims=(3,), max_par=2, window=10, seed=20260126, max_clique=59049, evidence=(88,),
+                 desc="synthetic PIGS-shape BN (441 nodes, card 3, max clique 3^10)"),
+    # munin_small: 102 cliques, 37 levels, max clique 5^9, sum |clique| 3 185 150 (oracle-friendly stand-in)
+    "munin_small": dict(n=120, dims=(5,), max_par=2, window=9, seed=20260148, max_clique=1953125, evidence=(0,),
+                        desc="synthetic MUNIN-shape stand-in (120 nodes, card 5, max clique 5^9)"),
+    # munin: 105 cliques, 29 levels, max clique 5^10 = 9.8e6, sum |clique| 14 551 925
+    "munin": dict(n=120, dims=(5,), max_par=2, window=12, seed=20260127, max_clique=9765625, evidence=(0,),
+                  desc="synthetic MUNIN-shape BN (120 nodes, card 5, max clique 5^10 ~ 1e7)"),
+}
+
+
+def window_network(n, dims, max_par, window, seed, par_geom=0.0):
+    """Returns (var_dims int32[n], parents list[list[int]] in GIVEN order, cpts list[np.ndarray (dim, n_parent_cfgs)])."""
+    rng = np.random.Generator(np.random.MT19937(seed))
+    var_dims = np.array([dims[int(rng.integers(0, len(dims)))] for _ in range(n)], np.int32)
+    parents, cpts = [], []
+    for i in range(n):
+        lo = max(0, i - window)
+        if par_geom:  # most nodes get 1-2 parents, a few up to max_par (HEPAR2-like in-degree profile)
+            k = 0 if i == 0 else int(min(i - lo, max_par, rng.geometric(par_geom)))
+        else:
+            k = 0 if i == 0 else int(min(i - lo, rng.integers(1, max_par + 1)))
+        pa = sorted(int(x) for x in rng.choice(np.arange(lo, i), size=k, replace=False)) if k else []
+        ncfg = int(np.prod(var_dims[pa])) if pa else 1
+        p = rng.dirichlet(np.ones(int(var_dims[i])), size=ncfg).T  # (dim, ncfg): FOR variable most significant
+        parents.append(pa)
+        cpts.append(np.round(p, 4))
+    return var_dims, parents, cpts
+
+
+def write_xmlbif(path, var_dims, parents, cpts, name="synthetic"):
+    with open(path, "w") as f:
+        f.write('<?xml version="1.0" encoding="UTF-8"?>\n<BIF>\n    <NETWORK>\n        <NAME>%s</NAME>\n' % name)
+        for i, d in enumerate(var_dims):
+            f.write("        <VARIABLE>\n            <NAME>V%d</NAME>\n            <TYPE>discrete</TYPE>\n" % i)
+            for s in range(int(d)):
+                f.write("            <VALUE>s%d</VALUE>\n" % s)
+            f.write("        </VARIABLE>\n")
+        for i in range(len(var_dims)):
+            f.write("        <PROBABILITY>\n            <FOR>V%d</FOR>\n" % i)
+            for p in parents[i]:
+                f.write("            <GIVEN>V%d</GIVEN>\n" % p)
+            f.write("            <TABLE>" + " ".join("%.4f" % x for x in cpts[i].reshape(-1)) + " </TABLE>\n        </PROBABILITY>\n")
+        f.write("    </NETWORK>\n</BIF>\n")
+
+
+def make_shape(name, path, seed=None, **override):
+    """Writes the XMLBIF of a named shape; returns var_dims."""
+    cfg = dict(SHAPES[name])
+    cfg.update(override)
+    if seed is not None:
+        cfg["seed"] = seed
+    var_dims, parents, cpts = window_network(cfg["n"], cfg["dims"], cfg["max_par"], cfg["window"], cfg["seed"], cfg.get("par_geom", 0.0))
+    write_xmlbif(path, var_dims, parents, cpts, name=name)
+    return var_dims
+
+
+def write_empty_pt(path):
+    """The reference only needs the -f4 file to OPEN (src/Inference.cpp:120-124); MSE/HD then print as nan."""
+    with open(path, "w") as f:
+        f.write("\n")

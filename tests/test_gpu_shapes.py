@@ -1,0 +1,97 @@
+"""GPU parity on the synthetic shapes of BASELINE.json configs 3-5 and on the host mirror / CLI (run with -m gpu).
+Trees are built by the C++ host mirror from the committed XMLBIF files; expected posteriors come from the unmodified
+reference (tests/golden/synth/*_ref.npz). Tolerance: posteriors max-abs <= 1e-9, labels bit-identical."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, ROOT, load_golden
+from fastbn_b200 import capi, hostapi, synth
+from oracle import jtoracle
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-9
+
+
+def _shape(name):
+    m = hostapi.HostModel(os.path.join(GOLDEN, "synth", name + ".xml"))
+    t = m.tree()
+    m.close()
+    return t, load_golden(os.path.join("synth", name + "_ref"))
+
+
+@pytest.mark.parametrize("name,team", [("hepar2", 0), ("hepar2", 1), ("hepar2", 8), ("pigs", 0), ("pigs", 2), ("pigs", 32)])
+def test_shape_matches_reference(name, team):
+    t, g = _shape(name)
+    p = capi.Plan(t, device=0, team_warps=team)
+    labels, post, st = p.run(g["ev_off"], g["ev_vars"], g["ev_vals"])
+    p.close()
+    assert np.nanmax(np.abs(post - g["post"])) <= TOL
+    assert np.array_equal(labels, g["labels"])
+
+
+@pytest.mark.parametrize("name,n,nev", [("hepar2", 20000, 14), ("hepar2", 5000, 35), ("pigs", 3000, 88)])
+def test_shape_batch_properties(name, n, nev):
+    """many tiles: every non-evidence variable sums to 1, evidence variables are zero rows, repeated cases give repeated
+    results, and a seeded prefix matches the CPU oracle."""
+    t, _ = _shape(name)
+    d = t["var_dims"]
+    off, ev, ew = synth.uniform_evidence(d, n, nev, seed=4242)
+    ev[-nev:] = ev[:nev]      # last case == first case
+    ew[-nev:] = ew[:nev]
+    p = capi.Plan(t, device=0)
+    labels, post, _ = p.run(off, ev, ew)
+    p.close()
+    voff = np.concatenate([[0], np.cumsum(d)])
+    sums = np.add.reduceat(post, voff[:-1], axis=1)
+    is_ev = np.zeros((n, len(d)), bool)
+    is_ev[np.repeat(np.arange(n), nev), ev] = True
+    assert np.all(np.abs(sums[~is_ev] - 1.0) < 1e-10)
+    assert np.all(sums[is_ev] == 0.0)
+    assert np.array_equal(post[0], post[-1]) and labels[0] == labels[-1]
+    k = 24
+    o = jtoracle.Oracle(t)
+    opost, olab = o.run_batch(off[:k + 1], ev[:k * nev], ew[:k * nev])
+    o.close()
+    assert np.max(np.abs(post[:k] - opost)) <= TOL and np.array_equal(labels[:k], olab)
+
+
+def test_host_mirror_evaluate_alarm():
+    """JunctionTree::EvaluateAccuracy of the C++ mirror on the reference's default run: accuracy 1, MSE 6.50867e-17, HD 4.6999e-17"""
+    g = load_golden("alarm_1k_ref")
+    m = hostapi.HostModel(os.path.join(GOLDEN, "alarm", "alarm.xml"), os.path.join(GOLDEN, "alarm", "testing_alarm_1k_p20"))
+    r = m.evaluate(os.path.join(GOLDEN, "alarm", "alarm_1k_pt"), want_post=True)
+    assert r["accuracy"] == 1.0
+    assert abs(r["average_mse"] - 6.50867e-17) < 1e-19 and abs(r["average_hd"] - 4.6999e-17) < 1e-19
+    assert np.array_equal(r["labels"], g["labels"])
+    assert np.nanmax(np.abs(r["post"] - g["post"])) <= TOL
+    m.close()
+    m = hostapi.HostModel(os.path.join(GOLDEN, "alarm", "alarm.xml"), os.path.join(GOLDEN, "alarm", "alarm_1k_p20"))
+    r = m.evaluate(os.path.join(GOLDEN, "alarm", "alarm_1k_pt"))
+    assert abs(r["accuracy"] - 0.513) < 1e-12
+    m.close()
+
+
+def test_cli_default_run_prints_reference_lines(tmp_path):
+    """`BayesianNetwork` with no flags = `-a 2 -t 1` on ALARM (reference README / SURVEY.md 8(c) fixtures); -o writes a pt
+    file that round-trips through the loader to MSE 0 against itself and reproduces the shipped golden file to 7 decimals."""
+    exe = os.path.join(ROOT, "fastbn_b200", "bin", "BayesianNetwork")
+    ds = tmp_path / "dataset"
+    bd = tmp_path / "build"
+    ds.mkdir()
+    bd.mkdir()
+    os.symlink(os.path.join(GOLDEN, "alarm"), ds / "alarm")
+    r = subprocess.run([exe], cwd=bd, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    for line in ["number of cliques = 27, number of separators = 26", "ave clique size = 41.1111, max size = 144",
+                 "maximum level of the junction tree = 15", "average MSE = 6.50867e-17", "average HD = 4.6999e-17", "accuracy = 1"]:
+        assert line in r.stdout, line
+    assert "jt: " in r.stdout
+    r = subprocess.run([exe, "-a", "2", "-t", "4", "-f3", "alarm/alarm_1k_p20"], cwd=bd, capture_output=True, text=True, timeout=300)
+    assert "accuracy = 0.513" in r.stdout
+    out = tmp_path / "out_pt"
+    r = subprocess.run([exe, "-D", str(ds), "-o", "../out_pt"], cwd=bd, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    assert open(out).read() == open(os.path.join(GOLDEN, "alarm", "alarm_1k_pt")).read()
