@@ -25,15 +25,42 @@ sys.path.insert(0, ROOT)
 GOLDEN = os.path.join(ROOT, "tests", "golden")
 
 WORKLOADS = {
-    # name: (tree fixture, xml, #evidence vars, default cases per GPU)
-    "alarm": dict(tree="alarm_tree_ref.npz", xml=os.path.join("alarm", "alarm.xml"), n_evidence=7, cases=1_000_000,
+    # name: tree source, #evidence vars, default cases per GPU per step
+    "alarm": dict(ref_cases=60000, tree="alarm_tree_ref.npz", xml=os.path.join("alarm", "alarm.xml"), n_evidence=7, cases=1_000_000,
                   desc="ALARM (37 nodes), 1M synthetic test cases, 20% evidence (7 vars), batched"),
+    # BASELINE.json configs 3-5 (parity-test shapes; benchable with --workload): trees built by the C++ host mirror
+    "hepar2": dict(ref_cases=1200, shape="hepar2", n_evidence=14, cases=1_000_000, desc="synthetic HEPAR2-shape BN (70 nodes, card 2-4), 20% evidence"),
+    "hepar2_50": dict(ref_cases=2400, shape="hepar2", n_evidence=35, cases=1_000_000, desc="synthetic HEPAR2-shape BN (70 nodes, card 2-4), 50% evidence"),
+    "pigs": dict(ref_cases=200, shape="pigs", n_evidence=88, cases=65_536, desc="synthetic PIGS-shape BN (441 nodes, card 3, max clique 3^10), 20% evidence"),
+    "munin_small": dict(ref_cases=8, shape="munin_small", n_evidence=0, cases=2048, desc="synthetic MUNIN-shape stand-in (max clique 5^9), 0% evidence"),
+    "munin": dict(ref_cases=1, shape="munin", n_evidence=0, cases=512, desc="synthetic MUNIN-shape BN (max clique 5^10 ~ 1e7), 0% evidence"),
 }
 
 
+def workload_xml(w):
+    """Path of the workload's XMLBIF (committed for alarm/hepar2/pigs, generated from the recorded seed otherwise)."""
+    from fastbn_b200 import synth
+    cfg = WORKLOADS[w]
+    if "xml" in cfg:
+        return os.path.join(GOLDEN, cfg["xml"])
+    p = os.path.join(GOLDEN, "synth", cfg["shape"] + ".xml")
+    if not os.path.exists(p):
+        os.makedirs(os.path.join(ROOT, "build", "synth"), exist_ok=True)
+        p = os.path.join(ROOT, "build", "synth", "%s_%d.xml" % (cfg["shape"], os.getpid()))
+        synth.make_shape(cfg["shape"], p)
+    return p
+
+
 def load_tree(w):
-    z = np.load(os.path.join(GOLDEN, WORKLOADS[w]["tree"]))
-    return {k: z[k] for k in z.files}
+    cfg = WORKLOADS[w]
+    if "tree" in cfg:
+        z = np.load(os.path.join(GOLDEN, cfg["tree"]))
+        return {k: z[k] for k in z.files}
+    from fastbn_b200 import hostapi
+    m = hostapi.HostModel(workload_xml(w))
+    t = m.tree()
+    m.close()
+    return t
 
 
 class ClockSampler(threading.Thread):
@@ -98,8 +125,10 @@ def cpu_reference_throughput(workload, cases_per_core, cores, seed):
     w = WORKLOADS[workload]
     tree = load_tree(workload)
     kind = "reference" if refdrv.available() else "port"
-    xml = os.path.join(GOLDEN, w["xml"])
-    cases_file = os.path.join(GOLDEN, "alarm", "testing_alarm_1k_p20")
+    xml = workload_xml(workload)
+    cases_file = os.path.join(ROOT, "build", "ref_cases_%d" % os.getpid())  # the reference's ctor wants a LIBSVM file
+    os.makedirs(os.path.dirname(cases_file), exist_ok=True)
+    synth.write_libsvm(cases_file, *synth.uniform_evidence(tree["var_dims"], 20, 0, seed=1))
     jobs = []
     for c in range(cores):
         off, ev, ew = synth.uniform_evidence(tree["var_dims"], cases_per_core, w["n_evidence"], seed=seed + c)
@@ -121,9 +150,10 @@ def run_reference_arm(args):
         return
     cores = os.cpu_count() or 1
     w = WORKLOADS[args.workload]
-    per_core = args.ref_cases_per_core
+    # bounded sample per step: a quarter of the cpu_baseline sample (a few seconds of CPU work per step)
+    per_core = args.ref_cases_per_core or max(1, w["ref_cases"] // 4)
     for _ in range(min(args.warmup, 1)):
-        cpu_reference_throughput(args.workload, max(100, per_core // 10), cores, 777)
+        cpu_reference_throughput(args.workload, max(1, per_core // 10), cores, 777)
     vals = []
     t0 = time.perf_counter()
     for s in range(args.steps):
@@ -150,7 +180,7 @@ def main():
     ap.add_argument("--workload", default="alarm", choices=sorted(WORKLOADS))
     ap.add_argument("--cases", type=int, default=0, help="cases per GPU per step (default: the workload's)")
     ap.add_argument("--team", type=int, default=0)
-    ap.add_argument("--ref-cases-per-core", type=int, default=4000)
+    ap.add_argument("--ref-cases-per-core", type=int, default=0, help="CPU sample per core (default: the workload's, ~10-20 s)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--e2e-steps", type=int, default=0, help="timed e2e steps (default: min(steps, 5))")
     args = ap.parse_args()
@@ -279,7 +309,7 @@ def main():
         }
         if world == 1 and not args.no_cpu_baseline:
             cores = os.cpu_count() or 1
-            v, kind, sample = cpu_reference_throughput(args.workload, args.ref_cases_per_core, cores, 555)
+            v, kind, sample = cpu_reference_throughput(args.workload, args.ref_cases_per_core or w["ref_cases"], cores, 555)
             line["cpu_baseline"] = {"value": v, "unit": "cases/s", "cores": cores, "kind": kind, "sample": sample}
         print(json.dumps(line), flush=True)
     plan.close()
