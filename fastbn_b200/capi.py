@@ -13,6 +13,9 @@ ABI_SYMBOLS = ["fbn_last_error", "fbn_device_count", "fbn_plan_create", "fbn_pla
                "fbn_run", "fbn_run_device", "fbn_evaluate", "fbn_score_device"]
 
 
+MODE_AUTO, MODE_FUSED, MODE_LEVEL = 0, 1, 2
+
+
 class FastBNError(RuntimeError):
     pass
 
@@ -24,12 +27,13 @@ class TreeDesc(C.Structure):
 
 
 class PlanOptions(C.Structure):
-    _fields_ = [("device", C.c_int32), ("team_warps", C.c_int32), ("max_resident", C.c_int32), ("reserved", C.c_int32 * 5)]
+    _fields_ = [("device", C.c_int32), ("team_warps", C.c_int32), ("max_resident", C.c_int32), ("mode", C.c_int32), ("reserved", C.c_int32 * 4)]
 
 
 class PlanInfo(C.Structure):
     _fields_ = [("n_vars", C.c_int32), ("n_cliques", C.c_int32), ("n_separators", C.c_int32), ("sum_dims", C.c_int32),
                 ("n_levels", C.c_int32), ("team_warps", C.c_int32), ("resident_tiles", C.c_int32), ("n_phases", C.c_int32),
+                ("mode", C.c_int32), ("launches_per_wave", C.c_int32),
                 ("clique_entries", C.c_int64), ("separator_entries", C.c_int64), ("parent_entries", C.c_int64),
                 ("marginal_entries", C.c_int64), ("scratch_bytes", C.c_int64), ("plan_bytes", C.c_int64),
                 ("alg_bytes_per_case", C.c_double), ("kernel_bytes_per_case", C.c_double)]
@@ -82,7 +86,7 @@ def _ptr(a):
 class Plan:
     """Device plan of one junction tree (fbn_plan). `tree` is a dict with the fields of fbn_tree_desc."""
 
-    def __init__(self, tree, device=-1, team_warps=0, max_resident=0):
+    def __init__(self, tree, device=-1, team_warps=0, max_resident=0, mode=0):
         self.L = load_library()
         t = tree
         self._keep = dict(
@@ -94,7 +98,7 @@ class Plan:
         d = TreeDesc(int(t["n_vars"]), _ptr(k["var_dims"]), int(t["n_cliques"]), int(t["n_separators"]), _ptr(k["table_nvars"]),
                      _ptr(k["table_vars"]), _ptr(k["clique_potentials"]), _ptr(k["sep_parent"]), _ptr(k["sep_child"]),
                      int(t["root"]), int(t["query_var"]))
-        opt = PlanOptions(device, team_warps, max_resident, (C.c_int32 * 5)())
+        opt = PlanOptions(device, team_warps, max_resident, mode, (C.c_int32 * 4)())
         h = C.c_void_p()
         _check(self.L, self.L.fbn_plan_create(C.byref(d), C.byref(opt), C.byref(h)))
         self.h = h

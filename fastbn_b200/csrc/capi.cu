@@ -16,6 +16,9 @@ size_t fused_smem_bytes(const DevPlan &P);
 cudaError_t fused_prepare(const DevPlan &P, int *blocks_per_sm);
 cudaError_t fused_launch(const DevPlan &P, int grid, double *scratch, int64_t n_cases, const int64_t *ev_off, int64_t ev_base,
                          const int32_t *ev_vars, const int32_t *ev_vals, int32_t *labels, double *post, cudaStream_t st);
+cudaError_t level_launch(const DevPlan &P, const std::vector<Phase> &phases, int resident, double *scratch, uint32_t *lamG,
+                         int64_t n_cases, const int64_t *ev_off, int64_t ev_base, const int32_t *ev_vars, const int32_t *ev_vals,
+                         int32_t *labels, double *post, cudaStream_t st, int64_t *n_launch);
 cudaError_t score_cases_launch(int64_t n_cases, int n_vars, int sum_dims, const VarInfo *vars, const double *post, const double *golden,
                                const int32_t *labels, const int32_t *truths, double *out_case, cudaStream_t st);
 cudaError_t score_reduce_launch(int64_t n_cases, const double *out_case, double *out4, cudaStream_t st);
@@ -57,6 +60,9 @@ struct fbn_plan {
     int n_sms = 0, blocks_per_sm = 0, grid = 0;
     std::vector<void *> dev_allocs;
     double *scratch = nullptr;
+    uint32_t *lamG = nullptr;   // level mode: evidence bit words of the resident tiles
+    bool level = false;
+    int launches_per_wave = 1;
     int64_t scratch_bytes = 0, plan_bytes = 0;
     cudaStream_t s_in = nullptr, s_k = nullptr, s_out = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -89,9 +95,7 @@ static int upload(fbn_plan *p, const std::vector<T> &v, const T **out) {
     return FBN_OK;
 }
 
-static int pick_team(const fbn_tree_desc *t) {
-    // scratch rows per tile ~ clique entries; keep (resident tiles x tile bytes) within a few tens of GB and give
-    // big tables more warps per tile. 1 warp per tile for ALARM/HEPAR2-size trees.
+static double tree_entries(const fbn_tree_desc *t) {  // sum of clique table sizes
     double entries = 0;
     int64_t pos = 0;
     for (int c = 0; c < t->n_cliques; ++c) {
@@ -100,12 +104,31 @@ static int pick_team(const fbn_tree_desc *t) {
         pos += t->table_nvars[c];
         entries += sz;
     }
+    return entries;
+}
+
+// above this many clique entries per case AUTO uses level mode (tile >= ~0.5 GB: too few tiles fit for one CTA per tile)
+static const double kLevelAutoEntries = 2.0e6;
+static const int64_t kLevelMaxResident = 4096;
+
+static int pick_team(double entries) {
+    // fused mode: more warps per tile for bigger tables (measured on ALARM / HEPAR2- / PIGS-shape)
     if (entries <= 8192) return 1;
-    if (entries <= 32768) return 2;
-    if (entries <= 131072) return 4;
-    if (entries <= 1048576) return 8;
-    if (entries <= 8388608) return 16;
+    if (entries <= 32768) return 4;
+    if (entries <= 131072) return 8;
+    if (entries <= 1048576) return 16;
     return 32;
+}
+
+// one inference pass over n_cases cases whose inputs are on the device: fused kernel or the per-level launches
+static cudaError_t launch_inference(fbn_plan *p, int64_t n_cases, const int64_t *ev_off, int64_t ev_base, const int32_t *ev_vars,
+                                    const int32_t *ev_vals, int32_t *labels, double *post, cudaStream_t st, int64_t *n_launch) {
+    if (n_cases <= 0) { *n_launch = 0; return cudaSuccess; }
+    if (p->level)
+        return fbn::level_launch(p->dp, p->hp.phases, p->grid, p->scratch, p->lamG, n_cases, ev_off, ev_base, ev_vars, ev_vals,
+                                 labels, post, st, n_launch);
+    *n_launch = 1;
+    return fbn::fused_launch(p->dp, p->grid, p->scratch, n_cases, ev_off, ev_base, ev_vars, ev_vals, labels, post, st);
 }
 
 extern "C" int fbn_plan_create(const fbn_tree_desc *tree, const fbn_plan_options *opt, fbn_plan **out) {
@@ -129,11 +152,32 @@ extern "C" int fbn_plan_create(const fbn_tree_desc *tree, const fbn_plan_options
             pos += tree->table_nvars[i];
         }
     }
-    int team = opt && opt->team_warps > 0 ? opt->team_warps : pick_team(tree);
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, dev));
+    size_t free_b = 0, total_b = 0;
+    CK(cudaMemGetInfo(&free_b, &total_b));
+    const int64_t budget = (int64_t)(free_b * 0.45);  // leave room for the caller's evidence / posterior buffers
+    const double entries = tree_entries(tree);
+    int mode = opt ? opt->mode : FBN_MODE_AUTO;
+    if (const char *e = getenv("FBN_MODE")) mode = atoi(e);
+    if (mode != FBN_MODE_FUSED && mode != FBN_MODE_LEVEL) mode = entries > kLevelAutoEntries ? FBN_MODE_LEVEL : FBN_MODE_FUSED;
+    const bool level = mode == FBN_MODE_LEVEL;
+    int team = opt && opt->team_warps > 0 ? opt->team_warps : 0;
+    if (!team && !level) team = pick_team(entries);
+    if (!team && level) {
+        // nominal warps per tile: enough CTAs over all resident tiles to fill the GPU several times over
+        int64_t est_tile = (int64_t)(entries * 1.25 + 4096) * fbn::kLanes * 8;
+        int64_t res = std::max<int64_t>(1, std::min<int64_t>(kLevelMaxResident, budget / est_tile));
+        if (opt && opt->max_resident > 0) res = std::min<int64_t>(res, opt->max_resident);
+        int64_t nb = (8 * (int64_t)prop.multiProcessorCount + res - 1) / res;
+        nb = std::max<int64_t>(2, std::min<int64_t>(nb, 512));
+        team = (int)nb * fbn::kLevelWarps;
+    }
 
     fbn_plan *p = new fbn_plan();
     p->device = dev;
-    std::string err = fbn::build_plan(*tree, team, p->hp);
+    p->level = level;
+    std::string err = fbn::build_plan(*tree, team, p->hp, level);
     if (!err.empty()) {
         delete p;
         return fail(FBN_ERR_INVALID, err);
@@ -148,28 +192,32 @@ extern "C" int fbn_plan_create(const fbn_tree_desc *tree, const fbn_plan_options
     d.n_vars = h.n_vars; d.sum_dims = h.sum_dims; d.query_var = h.query_var;
     d.tile_rows = h.tile_rows; d.mg_row0 = h.mg_row0;
     d.max_normslots = h.max_normslots; d.max_pslots = h.max_pslots; d.max_mask_words = h.max_mask_words; d.team = h.team;
+    d.part_row0 = h.part_row0; d.normpart_row0 = h.normpart_row0; d.nb_max = h.nb_max; d.lam_words = h.sum_dims + h.n_vars;
 
-    cudaDeviceProp prop;
-    CK(cudaGetDeviceProperties(&prop, dev));
     p->n_sms = prop.multiProcessorCount;
-    if (fbn::fused_smem_bytes(d) > (size_t)prop.sharedMemPerBlockOptin) {
-        fbn_plan_destroy(p);
-        return fail(FBN_ERR_INVALID, "tree needs more shared memory per tile than the device has");
-    }
-    cudaError_t ce = fbn::fused_prepare(d, &p->blocks_per_sm);
-    if (ce != cudaSuccess) {
-        fbn_plan_destroy(p);
-        return fail(FBN_ERR_CUDA, std::string("kernel setup failed (is this an sm_100 device?): ") + cudaGetErrorString(ce));
-    }
-    if (p->blocks_per_sm < 1) p->blocks_per_sm = 1;
+    cudaError_t ce;
     int64_t tile_bytes = (int64_t)h.tile_rows * fbn::kLanes * 8;
-    int64_t resident = (int64_t)p->n_sms * p->blocks_per_sm;
-    size_t free_b = 0, total_b = 0;
-    CK(cudaMemGetInfo(&free_b, &total_b));
-    int64_t budget = (int64_t)(free_b * 0.45);  // leave room for the caller's evidence / posterior buffers
-    if (resident * tile_bytes > budget) resident = std::max<int64_t>(1, budget / tile_bytes);
+    int64_t resident;
+    if (level) {
+        resident = std::max<int64_t>(1, std::min<int64_t>(kLevelMaxResident, budget / tile_bytes));
+        p->launches_per_wave = 2;
+        for (const fbn::Phase &ph : h.phases) p->launches_per_wave += 1 + (ph.fin_end > ph.fin_begin ? 1 : 0);
+    } else {
+        if (fbn::fused_smem_bytes(d) > (size_t)prop.sharedMemPerBlockOptin) {
+            fbn_plan_destroy(p);
+            return fail(FBN_ERR_INVALID, "tree needs more shared memory per tile than the device has");
+        }
+        ce = fbn::fused_prepare(d, &p->blocks_per_sm);
+        if (ce != cudaSuccess) {
+            fbn_plan_destroy(p);
+            return fail(FBN_ERR_CUDA, std::string("kernel setup failed (is this an sm_100 device?): ") + cudaGetErrorString(ce));
+        }
+        if (p->blocks_per_sm < 1) p->blocks_per_sm = 1;
+        resident = (int64_t)p->n_sms * p->blocks_per_sm;
+        if (resident * tile_bytes > budget) resident = std::max<int64_t>(1, budget / tile_bytes);
+    }
     if (opt && opt->max_resident > 0) resident = std::min<int64_t>(resident, opt->max_resident);
-    if (resident >= p->n_sms) resident = resident / p->n_sms * p->n_sms;  // whole waves over the SMs
+    if (!level && resident >= p->n_sms) resident = resident / p->n_sms * p->n_sms;  // whole waves over the SMs
     p->grid = (int)resident;
     p->scratch_bytes = resident * tile_bytes;
     ce = cudaMalloc((void **)&p->scratch, (size_t)p->scratch_bytes);
@@ -178,6 +226,10 @@ extern "C" int fbn_plan_create(const fbn_tree_desc *tree, const fbn_plan_options
         return fail(FBN_ERR_NOMEM, "cannot allocate tile scratch");
     }
     CK(cudaMemset(p->scratch, 0, (size_t)p->scratch_bytes));
+    if (level) {
+        CK(cudaMalloc((void **)&p->lamG, (size_t)resident * d.lam_words * 4));
+        p->plan_bytes += resident * (int64_t)d.lam_words * 4;
+    }
     CK(cudaStreamCreateWithFlags(&p->s_in, cudaStreamNonBlocking));
     CK(cudaStreamCreateWithFlags(&p->s_k, cudaStreamNonBlocking));
     CK(cudaStreamCreateWithFlags(&p->s_out, cudaStreamNonBlocking));
@@ -204,6 +256,7 @@ extern "C" void fbn_plan_destroy(fbn_plan *p) {
     cudaDeviceSynchronize();
     for (void *d : p->dev_allocs) cudaFree(d);
     cudaFree(p->scratch);
+    cudaFree(p->lamG);
     cudaFree(p->score_case);
     cudaFree(p->score_out4);
     for (auto &b : p->buf) free_chunk(b);
@@ -222,6 +275,7 @@ extern "C" int fbn_plan_get_info(const fbn_plan *p, fbn_plan_info *o) {
     memset(o, 0, sizeof(*o));
     o->n_vars = h.n_vars; o->n_cliques = h.n_cliques; o->n_separators = h.n_seps; o->sum_dims = h.sum_dims;
     o->n_levels = h.n_levels; o->team_warps = h.team; o->resident_tiles = p->grid; o->n_phases = (int32_t)h.phases.size();
+    o->mode = p->level ? FBN_MODE_LEVEL : FBN_MODE_FUSED; o->launches_per_wave = p->launches_per_wave;
     o->clique_entries = h.clique_entries; o->separator_entries = h.sep_entries; o->parent_entries = h.parent_entries;
     o->marginal_entries = h.marginal_entries; o->scratch_bytes = p->scratch_bytes; o->plan_bytes = p->plan_bytes;
     o->alg_bytes_per_case = h.alg_bytes_per_case; o->kernel_bytes_per_case = h.kernel_bytes_per_case;
@@ -236,7 +290,8 @@ extern "C" int fbn_run_device(fbn_plan *p, int64_t n_cases, const int64_t *ev_of
     CK(cudaSetDevice(p->device));
     cudaStream_t st = (cudaStream_t)stream;
     if (stats) CK(cudaEventRecord(p->ev0, st));
-    CK(fbn::fused_launch(p->dp, p->grid, p->scratch, n_cases, ev_offsets, 0, ev_vars, ev_vals, labels_out, posteriors_out, st));
+    int64_t nl = 0;
+    CK(launch_inference(p, n_cases, ev_offsets, 0, ev_vars, ev_vals, labels_out, posteriors_out, st, &nl));
     if (stats) {
         CK(cudaEventRecord(p->ev1, st));
         CK(cudaEventSynchronize(p->ev1));
@@ -245,7 +300,7 @@ extern "C" int fbn_run_device(fbn_plan *p, int64_t n_cases, const int64_t *ev_of
         memset(stats, 0, sizeof(*stats));
         stats->kernel_ms = ms;
         stats->total_ms = ms;
-        stats->n_launches = n_cases > 0 ? 1 : 0;
+        stats->n_launches = nl;
     }
     return FBN_OK;
 }
@@ -395,8 +450,8 @@ static int run_impl(fbn_plan *p, int64_t n_cases, const int64_t *ev_offsets, con
         }
         CK(cudaEventRecord(b.in_done, p->s_in));
         CK(cudaStreamWaitEvent(p->s_k, b.in_done, 0));
-        CK(fbn::fused_launch(p->dp, p->grid, p->scratch, n, b.d_off, e0, b.d_vars, b.d_vals, b.d_labels,
-                             want_post ? b.d_post : nullptr, p->s_k));
+        int64_t nl = 0;
+        CK(launch_inference(p, n, b.d_off, e0, b.d_vars, b.d_vals, b.d_labels, want_post ? b.d_post : nullptr, p->s_k, &nl));
         if (want_gold)
             CK(fbn::score_cases_launch(n, p->hp.n_vars, sd, p->dp.vars, b.d_post, b.d_gold, b.d_labels, b.d_truth,
                                        p->score_case + 3 * c0, p->s_k));
@@ -408,7 +463,7 @@ static int run_impl(fbn_plan *p, int64_t n_cases, const int64_t *ev_offsets, con
         CK(cudaEventRecord(b.out_done, p->s_out));
         pend[bi].c0 = c0; pend[bi].n = n; pend[bi].active = true;
         if (stats) {
-            stats->n_launches += want_gold ? 2 : 1;
+            stats->n_launches += nl + (want_gold ? 1 : 0);
             stats->h2d_bytes += (n + 1) * 8 + ne * 8 + (want_gold ? n * ((int64_t)sd * 8 + 4) : 0);
             stats->d2h_bytes += n * 4 + (want_post_host ? n * (int64_t)sd * 8 : 0);
         }

@@ -95,7 +95,7 @@ std::vector<int> enumerate_digits(const Table &tab, const std::vector<int> &pos)
 
 }  // namespace
 
-std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P) {
+std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level) {
     std::string err;
     const int nv = t.n_vars, nc = t.n_cliques, ns = t.n_separators;
     if (nv <= 0 || nc <= 0 || ns != nc - 1) return "need n_vars > 0, n_cliques > 0 and n_separators == n_cliques - 1";
@@ -103,8 +103,10 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P) {
         return "null array in fbn_tree_desc";
     if (t.root < 0 || t.root >= nc) return "root out of range";
     if (t.query_var < 0 || t.query_var >= nv) return "query_var out of range";
-    if (team < 1 || team > 32 || (team & (team - 1))) return "team_warps must be a power of two in [1,32]";
+    if (!level && (team < 1 || team > 32 || (team & (team - 1)))) return "team_warps must be a power of two in [1,32]";
+    if (level && (team < 1 || team > 65536)) return "level mode: gang warps must be in [1,65536]";
     P = HostPlan();
+    P.level = level;
     P.n_vars = nv; P.n_cliques = nc; P.n_seps = ns; P.query_var = t.query_var; P.team = team;
     P.vars.resize(nv);
     int64_t sd = 0;
@@ -325,8 +327,9 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P) {
     // too few columns to keep `team` warps busy; then the rows are cut into chunks whose partial sums meet in shared
     // memory. Evidence-mask tables (one 32-bit word per row and per column of every clique of the phase) are built in
     // shared memory at the start of a collect phase when they fit.
-    const int kMaxPslots = 192;
-    const int kMaxMaskWords = getenv("FBN_NO_TABLES") ? 0 : 6144;
+    // fused mode keeps partial sums and mask tables in shared memory; level mode keeps partials in scratch rows
+    const int64_t kMaxPslots = level ? std::max<int64_t>(192, std::min<int64_t>(1 << 16, P.clique_entries / 8)) : 192;
+    const int kMaxMaskWords = (level || getenv("FBN_NO_TABLES")) ? 0 : 6144;
     auto emit_phase = [&](int kind, const std::vector<int> &ops) {
         Phase ph = Phase();
         ph.kind = kind;
@@ -363,7 +366,7 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P) {
             if (kind == 0) {
                 CollectOp &op = P.cops[o];
                 op.normslot = normslots++;
-                op.chunks = (int32_t)chunks; op.rows_per_chunk = (int32_t)per; op.pslot0 = pslot0; op.rot = (int32_t)(units % team);
+                op.chunks = (int32_t)chunks; op.rows_per_chunk = (int32_t)per; op.pslot0 = pslot0; op.rot = (int32_t)(level ? units : units % team);
                 if (mask_words + rows + cols <= kMaxMaskWords) {
                     op.rowmask_off = mask_words; op.colmask_off = mask_words + (int32_t)rows;
                     mask_words += (int32_t)(rows + cols);
@@ -372,7 +375,7 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P) {
                 }
             } else {
                 PullOp &op = P.pops[o];
-                op.chunks = (int32_t)chunks; op.rows_per_chunk = (int32_t)per; op.pslot0 = pslot0; op.rot = (int32_t)(units % team);
+                op.chunks = (int32_t)chunks; op.rows_per_chunk = (int32_t)per; op.pslot0 = pslot0; op.rot = (int32_t)(level ? units : units % team);
             }
             units += chunks * cols;
             P.oplist.push_back(o);
@@ -400,6 +403,7 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P) {
         ph.fin_end = (int32_t)P.fins.size();
         ph.n_normslots = normslots;
         ph.mask_words = mask_words;
+        ph.n_units = (int32_t)std::min<int64_t>(units, INT32_MAX);
         P.max_normslots = std::max(P.max_normslots, normslots);
         P.max_pslots = std::max(P.max_pslots, pslots);
         P.max_mask_words = std::max(P.max_mask_words, mask_words);
@@ -418,6 +422,15 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P) {
         for (int v = 0; v < nv; ++v)
             if (marg_avail[v] == d - 1) ops.push_back(marg_op[v]);
         if (!ops.empty()) emit_phase(1, ops);
+    }
+
+    if (level) {  // partial-sum rows and per-CTA norm rows are appended to the tile
+        P.nb_max = (team + kLevelWarps - 1) / kLevelWarps;
+        P.part_row0 = P.tile_rows;
+        P.normpart_row0 = P.part_row0 + P.max_pslots;
+        int64_t rows = (int64_t)P.normpart_row0 + (int64_t)P.max_normslots * P.nb_max;
+        if (rows > ((int64_t)1 << 30)) return "tree too large: more than 2^30 scratch rows per tile";
+        P.tile_rows = (int32_t)rows;
     }
 
     // ---- byte accounting ----

@@ -39,7 +39,7 @@ struct CollectOp {
     // work decomposition: unit u in [0, cols*chunks): col = u / chunks, rows [ (u%chunks)*rows_per_chunk, ...)
     int32_t chunks, rows_per_chunk;
     int32_t pslot0;       // chunks > 1: partial slot of (col, chunk) = pslot0 + col*chunks + chunk
-    int32_t rot;          // units of earlier ops in the phase, mod team: keeps the round-robin over warps going
+    int32_t rot;          // units of earlier ops in the phase (fused mode: mod team): keeps the round-robin over warps going
     int32_t rowmask_off;  // shared-memory word offsets of this op's per-tile evidence mask tables (rows / cols words),
     int32_t colmask_off;  //   -1: tables do not fit, fall back to per-entry mask evaluation
     int32_t pad0, pad1;
@@ -79,7 +79,7 @@ struct Phase {
     int32_t fin_begin, fin_end;
     int32_t n_normslots;
     int32_t mask_words;        // shared-memory words of evidence mask tables this phase builds
-    int32_t pad0;
+    int32_t n_units;           // warp work units of the phase (level mode: sizes the grid)
 };
 
 struct VarInfo {
@@ -103,7 +103,13 @@ struct DevPlan {
     int32_t tile_rows;   // rows per tile
     int32_t mg_row0;
     int32_t max_normslots, max_pslots, max_mask_words;
-    int32_t team;        // warps per tile
+    int32_t team;        // warps per tile (level mode: nominal gang warps the split was planned for)
+    // level mode only (one launch per phase, many CTAs per tile): split-column partials and per-CTA norm partials live in
+    // the tile's scratch rows instead of shared memory; evidence bit words live in a per-tile global array
+    int32_t part_row0;      // first of max_pslots rows
+    int32_t normpart_row0;  // first of max_normslots * nb_max rows: row (normslot * nb_max + cta)
+    int32_t nb_max;         // CTAs per tile a phase may be launched with
+    int32_t lam_words;      // sum_dims + n_vars
 };
 
 // --- host-side plan ----------------------------------------------------------------------------------------------
@@ -122,6 +128,8 @@ struct HostPlan {
     int32_t tile_rows = 0, cl_row0 = 0, mup_row0 = 0, dn_row0 = 0, inv_row0 = 0, mg_row0 = 0;
     int32_t max_normslots = 0, max_pslots = 0, max_mask_words = 0;
     int32_t team = 1;
+    bool level = false;          // level mode (see DevPlan)
+    int32_t part_row0 = 0, normpart_row0 = 0, nb_max = 1;
     int64_t n_units = 0;  // warp work units per tile (for tests / info)
     int64_t clique_entries = 0, sep_entries = 0, parent_entries = 0, marginal_entries = 0;
     // per-variable marginal source, for tests: table index (clique c, or n_cliques + s)
@@ -133,6 +141,9 @@ struct HostPlan {
 
 struct fbn_tree_desc;
 namespace fbn {
-// Validates the tree and builds the host plan for `team` warps per tile. Returns empty string on success.
-std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &out);
+constexpr int kLevelWarps = 8;  // warps per CTA of the level-mode kernels
+// Validates the tree and builds the host plan. Fused mode (level = false): `team` warps (power of two <= 32) of ONE CTA
+// work on a tile. Level mode: `team` is the nominal number of warps (any positive count, over several CTAs) that work on
+// a tile in one phase launch. Returns empty string on success.
+std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &out, bool level = false);
 }

@@ -27,6 +27,13 @@ extern "C" {
 #define FBN_ERR_CUDA 3      /* a CUDA runtime call failed */
 #define FBN_ERR_NOMEM 4
 
+/* Execution modes. FUSED: one persistent kernel, one CTA per tile of 32 cases, whole tree per launch (small / medium
+ * trees). LEVEL: one launch per tree level over all resident tiles, many CTAs per tile, big tables split across CTAs with a
+ * two-stage reduction (PIGS-/MUNIN-shape). AUTO picks by table sizes. */
+#define FBN_MODE_AUTO 0
+#define FBN_MODE_FUSED 1
+#define FBN_MODE_LEVEL 2
+
 /*
  * Flat, immutable description of a calibrated-to-be junction tree, i.e. of the reference's
  * JunctionTreeStructure + JunctionTree state right after the JunctionTree ctor (src/JunctionTree.cpp:3-46):
@@ -58,17 +65,21 @@ typedef struct fbn_plan fbn_plan; /* opaque: device-resident flattened tree + sc
 
 typedef struct fbn_plan_options {
     int32_t device;        /* CUDA device ordinal; -1 = current device */
-    int32_t team_warps;    /* warps cooperating on one 32-case tile; 0 = choose from the tree size */
+    int32_t team_warps;    /* fused mode: warps (power of two <= 32) of the one CTA that owns a 32-case tile;
+                              level mode: nominal warps per tile over all CTAs of a phase launch; 0 = choose */
     int32_t max_resident;  /* cap on resident tiles (scratch = max_resident x tile bytes); 0 = choose */
-    int32_t reserved[5];
+    int32_t mode;          /* FBN_MODE_AUTO / FBN_MODE_FUSED / FBN_MODE_LEVEL */
+    int32_t reserved[4];
 } fbn_plan_options;
 
 typedef struct fbn_plan_info {
     int32_t n_vars, n_cliques, n_separators, sum_dims;
     int32_t n_levels;            /* == reference max_level (cliques and separators alternate) */
-    int32_t team_warps;          /* chosen threads-per-tile / 32 */
+    int32_t team_warps;          /* chosen warps per tile (see fbn_plan_options) */
     int32_t resident_tiles;      /* tiles in flight (grid size) */
     int32_t n_phases;
+    int32_t mode;                /* FBN_MODE_FUSED or FBN_MODE_LEVEL */
+    int32_t launches_per_wave;   /* kernels per wave of resident tiles (1 in fused mode) */
     int64_t clique_entries;      /* sum |clique| */
     int64_t separator_entries;   /* sum |separator| */
     int64_t parent_entries;      /* sum over edges of |parent clique| */

@@ -19,7 +19,9 @@ extern "C" const char *emu_last_error() { return g_err.c_str(); }
 extern "C" int emu_run(const fbn_tree_desc *tree, int team, int64_t n_cases, const int64_t *ev_off, const int32_t *ev_vars,
                        const int32_t *ev_vals, int32_t *labels, double *post, int64_t *info /* 8 */) {
     HostPlan P;
-    g_err = build_plan(*tree, team, P);
+    const bool level = team < 0;  // negative: level mode planned for -team gang warps (fastbn_b200/csrc/level_kernels.cu)
+    if (level) team = -team;
+    g_err = build_plan(*tree, team, P, level);
     if (!g_err.empty()) return 1;
     if (info) {
         info[0] = (int64_t)P.phases.size(); info[1] = P.n_units; info[2] = (int64_t)P.fins.size();

@@ -32,6 +32,31 @@ def test_shape_matches_reference(name, team):
     assert np.array_equal(labels, g["labels"])
 
 
+@pytest.mark.parametrize("name,team,max_resident", [("hepar2", 0, 0), ("hepar2", 8, 3), ("hepar2", 200, 5), ("pigs", 0, 0), ("pigs", 64, 2),
+                                                    ("pigs", 1000, 1)])
+def test_level_mode_matches_reference(name, team, max_resident):
+    """one launch per tree level, many CTAs per tile (the MUNIN-shape path), incl. several waves of few resident tiles"""
+    t, g = _shape(name)
+    p = capi.Plan(t, device=0, team_warps=team, max_resident=max_resident, mode=capi.MODE_LEVEL)
+    assert p.info.mode == capi.MODE_LEVEL and p.info.launches_per_wave > p.info.n_phases
+    labels, post, st = p.run(g["ev_off"], g["ev_vars"], g["ev_vals"])
+    p.close()
+    assert np.nanmax(np.abs(post - g["post"])) <= TOL
+    assert np.array_equal(labels, g["labels"])
+    assert st.n_launches >= p.info.launches_per_wave
+
+
+def test_level_mode_alarm_fixtures_and_nan(alarm_tree):
+    p = capi.Plan(alarm_tree, device=0, mode=capi.MODE_LEVEL)
+    for name in ["alarm_1k_ref", "alarm_edge_ref"]:
+        g = load_golden(name)
+        labels, post, _ = p.run(g["ev_off"], g["ev_vars"], g["ev_vals"])
+        assert np.array_equal(np.isnan(post), np.isnan(g["post"]))
+        assert np.nanmax(np.abs(post - g["post"])) <= TOL
+        assert np.array_equal(labels, g["labels"])
+    p.close()
+
+
 @pytest.mark.parametrize("name,n,nev", [("hepar2", 20000, 14), ("hepar2", 5000, 35), ("pigs", 3000, 88)])
 def test_shape_batch_properties(name, n, nev):
     """many tiles: every non-evidence variable sums to 1, evidence variables are zero rows, repeated cases give repeated
