@@ -6,7 +6,8 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libfastbn_b200.so")
+# FASTBN_B200_LIB selects another build of the same library (kernel tuning experiments, tools/prof_run.py)
+LIB_PATH = os.environ.get("FASTBN_B200_LIB") or os.path.join(_HERE, "libfastbn_b200.so")
 
 # every symbol include/fastbn_b200.h declares
 ABI_SYMBOLS = ["fbn_last_error", "fbn_device_count", "fbn_plan_create", "fbn_plan_destroy", "fbn_plan_get_info",

@@ -116,7 +116,6 @@ static int pick_team(double entries) {
     if (entries <= 8192) return 1;
     if (entries <= 32768) return 4;
     if (entries <= 131072) return 8;
-    if (entries <= 1048576) return 16;
     return 32;
 }
 
@@ -191,7 +190,7 @@ extern "C" int fbn_plan_create(const fbn_tree_desc *tree, const fbn_plan_options
     d.n_phases = (int32_t)h.phases.size();
     d.n_vars = h.n_vars; d.sum_dims = h.sum_dims; d.query_var = h.query_var;
     d.tile_rows = h.tile_rows; d.mg_row0 = h.mg_row0;
-    d.max_normslots = h.max_normslots; d.max_pslots = h.max_pslots; d.max_mask_words = h.max_mask_words; d.team = h.team;
+    d.max_normslots = h.max_normslots; d.max_pslots = h.max_pslots; d.max_mask_words = h.max_mask_words; d.team = h.team; d.cb = h.cb;
     d.part_row0 = h.part_row0; d.normpart_row0 = h.normpart_row0; d.nb_max = h.nb_max; d.lam_words = h.sum_dims + h.n_vars;
 
     p->n_sms = prop.multiProcessorCount;

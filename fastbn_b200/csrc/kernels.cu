@@ -6,11 +6,10 @@
 #include <cstdint>
 #include <cuda_runtime.h>
 
+#include "ops.cuh"
 #include "plan.h"
 
 namespace fbn {
-
-__device__ __forceinline__ double *row_ptr(double *S, int32_t row) { return S + (int64_t)row * kLanes; }
 
 struct Smem {
     uint32_t *lam;    // [sum_dims]  bit l set <=> state allowed for case l of the tile
@@ -20,120 +19,73 @@ struct Smem {
     double *part;     // [max_pslots][32]
 };
 
-// Inner loop of COLLECT for one column and a row range, NC = number of children (compile-time for 0..3).
-//   C[e] = pristine[e] * mask(e) * prod_k ( child message_k[map_k(e)] / norm_k ),  returns sum_r C[r,col]
-template <int NC, bool TABLES>
-__device__ __forceinline__ double collect_rows(const DevPlan &P, const CollectOp &op, const Smem &sm, double *S, int lane, int j,
-                                               int r0, int r1, double scale) {
-    const int nchild = NC >= 0 ? NC : op.nchild, cols = op.cols;
-    uint32_t cm;
-    if (TABLES) {
-        cm = sm.mask[op.colmask_off + j];
-    } else {
-        const uint16_t *__restrict__ cl16 = P.lam16 + op.collam_off + (int64_t)j * op.ncolv;
-        cm = 0xffffffffu;
-        for (int i = 0; i < op.ncolv; ++i) cm &= sm.lam[__ldg(cl16 + i)];
-    }
-    const int32_t *__restrict__ cpart = P.idx32 + op.colpart_off + (int64_t)j * nchild;
-    int32_t cp[NC > 0 ? NC : 1];
-    if (NC > 0) {
-#pragma unroll
-        for (int k = 0; k < NC; ++k) cp[k] = __ldg(cpart + k);
-    }
-    const int32_t *__restrict__ rp = P.idx32 + op.rowpart_off + (int64_t)r0 * nchild;
-    const uint32_t *rowmask = sm.mask + op.rowmask_off;
-    const double *__restrict__ pot = P.pot + op.pot_off + j;
-    double *cl = row_ptr(S, op.cl_row + j);
-    double acc = 0.0;
-#pragma unroll 2
-    for (int r = r0; r < r1; ++r, rp += nchild) {
-        uint32_t m = cm;
-        if (TABLES) {
-            m &= rowmask[r];
-        } else {
-            const uint16_t *rl = P.lam16 + op.rowlam_off + (int64_t)r * op.nrest;
-            for (int i = 0; i < op.nrest; ++i) m &= sm.lam[__ldg(rl + i)];
-        }
-        const int64_t e = (int64_t)r * cols;
-        double v = __ldg(pot + e) * scale;
-        if (NC > 0) {
-#pragma unroll
-            for (int k = 0; k < NC; ++k) v *= *row_ptr(S, __ldg(rp + k) + cp[k]);
-        } else if (NC < 0) {
-            for (int k = 0; k < nchild; ++k) v *= *row_ptr(S, __ldg(rp + k) + __ldg(cpart + k));
-        }
-        v = ((m >> lane) & 1u) ? v : 0.0;
-        cl[e * kLanes] = v;
-        acc += v;
-    }
-    return acc;
-}
-
-// COLLECT op: all columns (and row chunks) of one clique that this warp owns.
-template <int TEAM>
+// COLLECT op: all units (column block x row chunk) of one clique that this warp owns.
+template <int TEAM, int kColBlock>
 __device__ __forceinline__ void collect_op(const DevPlan &P, const CollectOp &__restrict__ op, double *S, const Smem &sm, int lane, int warp) {
     double scale = 1.0;
     const int32_t *__restrict__ invrows = P.idx32 + op.invrow_off;
     for (int k = 0; k < op.nchild; ++k) scale *= *row_ptr(S, __ldg(invrows + k));
-    const int units = op.cols * op.chunks;
+    const int units = (op.cols + kColBlock - 1) / kColBlock * op.chunks;
     const bool tables = op.rowmask_off >= 0;
     double nacc = 0.0;
     for (int u = (warp - op.rot) & (TEAM - 1); u < units; u += TEAM) {
-        int j = u, r0 = 0, r1 = op.rows;
-        if (op.chunks > 1) {
-            j = u / op.chunks;
-            r0 = (u - j * op.chunks) * op.rows_per_chunk;
-            r1 = min(op.rows, r0 + op.rows_per_chunk);
-        }
-        double acc;
+        int j0, nc, ck, r0, r1;
+        collect_unit<kColBlock>(op, u, j0, nc, ck, r0, r1);
+        uint32_t cm[kColBlock];
+        double acc[kColBlock];
+#pragma unroll
+        for (int c = 0; c < kColBlock; ++c) acc[c] = 0.0;
         if (tables) {
-            switch (op.nchild) {
-                case 0: acc = collect_rows<0, true>(P, op, sm, S, lane, j, r0, r1, scale); break;
-                case 1: acc = collect_rows<1, true>(P, op, sm, S, lane, j, r0, r1, scale); break;
-                case 2: acc = collect_rows<2, true>(P, op, sm, S, lane, j, r0, r1, scale); break;
-                case 3: acc = collect_rows<3, true>(P, op, sm, S, lane, j, r0, r1, scale); break;
-                default: acc = collect_rows<-1, true>(P, op, sm, S, lane, j, r0, r1, scale); break;
-            }
+#pragma unroll
+            for (int c = 0; c < kColBlock; ++c) cm[c] = sm.mask[op.colmask_off + min(j0 + c, op.cols - 1)];
+            RowMaskTable rm{sm.mask + op.rowmask_off};
+            collect_block_any<kColBlock>(P, op, rm, cm, S, lane, j0, nc, r0, r1, scale, acc);
         } else {
-            acc = collect_rows<-1, false>(P, op, sm, S, lane, j, r0, r1, scale);
+#pragma unroll
+            for (int c = 0; c < kColBlock; ++c) {
+                const uint16_t *__restrict__ cl16 = P.lam16 + op.collam_off + (int64_t)min(j0 + c, op.cols - 1) * op.ncolv;
+                uint32_t m = 0xffffffffu;
+                for (int i = 0; i < op.ncolv; ++i) m &= sm.lam[__ldg(cl16 + i)];
+                cm[c] = m;
+            }
+            RowMaskLam rm{sm.lam, P.lam16 + op.rowlam_off, op.nrest, 0u};
+            collect_block_any<kColBlock>(P, op, rm, cm, S, lane, j0, nc, r0, r1, scale, acc);
         }
-        if (op.chunks > 1) sm.part[(op.pslot0 + u) * kLanes + lane] = acc;
-        else *row_ptr(S, op.mup_row + j) = acc;
-        nacc += acc;
+#pragma unroll
+        for (int c = 0; c < kColBlock; ++c)
+            if (c < nc) {
+                if (op.chunks > 1) sm.part[(op.pslot0 + (j0 + c) * op.chunks + ck) * kLanes + lane] = acc[c];
+                else *row_ptr(S, op.mup_row + j0 + c) = acc[c];
+                nacc += acc[c];
+            }
     }
     sm.normacc[(op.normslot * TEAM + warp) * kLanes + lane] = nacc;
 }
 
 // PULL op: out[q] = sum_r src[base_q + rest_r] * fac[basecol_q + restcol_r]
-template <int TEAM>
+template <int TEAM, int kColBlock>
 __device__ __forceinline__ void pull_op(const DevPlan &P, const PullOp &__restrict__ op, double *S, const Smem &sm, int lane, int warp) {
-    const int units = op.nT * op.chunks;
-    const int2 *__restrict__ tb = reinterpret_cast<const int2 *>(P.idx32 + op.tbase_off);
-    const int2 *__restrict__ tr = reinterpret_cast<const int2 *>(P.idx32 + op.trest_off);
+    const int units = (op.nT + kColBlock - 1) / kColBlock * op.chunks;
     for (int u = (warp - op.rot) & (TEAM - 1); u < units; u += TEAM) {
-        int q = u, r0 = 0, r1 = op.nR;
-        if (op.chunks > 1) {
-            q = u / op.chunks;
-            r0 = (u - q * op.chunks) * op.rows_per_chunk;
-            r1 = min(op.nR, r0 + op.rows_per_chunk);
-        }
-        const int2 b = __ldg(tb + q);
-        const double *src = row_ptr(S, op.src_row + b.x);
-        const double *fac = row_ptr(S, op.fac_row + b.y);
-        double acc = 0.0;
-#pragma unroll 4
-        for (int r = r0; r < r1; ++r) {
-            const int2 t = __ldg(tr + r);
-            acc += src[(int64_t)t.x * kLanes] * fac[(int64_t)t.y * kLanes];
-        }
-        if (op.chunks > 1) {
-            sm.part[(op.pslot0 + u) * kLanes + lane] = acc;
-        } else if (op.kind == 1) {
-            const double m = *row_ptr(S, op.mup_row + q);
-            *row_ptr(S, op.dst_row + q) = (m == 0.0) ? 0.0 : acc / m;  // TableDivision 0-guard, PotentialTable.cpp:718-734
-        } else {
-            *row_ptr(S, op.dst_row + q) = acc;
-        }
+        int q0, nq, ck, r0, r1;
+        pull_unit<kColBlock>(op, u, q0, nq, ck, r0, r1);
+        double acc[kColBlock];
+#pragma unroll
+        for (int c = 0; c < kColBlock; ++c) acc[c] = 0.0;
+        pull_block<kColBlock>(P, op, S, q0, r0, r1, acc);
+#pragma unroll
+        for (int c = 0; c < kColBlock; ++c)
+            if (c < nq) {
+                const int q = q0 + c;
+                if (op.chunks > 1) {
+                    sm.part[(op.pslot0 + q * op.chunks + ck) * kLanes + lane] = acc[c];
+                } else if (op.kind == 1) {
+                    const double m = *row_ptr(S, op.mup_row + q);
+                    *row_ptr(S, op.dst_row + q) = (m == 0.0) ? 0.0 : acc[c] / m;  // TableDivision 0-guard, PotentialTable.cpp:718-734
+                } else {
+                    *row_ptr(S, op.dst_row + q) = acc[c];
+                }
+            }
     }
 }
 
@@ -153,8 +105,8 @@ __device__ __forceinline__ void fin_item(const FinItem &F, double *S, const Smem
     *row_ptr(S, F.dst_row) = s;
 }
 
-template <int TEAM>
-__global__ void __launch_bounds__(TEAM * 32, 32 / TEAM) jt_fused_kernel(const DevPlan P, double *__restrict__ scratch, int64_t n_cases,
+template <int TEAM, int CB>
+__global__ void __launch_bounds__(TEAM * 32, (FBN_OCC / TEAM) > 0 ? (FBN_OCC / TEAM) : 1) jt_fused_kernel(const DevPlan P, double *__restrict__ scratch, int64_t n_cases,
                                                             const int64_t *__restrict__ ev_off, int64_t ev_base,
                                                             const int32_t *__restrict__ ev_vars,
                                                             const int32_t *__restrict__ ev_vals, int32_t *__restrict__ labels,
@@ -215,11 +167,11 @@ __global__ void __launch_bounds__(TEAM * 32, 32 / TEAM) jt_fused_kernel(const De
                 }
                 if (TEAM > 1) __syncthreads(); else __syncwarp();
                 for (int oi = p.op_begin; oi < p.op_end; ++oi) {
-                    collect_op<TEAM>(P, P.cops[P.oplist[oi]], S, sm, lane, warp);
+                    collect_op<TEAM, CB>(P, P.cops[P.oplist[oi]], S, sm, lane, warp);
                 }
             } else {
                 for (int oi = p.op_begin; oi < p.op_end; ++oi) {
-                    pull_op<TEAM>(P, P.pops[P.oplist[oi]], S, sm, lane, warp);
+                    pull_op<TEAM, CB>(P, P.pops[P.oplist[oi]], S, sm, lane, warp);
                 }
             }
             if (p.fin_end > p.fin_begin) {
@@ -322,9 +274,11 @@ size_t fused_smem_bytes(const DevPlan &P) {
 template <int TEAM>
 static cudaError_t prep(const DevPlan &P, int *blocks_per_sm) {
     size_t smem = fused_smem_bytes(P);
-    cudaError_t e = cudaFuncSetAttribute(jt_fused_kernel<TEAM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    constexpr int CB = TEAM == 1 ? 1 : 2;
+    if (P.cb != CB) return cudaErrorInvalidValue;
+    cudaError_t e = cudaFuncSetAttribute(jt_fused_kernel<TEAM, CB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, jt_fused_kernel<TEAM>, TEAM * 32, smem);
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, jt_fused_kernel<TEAM, CB>, TEAM * 32, smem);
 }
 
 cudaError_t fused_prepare(const DevPlan &P, int *blocks_per_sm) {
@@ -345,7 +299,7 @@ cudaError_t fused_launch(const DevPlan &P, int grid, double *scratch, int64_t n_
     if (n_tiles == 0) return cudaSuccess;
     if (grid > n_tiles) grid = (int)n_tiles;
     size_t smem = fused_smem_bytes(P);
-#define FBN_LAUNCH(T) jt_fused_kernel<T><<<grid, T * 32, smem, st>>>(P, scratch, n_cases, ev_off, ev_base, ev_vars, ev_vals, labels, post, n_tiles)
+#define FBN_LAUNCH(T) jt_fused_kernel<T, (T == 1 ? 1 : 2)><<<grid, T * 32, smem, st>>>(P, scratch, n_cases, ev_off, ev_base, ev_vars, ev_vals, labels, post, n_tiles)
     switch (P.team) {
         case 1: FBN_LAUNCH(1); break;
         case 2: FBN_LAUNCH(2); break;

@@ -12,13 +12,12 @@
 
 #include <cuda_runtime.h>
 
+#include "ops.cuh"
 #include "plan.h"
 
 namespace fbn {
 
 namespace {
-
-__device__ __forceinline__ double *lrow(double *S, int32_t row) { return S + (int64_t)row * kLanes; }
 
 // evidence -> per-tile lambda bit words in global memory (LoadDiscreteEvidence, src/JunctionTree.cpp:316-383, mask form
 // :386-457). One CTA per tile; words [0, sum_dims): bit l set <=> state allowed for case l; [sum_dims, +n_vars): observed.
@@ -43,56 +42,11 @@ __global__ void __launch_bounds__(128) lvl_evidence_kernel(const DevPlan P, uint
     }
 }
 
-// rows [r0, r1) of column j of one clique: C[e] = pristine[e] * mask(e) * prod_k message_k[map_k(e)] * scale
-// Row masks are evaluated lane-parallel: lane i builds the mask word of row rb+i, the row loop broadcasts it by shuffle.
-template <int NC>
-__device__ __forceinline__ double lvl_collect_rows(const DevPlan &P, const CollectOp &op, const uint32_t *__restrict__ lam, double *S,
-                                                   int lane, int j, int r0, int r1, double scale) {
-    const int nchild = NC >= 0 ? NC : op.nchild, cols = op.cols, nrest = op.nrest;
-    uint32_t cm = 0xffffffffu;
-    {
-        const uint16_t *__restrict__ cl16 = P.lam16 + op.collam_off + (int64_t)j * op.ncolv;
-        for (int i = 0; i < op.ncolv; ++i) cm &= __ldg(lam + __ldg(cl16 + i));
-    }
-    const int32_t *__restrict__ cpart = P.idx32 + op.colpart_off + (int64_t)j * nchild;
-    int32_t cp[NC > 0 ? NC : 1];
-    if (NC > 0) {
-#pragma unroll
-        for (int k = 0; k < NC; ++k) cp[k] = __ldg(cpart + k);
-    }
-    const double *__restrict__ pot = P.pot + op.pot_off + j;
-    double *cl = lrow(S, op.cl_row + j);
-    double acc = 0.0;
-    for (int rb = r0; rb < r1; rb += 32) {
-        uint32_t mm = 0xffffffffu;
-        if (rb + lane < r1) {
-            const uint16_t *__restrict__ rl = P.lam16 + op.rowlam_off + (int64_t)(rb + lane) * nrest;
-            for (int i = 0; i < nrest; ++i) mm &= __ldg(lam + __ldg(rl + i));
-        }
-        const int re = min(r1, rb + 32);
-        const int32_t *__restrict__ rp = P.idx32 + op.rowpart_off + (int64_t)rb * nchild;
-#pragma unroll 4
-        for (int r = rb; r < re; ++r, rp += nchild) {
-            const uint32_t m = cm & __shfl_sync(0xffffffffu, mm, r - rb);
-            const int64_t e = (int64_t)r * cols;
-            double v = __ldg(pot + e) * scale;
-            if (NC > 0) {
-#pragma unroll
-                for (int k = 0; k < NC; ++k) v *= *lrow(S, __ldg(rp + k) + cp[k]);
-            } else if (NC < 0) {
-                for (int k = 0; k < nchild; ++k) v *= *lrow(S, __ldg(rp + k) + __ldg(cpart + k));
-            }
-            v = ((m >> lane) & 1u) ? v : 0.0;
-            cl[e * kLanes] = v;
-            acc += v;
-        }
-    }
-    return acc;
-}
-
 // COLLECT phase: grid (CTAs per tile, tiles). Reference steps fused here: reset from backup, evidence masking, clique *=
-// child messages, column sums into the upstream separator (see CollectOp in plan.h).
-__global__ void __launch_bounds__(kLevelWarps * 32) lvl_collect_kernel(const DevPlan P, double *__restrict__ scratch,
+// child messages, column sums into the upstream separator (see CollectOp in plan.h). Row masks are evaluated
+// lane-parallel from the tile's lambda words (RowMaskLam, ops.cuh).
+template <int kColBlock>
+__global__ void __launch_bounds__(kLevelWarps * 32, kColBlock >= 8 ? 2 : 3) lvl_collect_kernel(const DevPlan P, double *__restrict__ scratch,
                                                                        const uint32_t *__restrict__ lamG, int phase_idx) {
     __shared__ double red[kLevelWarps][kLanes];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -104,29 +58,33 @@ __global__ void __launch_bounds__(kLevelWarps * 32) lvl_collect_kernel(const Dev
         const CollectOp &op = P.cops[P.oplist[oi]];
         double scale = 1.0;
         const int32_t *__restrict__ invrows = P.idx32 + op.invrow_off;
-        for (int k = 0; k < op.nchild; ++k) scale *= *lrow(S, __ldg(invrows + k));
-        const int units = op.cols * op.chunks;
+        for (int k = 0; k < op.nchild; ++k) scale *= *row_ptr(S, __ldg(invrows + k));
+        const int units = (op.cols + kColBlock - 1) / kColBlock * op.chunks;
         int start = (gw - op.rot % GW) % GW;
         if (start < 0) start += GW;
         double nacc = 0.0;
         for (int u = start; u < units; u += GW) {
-            int j = u, r0 = 0, r1 = op.rows;
-            if (op.chunks > 1) {
-                j = u / op.chunks;
-                r0 = (u - j * op.chunks) * op.rows_per_chunk;
-                r1 = min(op.rows, r0 + op.rows_per_chunk);
+            int j0, nc, ck, r0, r1;
+            collect_unit<kColBlock>(op, u, j0, nc, ck, r0, r1);
+            uint32_t cm[kColBlock];
+            double acc[kColBlock];
+#pragma unroll
+            for (int c = 0; c < kColBlock; ++c) {
+                acc[c] = 0.0;
+                const uint16_t *__restrict__ cl16 = P.lam16 + op.collam_off + (int64_t)min(j0 + c, op.cols - 1) * op.ncolv;
+                uint32_t m = 0xffffffffu;
+                for (int i = 0; i < op.ncolv; ++i) m &= __ldg(lam + __ldg(cl16 + i));
+                cm[c] = m;
             }
-            double acc;
-            switch (op.nchild) {
-                case 0: acc = lvl_collect_rows<0>(P, op, lam, S, lane, j, r0, r1, scale); break;
-                case 1: acc = lvl_collect_rows<1>(P, op, lam, S, lane, j, r0, r1, scale); break;
-                case 2: acc = lvl_collect_rows<2>(P, op, lam, S, lane, j, r0, r1, scale); break;
-                case 3: acc = lvl_collect_rows<3>(P, op, lam, S, lane, j, r0, r1, scale); break;
-                default: acc = lvl_collect_rows<-1>(P, op, lam, S, lane, j, r0, r1, scale); break;
-            }
-            if (op.chunks > 1) *lrow(S, P.part_row0 + op.pslot0 + u) = acc;
-            else *lrow(S, op.mup_row + j) = acc;
-            nacc += acc;
+            RowMaskLam rm{lam, P.lam16 + op.rowlam_off, op.nrest, 0u};
+            collect_block_any<kColBlock>(P, op, rm, cm, S, lane, j0, nc, r0, r1, scale, acc);
+#pragma unroll
+            for (int c = 0; c < kColBlock; ++c)
+                if (c < nc) {
+                    if (op.chunks > 1) *row_ptr(S, P.part_row0 + op.pslot0 + (j0 + c) * op.chunks + ck) = acc[c];
+                    else *row_ptr(S, op.mup_row + j0 + c) = acc[c];
+                    nacc += acc[c];
+                }
         }
         // this CTA's share of sum(clique): one partial row per (clique, CTA)
         red[warp][lane] = nacc;
@@ -135,56 +93,44 @@ __global__ void __launch_bounds__(kLevelWarps * 32) lvl_collect_kernel(const Dev
             double s = 0.0;
 #pragma unroll
             for (int w = 0; w < kLevelWarps; ++w) s += red[w][lane];
-            *lrow(S, P.normpart_row0 + op.normslot * P.nb_max + blockIdx.x) = s;
+            *row_ptr(S, P.normpart_row0 + op.normslot * P.nb_max + blockIdx.x) = s;
         }
         __syncthreads();
     }
 }
 
 // PULL phase (distribute messages and per-variable marginals): out[q] = sum_r src[base_q + rest_r] * fac[basecol_q + restcol_r]
-__global__ void __launch_bounds__(kLevelWarps * 32) lvl_pull_kernel(const DevPlan P, double *__restrict__ scratch, int phase_idx) {
+template <int kColBlock>
+__global__ void __launch_bounds__(kLevelWarps * 32, kColBlock >= 8 ? 2 : 3) lvl_pull_kernel(const DevPlan P, double *__restrict__ scratch, int phase_idx) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int gw = blockIdx.x * kLevelWarps + warp, GW = gridDim.x * kLevelWarps;
     double *S = scratch + (int64_t)blockIdx.y * P.tile_rows * kLanes + lane;
     const Phase ph = P.phases[phase_idx];
     for (int oi = ph.op_begin; oi < ph.op_end; ++oi) {
         const PullOp &op = P.pops[P.oplist[oi]];
-        const int units = op.nT * op.chunks;
-        const int2 *__restrict__ tb = reinterpret_cast<const int2 *>(P.idx32 + op.tbase_off);
-        const int2 *__restrict__ tr = reinterpret_cast<const int2 *>(P.idx32 + op.trest_off);
+        const int units = (op.nT + kColBlock - 1) / kColBlock * op.chunks;
         int start = (gw - op.rot % GW) % GW;
         if (start < 0) start += GW;
         for (int u = start; u < units; u += GW) {
-            int q = u, r0 = 0, r1 = op.nR;
-            if (op.chunks > 1) {
-                q = u / op.chunks;
-                r0 = (u - q * op.chunks) * op.rows_per_chunk;
-                r1 = min(op.nR, r0 + op.rows_per_chunk);
-            }
-            const int2 b = __ldg(tb + q);
-            const double *src = lrow(S, op.src_row + b.x);
-            const double *fac = lrow(S, op.fac_row + b.y);
-            double acc0 = 0.0, acc1 = 0.0;
-            int r = r0;
-#pragma unroll 2
-            for (; r + 1 < r1; r += 2) {
-                const int2 t0 = __ldg(tr + r), t1 = __ldg(tr + r + 1);
-                acc0 += src[(int64_t)t0.x * kLanes] * fac[(int64_t)t0.y * kLanes];
-                acc1 += src[(int64_t)t1.x * kLanes] * fac[(int64_t)t1.y * kLanes];
-            }
-            if (r < r1) {
-                const int2 t0 = __ldg(tr + r);
-                acc0 += src[(int64_t)t0.x * kLanes] * fac[(int64_t)t0.y * kLanes];
-            }
-            const double acc = acc0 + acc1;
-            if (op.chunks > 1) {
-                *lrow(S, P.part_row0 + op.pslot0 + u) = acc;
-            } else if (op.kind == 1) {
-                const double m = *lrow(S, op.mup_row + q);
-                *lrow(S, op.dst_row + q) = (m == 0.0) ? 0.0 : acc / m;  // TableDivision 0-guard, PotentialTable.cpp:718-734
-            } else {
-                *lrow(S, op.dst_row + q) = acc;
-            }
+            int q0, nq, ck, r0, r1;
+            pull_unit<kColBlock>(op, u, q0, nq, ck, r0, r1);
+            double acc[kColBlock];
+#pragma unroll
+            for (int c = 0; c < kColBlock; ++c) acc[c] = 0.0;
+            pull_block<kColBlock>(P, op, S, q0, r0, r1, acc);
+#pragma unroll
+            for (int c = 0; c < kColBlock; ++c)
+                if (c < nq) {
+                    const int q = q0 + c;
+                    if (op.chunks > 1) {
+                        *row_ptr(S, P.part_row0 + op.pslot0 + q * op.chunks + ck) = acc[c];
+                    } else if (op.kind == 1) {
+                        const double m = *row_ptr(S, op.mup_row + q);
+                        *row_ptr(S, op.dst_row + q) = (m == 0.0) ? 0.0 : acc[c] / m;  // TableDivision 0-guard, PotentialTable.cpp:718-734
+                    } else {
+                        *row_ptr(S, op.dst_row + q) = acc[c];
+                    }
+                }
         }
     }
 }
@@ -199,18 +145,18 @@ __global__ void __launch_bounds__(kLevelWarps * 32) lvl_fin_kernel(const DevPlan
     const FinItem F = P.fins[f];
     double s = 0.0;
     if (F.type == FIN_NORM) {
-        const double *np = lrow(S, P.normpart_row0 + F.slot0 * P.nb_max);
+        const double *np = row_ptr(S, P.normpart_row0 + F.slot0 * P.nb_max);
         for (int b = 0; b < nb; ++b) s += np[(int64_t)b * kLanes];
-        *lrow(S, F.dst_row) = 1.0 / s;
+        *row_ptr(S, F.dst_row) = 1.0 / s;
         return;
     }
-    const double *pp = lrow(S, P.part_row0 + F.slot0);
+    const double *pp = row_ptr(S, P.part_row0 + F.slot0);
     for (int i = 0; i < F.nslots; ++i) s += pp[(int64_t)i * kLanes];
     if (F.type == FIN_D) {
-        const double m = *lrow(S, F.aux_row);
+        const double m = *row_ptr(S, F.aux_row);
         s = (m == 0.0) ? 0.0 : s / m;
     }
-    *lrow(S, F.dst_row) = s;
+    *row_ptr(S, F.dst_row) = s;
 }
 
 // posteriors + label (GetProbabilitiesOneNode src/JunctionTree.cpp:1392-1454, Inference::ArgMax src/Inference.cpp:92-102)
@@ -226,7 +172,7 @@ __global__ void __launch_bounds__(kLevelWarps * 32) lvl_output_kernel(const DevP
     const bool valid = cs < n_cases;
     const VarInfo vi = P.vars[v];
     const bool observed = (lam[P.sum_dims + v] >> lane) & 1u;
-    const double *mg = lrow(S, P.mg_row0 + vi.off);
+    const double *mg = row_ptr(S, P.mg_row0 + vi.off);
     double sum = 0.0;
     for (int d = 0; d < vi.dim; ++d) sum += mg[d * kLanes];
     double best = 0.0;
@@ -245,6 +191,7 @@ __global__ void __launch_bounds__(kLevelWarps * 32) lvl_output_kernel(const DevP
 cudaError_t level_launch(const DevPlan &P, const std::vector<Phase> &phases, int resident, double *scratch, uint32_t *lamG,
                          int64_t n_cases, const int64_t *ev_off, int64_t ev_base, const int32_t *ev_vars, const int32_t *ev_vals,
                          int32_t *labels, double *post, cudaStream_t st, int64_t *n_launch) {
+    if (P.cb != 4 && P.cb != 8) return cudaErrorInvalidValue;
     const int64_t n_tiles = (n_cases + kLanes - 1) / kLanes;
     int64_t launches = 0;
     for (int64_t tile0 = 0; tile0 < n_tiles; tile0 += resident) {
@@ -257,8 +204,13 @@ cudaError_t level_launch(const DevPlan &P, const std::vector<Phase> &phases, int
             int nb = (ph.n_units + 2 * kLevelWarps - 1) / (2 * kLevelWarps);
             nb = std::max(1, std::min(nb, P.nb_max));
             dim3 grid((unsigned)nb, wt);
-            if (ph.kind == 0) lvl_collect_kernel<<<grid, kLevelWarps * 32, 0, st>>>(P, scratch, lamG, (int)pi);
-            else lvl_pull_kernel<<<grid, kLevelWarps * 32, 0, st>>>(P, scratch, (int)pi);
+            if (P.cb == 8) {
+                if (ph.kind == 0) lvl_collect_kernel<8><<<grid, kLevelWarps * 32, 0, st>>>(P, scratch, lamG, (int)pi);
+                else lvl_pull_kernel<8><<<grid, kLevelWarps * 32, 0, st>>>(P, scratch, (int)pi);
+            } else {
+                if (ph.kind == 0) lvl_collect_kernel<4><<<grid, kLevelWarps * 32, 0, st>>>(P, scratch, lamG, (int)pi);
+                else lvl_pull_kernel<4><<<grid, kLevelWarps * 32, 0, st>>>(P, scratch, (int)pi);
+            }
             ++launches;
             const int nfin = ph.fin_end - ph.fin_begin;
             if (nfin > 0) {

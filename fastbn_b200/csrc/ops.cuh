@@ -1,0 +1,160 @@
+// Device-side building blocks shared by the fused kernel (kernels.cu) and the level kernels (level_kernels.cu).
+// Thread mapping everywhere: lane = test case inside a 32-case tile; a warp owns a UNIT = a block of up to CB
+// adjacent columns (collect) / target entries (pull) of one table times a range of rows. Register blocking over the
+// columns gives CB independent 256-byte row loads per index load (memory-level parallelism) and amortises the
+// warp-uniform index loads; all scratch accesses are coalesced 256-byte rows.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "plan.h"
+
+namespace fbn {
+
+__device__ __forceinline__ double *row_ptr(double *S, int32_t row) { return S + (int64_t)row * kLanes; }
+
+// ---- row evidence masks -----------------------------------------------------------------------------------------
+// mask word of clique row r: bit l set <=> case l of the tile allows that row (AND of the lambda words of the row's digits)
+struct RowMaskTable {  // fused mode, tables built once per phase in shared memory
+    static constexpr int kSpan = 1 << 30;  // rows per begin(): the whole range
+    const uint32_t *tab;
+    __device__ __forceinline__ void begin(int, int, int) {}
+    __device__ __forceinline__ uint32_t get(int r, int) const { return tab[r]; }
+};
+struct RowMaskLam {  // evaluated on the fly, lane-parallel: lane i builds the word of row rb+i, get() broadcasts it
+    static constexpr int kSpan = 32;
+    const uint32_t *lam;       // lambda words of the tile (shared or global memory)
+    const uint16_t *rowlam;    // op's rows x nrest lambda indices
+    int nrest;
+    uint32_t mine;
+    __device__ __forceinline__ void begin(int rb, int r1, int lane) {
+        mine = 0xffffffffu;
+        if (rb + lane < r1) {
+            const uint16_t *__restrict__ rl = rowlam + (int64_t)(rb + lane) * nrest;
+            for (int i = 0; i < nrest; ++i) mine &= lam[__ldg(rl + i)];
+        }
+    }
+    __device__ __forceinline__ uint32_t get(int r, int rb) const { return __shfl_sync(0xffffffffu, mine, r - rb); }
+};
+
+// ---- COLLECT -----------------------------------------------------------------------------------------------------
+// Columns [j0, j0+nc) (nc <= CB), rows [r0, r1) of one clique:
+//   C[e] = pristine[e] * scale * mask(e) * prod_k message_k[rowpart_k(r) + colpart_k(j)];  acc[c] += C[r, j0+c]
+// NC = number of children (compile-time 0..3, -1 = generic). Loads of columns beyond nc are clamped to the last column
+// (valid addresses, results discarded), so the inner loop has no divergent control flow.
+template <int NC, int CB, class RowMask>
+__device__ __forceinline__ void collect_block(const DevPlan &P, const CollectOp &op, RowMask &rmask, const uint32_t (&cm)[CB], double *S,
+                                              int lane, int j0, int nc, int r0, int r1, double scale, double (&acc)[CB]) {
+    const int nchild = NC >= 0 ? NC : op.nchild, cols = op.cols;
+    int jc[CB];
+#pragma unroll
+    for (int c = 0; c < CB; ++c) jc[c] = min(j0 + c, cols - 1);
+    int32_t cp[NC > 0 ? NC : 1][CB];
+    const int32_t *__restrict__ colpart = P.idx32 + op.colpart_off;
+    if (NC > 0) {
+#pragma unroll
+        for (int k = 0; k < NC; ++k)
+#pragma unroll
+            for (int c = 0; c < CB; ++c) cp[k][c] = __ldg(colpart + (int64_t)jc[c] * NC + k);
+    }
+    const double *__restrict__ pot = P.pot + op.pot_off;
+    double *cl = row_ptr(S, op.cl_row);
+    const int32_t *__restrict__ rowpart = P.idx32 + op.rowpart_off;
+    for (int rb = r0; rb < r1; rb += RowMask::kSpan) {
+        rmask.begin(rb, r1, lane);
+        const int re = RowMask::kSpan > 32 ? r1 : min(r1, rb + RowMask::kSpan);
+#pragma unroll(CB >= 4 ? 1 : 2)
+        for (int r = rb; r < re; ++r) {
+            const uint32_t mr = rmask.get(r, rb);
+            const int64_t e = (int64_t)r * cols;
+            double v[CB];
+#pragma unroll
+            for (int c = 0; c < CB; ++c) v[c] = __ldg(pot + e + jc[c]) * scale;
+            if (NC > 0) {
+                int32_t rp[NC > 0 ? NC : 1];
+#pragma unroll
+                for (int k = 0; k < NC; ++k) rp[k] = __ldg(rowpart + (int64_t)r * NC + k);
+#pragma unroll
+                for (int k = 0; k < NC; ++k)
+#pragma unroll
+                    for (int c = 0; c < CB; ++c) v[c] *= *row_ptr(S, rp[k] + cp[k][c]);
+            } else if (NC < 0) {
+                for (int k = 0; k < nchild; ++k) {
+                    const int32_t rpk = __ldg(rowpart + (int64_t)r * nchild + k);
+#pragma unroll
+                    for (int c = 0; c < CB; ++c) v[c] *= *row_ptr(S, rpk + __ldg(colpart + (int64_t)jc[c] * nchild + k));
+                }
+            }
+#pragma unroll
+            for (int c = 0; c < CB; ++c) {
+                const double w = (((mr & cm[c]) >> lane) & 1u) ? v[c] : 0.0;
+                if (c < nc) cl[(e + j0 + c) * kLanes] = w;
+                acc[c] += w;
+            }
+        }
+    }
+}
+
+template <int CB, class RowMask>
+__device__ __forceinline__ void collect_block_any(const DevPlan &P, const CollectOp &op, RowMask &rmask, const uint32_t (&cm)[CB],
+                                                  double *S, int lane, int j0, int nc, int r0, int r1, double scale, double (&acc)[CB]) {
+    switch (op.nchild) {
+        case 0: collect_block<0, CB>(P, op, rmask, cm, S, lane, j0, nc, r0, r1, scale, acc); break;
+        case 1: collect_block<1, CB>(P, op, rmask, cm, S, lane, j0, nc, r0, r1, scale, acc); break;
+        case 2: collect_block<2, CB>(P, op, rmask, cm, S, lane, j0, nc, r0, r1, scale, acc); break;
+        case 3: collect_block<3, CB>(P, op, rmask, cm, S, lane, j0, nc, r0, r1, scale, acc); break;
+        default: collect_block<-1, CB>(P, op, rmask, cm, S, lane, j0, nc, r0, r1, scale, acc); break;
+    }
+}
+
+// unit u of a collect op -> column block + row range
+template <int CB>
+__device__ __forceinline__ void collect_unit(const CollectOp &op, int u, int &j0, int &nc, int &ck, int &r0, int &r1) {
+    int jb = u;
+    ck = 0; r0 = 0; r1 = op.rows;
+    if (op.chunks > 1) {
+        jb = u / op.chunks;
+        ck = u - jb * op.chunks;
+        r0 = ck * op.rows_per_chunk;
+        r1 = min(op.rows, r0 + op.rows_per_chunk);
+    }
+    j0 = jb * CB;
+    nc = min(CB, op.cols - j0);
+}
+
+// ---- PULL --------------------------------------------------------------------------------------------------------
+// targets [q0, q0+nq) (nq <= QB), rest entries [r0, r1):  acc[q] += src[tbase[q].x + trest[r].x] * fac[tbase[q].y + trest[r].y]
+template <int QB>
+__device__ __forceinline__ void pull_block(const DevPlan &P, const PullOp &op, double *S, int q0, int r0, int r1, double (&acc)[QB]) {
+    const int2 *__restrict__ tb = reinterpret_cast<const int2 *>(P.idx32 + op.tbase_off);
+    const int2 *__restrict__ tr = reinterpret_cast<const int2 *>(P.idx32 + op.trest_off);
+    const double *src[QB], *fac[QB];
+#pragma unroll
+    for (int q = 0; q < QB; ++q) {
+        const int2 b = __ldg(tb + min(q0 + q, op.nT - 1));
+        src[q] = row_ptr(S, op.src_row + b.x);
+        fac[q] = row_ptr(S, op.fac_row + b.y);
+    }
+#pragma unroll(QB >= 4 ? 2 : 4)
+    for (int r = r0; r < r1; ++r) {
+        const int2 t = __ldg(tr + r);
+#pragma unroll
+        for (int q = 0; q < QB; ++q) acc[q] += src[q][(int64_t)t.x * kLanes] * fac[q][(int64_t)t.y * kLanes];
+    }
+}
+
+template <int CB>
+__device__ __forceinline__ void pull_unit(const PullOp &op, int u, int &q0, int &nq, int &ck, int &r0, int &r1) {
+    int qb = u;
+    ck = 0; r0 = 0; r1 = op.nR;
+    if (op.chunks > 1) {
+        qb = u / op.chunks;
+        ck = u - qb * op.chunks;
+        r0 = ck * op.rows_per_chunk;
+        r1 = min(op.nR, r0 + op.rows_per_chunk);
+    }
+    q0 = qb * CB;
+    nq = min(CB, op.nT - q0);
+}
+
+}  // namespace fbn

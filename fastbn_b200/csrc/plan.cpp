@@ -107,6 +107,21 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
     if (level && (team < 1 || team > 65536)) return "level mode: gang warps must be in [1,65536]";
     P = HostPlan();
     P.level = level;
+    {
+        int64_t max_table = 0, pos = 0;
+        for (int i = 0; i < nc; ++i) {
+            int64_t sz = 1;
+            for (int k = 0; k < t.table_nvars[i]; ++k) sz = std::min<int64_t>((int64_t)1 << 40, sz * std::max(1, t.var_dims[t.table_vars[pos + k]]));
+            pos += t.table_nvars[i];
+            max_table = std::max(max_table, sz);
+        }
+        P.cb = level ? (max_table >= ((int64_t)1 << 20) ? 8 : 4) : (team == 1 ? 1 : 2);
+        if (const char *e = getenv("FBN_CB")) {
+            int v = atoi(e);
+            if (level ? (v == 4 || v == 8) : (v == 1 || v == 2)) P.cb = v;
+        }
+    }
+    const int64_t kColBlock = P.cb;
     P.n_vars = nv; P.n_cliques = nc; P.n_seps = ns; P.query_var = t.query_var; P.team = team;
     P.vars.resize(nv);
     int64_t sd = 0;
@@ -323,9 +338,9 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
     }
 
     // ---- phases, warp work units, split-column partial slots ----
-    // A column (collect) / target entry (pull) is one unit of warp work unless its row range is long and the phase has
-    // too few columns to keep `team` warps busy; then the rows are cut into chunks whose partial sums meet in shared
-    // memory. Evidence-mask tables (one 32-bit word per row and per column of every clique of the phase) are built in
+    // A block of cb adjacent columns (collect) / target entries (pull) is one unit of warp work unless its row range
+    // is long and the phase has too few column blocks to keep `team` warps busy; then the rows are cut into chunks whose
+    // partial sums meet in shared memory (fused mode) or scratch rows (level mode). Evidence-mask tables (one 32-bit word per row and per column of every clique of the phase) are built in
     // shared memory at the start of a collect phase when they fit.
     // fused mode keeps partial sums and mask tables in shared memory; level mode keeps partials in scratch rows
     const int64_t kMaxPslots = level ? std::max<int64_t>(192, std::min<int64_t>(1 << 16, P.clique_entries / 8)) : 192;
@@ -337,9 +352,10 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
         ph.fin_begin = (int32_t)P.fins.size();
         int64_t work = 0;
         for (int o : ops) work += kind == 0 ? (int64_t)P.cops[o].rows * P.cops[o].cols : (int64_t)P.pops[o].nT * P.pops[o].nR;
-        int64_t target = std::max<int64_t>(32, work / (4 * (int64_t)team));
-        auto chunks_of = [&](int64_t rows, int64_t tgt) {
+        int64_t target = std::max<int64_t>(128, work / (4 * (int64_t)team));  // table entries per unit
+        auto chunks_of = [&](int64_t rows, int64_t cols, int64_t tgt) {
             if (team == 1) return (int64_t)1;
+            tgt = std::max<int64_t>(8, tgt / std::min<int64_t>(cols, kColBlock));  // rows per unit
             int64_t ch = std::min<int64_t>(rows, (rows + tgt - 1) / tgt);
             int64_t per = (rows + ch - 1) / ch;
             return (rows + per - 1) / per;
@@ -348,7 +364,7 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
             int64_t pslots = 0;
             for (int o : ops) {
                 int64_t rows = kind == 0 ? P.cops[o].rows : P.pops[o].nR, cols = kind == 0 ? P.cops[o].cols : P.pops[o].nT;
-                int64_t ch = chunks_of(rows, target);
+                int64_t ch = chunks_of(rows, cols, target);
                 if (ch > 1) pslots += ch * cols;
             }
             if (pslots <= kMaxPslots) break;
@@ -358,7 +374,7 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
         int64_t units = 0;
         for (int o : ops) {
             int64_t rows = kind == 0 ? P.cops[o].rows : P.pops[o].nR, cols = kind == 0 ? P.cops[o].cols : P.pops[o].nT;
-            int64_t chunks = chunks_of(rows, target);
+            int64_t chunks = chunks_of(rows, cols, target);
             if (chunks > 1 && pslots + chunks * cols > kMaxPslots) chunks = 1;
             int64_t per = (rows + chunks - 1) / chunks;
             int32_t pslot0 = chunks > 1 ? pslots : -1;
@@ -377,7 +393,7 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
                 PullOp &op = P.pops[o];
                 op.chunks = (int32_t)chunks; op.rows_per_chunk = (int32_t)per; op.pslot0 = pslot0; op.rot = (int32_t)(level ? units : units % team);
             }
-            units += chunks * cols;
+            units += chunks * ((cols + kColBlock - 1) / kColBlock);
             P.oplist.push_back(o);
             if (chunks > 1)
                 for (int64_t j = 0; j < cols; ++j) {

@@ -15,7 +15,15 @@
 
 namespace fbn {
 
-constexpr int kLanes = 32;  // cases per tile == warp width
+constexpr int kLanes = 32;     // cases per tile == warp width
+#ifndef FBN_OCC
+#define FBN_OCC 32   // fused kernel: resident warps per SM the register allocation is bounded for
+#endif
+// Column blocking: adjacent columns (collect) / target entries (pull) a warp processes together (register blocking:
+// cb independent row loads per index load). Chosen per plan from measurements on B200 (profiles/):
+//   fused, 1 warp per tile (ALARM-size)  cb 1      fused, >= 2 warps per tile  cb 2
+//   level, largest table < 2^20 entries  cb 4      level, larger (MUNIN-shape) cb 8
+constexpr int kMaxColBlock = 8;
 
 // --- device-visible op descriptors -------------------------------------------------------------------------------
 // COLLECT of clique C (fuses reference steps: reset from backup [JunctionTree.cpp:302-311], evidence masking
@@ -36,7 +44,8 @@ struct CollectOp {
     int32_t nrest, ncolv;
     int32_t nchild;
     int32_t normslot;     // index of this op among the collect ops of its phase
-    // work decomposition: unit u in [0, cols*chunks): col = u / chunks, rows [ (u%chunks)*rows_per_chunk, ...)
+    // work decomposition: unit u in [0, ceil(cols/cb)*chunks): column block b = u / chunks (columns [cb*b, cb*b+cb)),
+    // rows [(u % chunks)*rows_per_chunk, ...)
     int32_t chunks, rows_per_chunk;
     int32_t pslot0;       // chunks > 1: partial slot of (col, chunk) = pslot0 + col*chunks + chunk
     int32_t rot;          // units of earlier ops in the phase (fused mode: mod team): keeps the round-robin over warps going
@@ -58,7 +67,7 @@ struct PullOp {
     int32_t dst_row;
     int32_t nT, nR;
     int32_t kind;
-    int32_t chunks, rows_per_chunk, pslot0, rot;  // as in CollectOp (cols = nT, rows = nR)
+    int32_t chunks, rows_per_chunk, pslot0, rot;  // as in CollectOp (cols = nT, rows = nR): blocks of cb targets
     int32_t pad;
 };
 
@@ -104,6 +113,7 @@ struct DevPlan {
     int32_t mg_row0;
     int32_t max_normslots, max_pslots, max_mask_words;
     int32_t team;        // warps per tile (level mode: nominal gang warps the split was planned for)
+    int32_t cb;          // columns / targets per unit the plan was made for
     // level mode only (one launch per phase, many CTAs per tile): split-column partials and per-CTA norm partials live in
     // the tile's scratch rows instead of shared memory; evidence bit words live in a per-tile global array
     int32_t part_row0;      // first of max_pslots rows
@@ -127,7 +137,7 @@ struct HostPlan {
     int32_t n_levels = 0;
     int32_t tile_rows = 0, cl_row0 = 0, mup_row0 = 0, dn_row0 = 0, inv_row0 = 0, mg_row0 = 0;
     int32_t max_normslots = 0, max_pslots = 0, max_mask_words = 0;
-    int32_t team = 1;
+    int32_t team = 1, cb = 1;
     bool level = false;          // level mode (see DevPlan)
     int32_t part_row0 = 0, normpart_row0 = 0, nb_max = 1;
     int64_t n_units = 0;  // warp work units per tile (for tests / info)

@@ -27,6 +27,7 @@ extern "C" int emu_run(const fbn_tree_desc *tree, int team, int64_t n_cases, con
         info[0] = (int64_t)P.phases.size(); info[1] = P.n_units; info[2] = (int64_t)P.fins.size();
         info[3] = P.max_pslots; info[4] = P.max_normslots; info[5] = P.tile_rows; info[6] = P.n_levels; info[7] = P.parent_entries;
     }
+    const int kColBlock = P.cb;
     std::vector<double> S((size_t)P.tile_rows);
     std::vector<char> lam((size_t)P.sum_dims), obs((size_t)P.n_vars);
     std::vector<double> normacc((size_t)std::max(1, P.max_normslots) * team), part((size_t)std::max(1, P.max_pslots));
@@ -45,13 +46,19 @@ extern "C" int emu_run(const fbn_tree_desc *tree, int team, int64_t n_cases, con
             if (ph.kind == 0) std::fill(normacc.begin(), normacc.end(), 0.0);
             for (int oi = ph.op_begin; oi < ph.op_end; ++oi) {
                 const int o = P.oplist[oi];
-                const int units = ph.kind == 0 ? P.cops[o].cols * P.cops[o].chunks : P.pops[o].nT * P.pops[o].chunks;
-                for (int u = 0; u < units; ++u) {
+                const int ncolsop = ph.kind == 0 ? P.cops[o].cols : P.pops[o].nT;
+                const int chunks = ph.kind == 0 ? P.cops[o].chunks : P.pops[o].chunks;
+                const int units = (ncolsop + kColBlock - 1) / kColBlock * chunks;
+                for (int u = 0; u < units; ++u)
+                  for (int cc = 0; cc < kColBlock; ++cc) {  // the columns / targets of the unit's block
+                    const int jb = u / chunks, ck = u - jb * chunks;
+                    if (jb * kColBlock + cc >= ncolsop) break;
                     if (ph.kind == 0) {
                         const CollectOp &op = P.cops[o];
                         const int warp = (op.rot + u) % team;
-                        int j = u, r0 = 0, r1 = op.rows;
-                        if (op.chunks > 1) { j = u / op.chunks; r0 = (u - j * op.chunks) * op.rows_per_chunk; r1 = std::min(op.rows, r0 + op.rows_per_chunk); }
+                        const int j = jb * kColBlock + cc;
+                        int r0 = 0, r1 = op.rows;
+                        if (op.chunks > 1) { r0 = ck * op.rows_per_chunk; r1 = std::min(op.rows, r0 + op.rows_per_chunk); }
                         bool cm = true;
                         for (int i = 0; i < op.ncolv; ++i) cm = cm && lam[P.lam16[op.collam_off + (int64_t)j * op.ncolv + i]];
                         double scale = 1.0;
@@ -68,18 +75,19 @@ extern "C" int emu_run(const fbn_tree_desc *tree, int team, int64_t n_cases, con
                             S[op.cl_row + e] = v;
                             acc += v;
                         }
-                        if (op.chunks > 1) part[op.pslot0 + u] = acc;
+                        if (op.chunks > 1) part[op.pslot0 + j * op.chunks + ck] = acc;
                         else S[op.mup_row + j] = acc;
                         normacc[op.normslot * team + warp] += acc;
                     } else {
                         const PullOp &op = P.pops[o];
-                        int q = u, r0 = 0, r1 = op.nR;
-                        if (op.chunks > 1) { q = u / op.chunks; r0 = (u - q * op.chunks) * op.rows_per_chunk; r1 = std::min(op.nR, r0 + op.rows_per_chunk); }
+                        const int q = jb * kColBlock + cc;
+                        int r0 = 0, r1 = op.nR;
+                        if (op.chunks > 1) { r0 = ck * op.rows_per_chunk; r1 = std::min(op.nR, r0 + op.rows_per_chunk); }
                         const int32_t bx = P.idx32[op.tbase_off + 2 * q], by = P.idx32[op.tbase_off + 2 * q + 1];
                         double acc = 0.0;
                         for (int r = r0; r < r1; ++r)
                             acc += S[op.src_row + bx + P.idx32[op.trest_off + 2 * r]] * S[op.fac_row + by + P.idx32[op.trest_off + 2 * r + 1]];
-                        if (op.chunks > 1) part[op.pslot0 + u] = acc;
+                        if (op.chunks > 1) part[op.pslot0 + q * op.chunks + ck] = acc;
                         else if (op.kind == 1) { double m = S[op.mup_row + q]; S[op.dst_row + q] = m == 0.0 ? 0.0 : acc / m; }
                         else S[op.dst_row + q] = acc;
                     }

@@ -25,6 +25,19 @@ def test_plan_reproduces_reference(alarm_tree, team, name):
     assert info[7] == 1517  # sum over edges of |parent clique|
 
 
+@pytest.mark.parametrize("gang", [8, 24, 504])
+def test_level_mode_plan_reproduces_reference(alarm_tree, gang):
+    """level mode (one launch per tree level, `gang` warps over several CTAs per tile): negative team selects it in the emulator"""
+    g = load_golden("alarm_1k_ref")
+    post, lab, info = emu.run(alarm_tree, -gang, g["ev_off"][:201], g["ev_vars"][:g["ev_off"][200]], g["ev_vals"][:g["ev_off"][200]])
+    assert np.nanmax(np.abs(post - g["post"][:200])) <= 1e-9
+    assert np.array_equal(lab, g["labels"][:200])
+    g = load_golden("alarm_edge_ref")
+    post, lab, _ = emu.run(alarm_tree, -gang, g["ev_off"], g["ev_vars"], g["ev_vals"])
+    assert np.array_equal(np.isnan(post), np.isnan(g["post"]))
+    assert np.nanmax(np.abs(post - g["post"])) <= 1e-9
+
+
 def test_planner_rejects_malformed_trees(alarm_tree):
     z = np.zeros(1, np.int64)
     e = np.zeros(0, np.int32)
