@@ -180,6 +180,7 @@ def main():
     ap.add_argument("--workload", default="alarm", choices=sorted(WORKLOADS))
     ap.add_argument("--cases", type=int, default=0, help="cases per GPU per step (default: the workload's)")
     ap.add_argument("--team", type=int, default=0)
+    ap.add_argument("--mode", type=int, default=0, help="0 auto, 1 fused kernel, 2 level kernels")
     ap.add_argument("--ref-cases-per-core", type=int, default=0, help="CPU sample per core (default: the workload's, ~10-20 s)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--e2e-steps", type=int, default=0, help="timed e2e steps (default: min(steps, 5))")
@@ -203,10 +204,15 @@ def main():
 
     w = WORKLOADS[args.workload]
     tree = load_tree(args.workload)
-    n = args.cases or w["cases"]
-    plan = capi.Plan(tree, device=local, team_warps=args.team)
+    plan = capi.Plan(tree, device=local, team_warps=args.team, mode=args.mode)
     info = plan.info
     sd = info.sum_dims
+    n = args.cases or w["cases"]
+    if not args.cases and args.workload != "alarm":
+        wave = info.resident_tiles * 32  # whole waves of resident tiles (the ALARM config is fixed at 1M cases)
+        n = max(wave, n // wave * wave)
+    waves = -(-((n + 31) // 32) // info.resident_tiles)
+    launches_per_step = info.launches_per_wave * waves if info.mode == capi.MODE_LEVEL else 1
     # every rank gets its own slice of the synthetic case stream (weak scaling, no data-path collective)
     off_h, ev_h, ew_h = synth.uniform_evidence(tree["var_dims"], n, w["n_evidence"], seed=20260101 + rank)
 
@@ -245,7 +251,7 @@ def main():
     t_all1.record()
     barrier()
     total_ms = t_all0.elapsed_time(t_all1)
-    kern_ms = float(np.mean([a.elapsed_time(b) for a, b in zip(e0, e1)]))  # one kernel launch per step
+    kern_ms = float(np.mean([a.elapsed_time(b) for a, b in zip(e0, e1)]))  # all kernel launches of one step
     if world > 1:
         t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -291,20 +297,29 @@ def main():
         else:
             peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
         achieved = info.alg_bytes_per_case * n / (kern_ms * 1e-3) / 1e9
+        traffic = None
+        tpath = os.path.join(ROOT, "profiles", "traffic.json")  # ncu dram__bytes_read+write per case, by workload
+        if os.path.exists(tpath):
+            tj = json.load(open(tpath)).get(args.workload)
+            if tj:
+                traffic = tj["dram_bytes_per_case"] * n
         line = {
             "metric": "test cases/sec, exact JT inference", "value": value, "unit": "cases/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": w["desc"], "cases_per_gpu": n, "n_evidence": w["n_evidence"], "team_warps": info.team_warps,
+                       "mode": "level" if info.mode == capi.MODE_LEVEL else "fused", "launches_per_step": launches_per_step,
                        "resident_tiles": info.resident_tiles, "l2": "per-step working set (evidence + posteriors) %.0f MB > 126 MB L2"
                        % ((off_h.nbytes + ev_h.nbytes + ew_h.nbytes + n * sd * 8 + n * 4) / 1e6),
                        "labels_e2e_equal_device": same, "labelled_cases": int(counts[0].item()), "total_cases": int(counts[1].item())},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_source": peak_src, "alg_bytes_per_case": info.alg_bytes_per_case,
-                         "kernel_bytes_per_case": info.kernel_bytes_per_case, "kernel_ms": kern_ms, "kernel": "jt_fused_kernel"},
+                         "traffic": traffic, "peak_source": peak_src,
+                         "moved_gbs": info.kernel_bytes_per_case * n / (kern_ms * 1e-3) / 1e9, "alg_bytes_per_case": info.alg_bytes_per_case,
+                         "kernel_bytes_per_case": info.kernel_bytes_per_case, "kernel_ms": kern_ms,
+                         "kernel": "jt_fused_kernel" if info.mode == capi.MODE_FUSED else "lvl_collect_kernel+lvl_pull_kernel (all launches of a step)"},
             "e2e": {"value": e2e_value, "unit": "cases/s", "h2d_bytes_per_step": int(st.h2d_bytes), "d2h_bytes_per_step": int(st.d2h_bytes),
                     "steps": e2e_steps, "launches_per_step": int(st.n_launches)},
-            "gpu_launches": args.steps * 1,
+            "gpu_launches": args.steps * launches_per_step,
             "clocks": sampler.summary(),
         }
         if world == 1 and not args.no_cpu_baseline:

@@ -86,6 +86,14 @@ extern "C" int fbn_host_model_evaluate(fbn_host_model *m, const char *pt_path, c
     return FBN_OK;
 }
 
+extern "C" int fbn_host_model_load_golden(fbn_host_model *m, const char *pt_path, double *golden_out) {
+    if (!m || !pt_path || !golden_out) return FBN_ERR_INVALID;
+    CoutMute mute(m->jt->quiet);
+    m->jt->LoadGroundTruthProbabilityTable(pt_path);
+    memcpy(golden_out, m->jt->ground_truth_probability_tables.data(), sizeof(double) * m->jt->ground_truth_probability_tables.size());
+    return FBN_OK;
+}
+
 extern "C" int fbn_host_model_write_pt(fbn_host_model *m, const char *path) {
     if (!m || !path) return FBN_ERR_INVALID;
     m->jt->WritePotentialTableFile(path);

@@ -7,7 +7,7 @@ import numpy as np
 from . import capi
 
 HOST_ABI_SYMBOLS = ["fbn_host_model_create", "fbn_host_model_destroy", "fbn_host_model_tree", "fbn_host_model_info",
-                    "fbn_host_model_cases", "fbn_host_model_evaluate", "fbn_host_model_write_pt"]
+                    "fbn_host_model_cases", "fbn_host_model_load_golden", "fbn_host_model_evaluate", "fbn_host_model_write_pt"]
 
 
 def _lib():
@@ -20,6 +20,7 @@ def _lib():
         L.fbn_host_model_info.argtypes = [C.c_void_p, C.c_void_p]
         L.fbn_host_model_cases.argtypes = [C.c_void_p] + [C.POINTER(C.c_void_p)] * 4
         L.fbn_host_model_evaluate.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.fbn_host_model_load_golden.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p]
         L.fbn_host_model_write_pt.argtypes = [C.c_void_p, C.c_char_p]
         L._host_ready = True
     return L
@@ -77,6 +78,15 @@ class HostModel:
         off = _arr(p[0], n + 1, C.c_int64, np.int64)
         ne = int(off[-1]) if n else 0
         return off, _arr(p[1], ne, C.c_int32, np.int32), _arr(p[2], ne, C.c_int32, np.int32), _arr(p[3], n, C.c_int32, np.int32)
+
+    def golden(self, pt_path):
+        """Inference::LoadGroundTruthProbabilityTable: (n_cases, sum_dims) array, -1 in the first slot of evidence nodes."""
+        sd = int(np.sum(self.tree()["var_dims"]))
+        g = np.zeros((self.n_cases, sd), np.float64)
+        rc = self.L.fbn_host_model_load_golden(self.h, pt_path.encode(), g.ctypes.data_as(C.c_void_p))
+        if rc:
+            raise capi.FastBNError("fbn_host_model_load_golden failed: %d" % rc)
+        return g
 
     def evaluate(self, pt_path, devices=None, want_post=False):
         """JunctionTree::EvaluateAccuracy. Returns dict(accuracy, average_mse, average_hd, jt_seconds, kernel_ms, labels, post)."""

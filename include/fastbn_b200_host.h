@@ -27,6 +27,9 @@ int fbn_host_model_info(const fbn_host_model *m, int64_t *out8);
 /* CSR evidence + class labels of the loaded test cases (owned by the model) */
 int fbn_host_model_cases(const fbn_host_model *m, const int64_t **ev_offsets, const int32_t **ev_vars,
                          const int32_t **ev_vals, const int32_t **truths);
+/* Inference::LoadGroundTruthProbabilityTable (src/Inference.cpp:108-146): golden_out = n_cases x sum_dims, first entry of
+ * an evidence node's block is -1 */
+int fbn_host_model_load_golden(fbn_host_model *m, const char *pt_path, double *golden_out);
 /* EvaluateAccuracy(pt_path) over `devices` (NULL: device 0). out5 = {accuracy, average MSE, average HD, jt seconds,
  * kernel ms}. labels_out [n_cases] and posteriors_out [n_cases x sum_dims] may be NULL. */
 int fbn_host_model_evaluate(fbn_host_model *m, const char *pt_path, const int32_t *devices, int n_devices,
