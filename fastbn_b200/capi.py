@@ -28,7 +28,7 @@ class TreeDesc(C.Structure):
 
 
 class PlanOptions(C.Structure):
-    _fields_ = [("device", C.c_int32), ("team_warps", C.c_int32), ("max_resident", C.c_int32), ("mode", C.c_int32), ("reserved", C.c_int32 * 4)]
+    _fields_ = [("device", C.c_int32), ("team_warps", C.c_int32), ("max_resident", C.c_int32), ("mode", C.c_int32), ("cases_hint", C.c_int32), ("reserved", C.c_int32 * 3)]
 
 
 class PlanInfo(C.Structure):
@@ -87,7 +87,7 @@ def _ptr(a):
 class Plan:
     """Device plan of one junction tree (fbn_plan). `tree` is a dict with the fields of fbn_tree_desc."""
 
-    def __init__(self, tree, device=-1, team_warps=0, max_resident=0, mode=0):
+    def __init__(self, tree, device=-1, team_warps=0, max_resident=0, mode=0, cases_hint=0):
         self.L = load_library()
         t = tree
         self._keep = dict(
@@ -99,7 +99,7 @@ class Plan:
         d = TreeDesc(int(t["n_vars"]), _ptr(k["var_dims"]), int(t["n_cliques"]), int(t["n_separators"]), _ptr(k["table_nvars"]),
                      _ptr(k["table_vars"]), _ptr(k["clique_potentials"]), _ptr(k["sep_parent"]), _ptr(k["sep_child"]),
                      int(t["root"]), int(t["query_var"]))
-        opt = PlanOptions(device, team_warps, max_resident, mode, (C.c_int32 * 4)())
+        opt = PlanOptions(device, team_warps, max_resident, mode, cases_hint, (C.c_int32 * 3)())
         h = C.c_void_p()
         _check(self.L, self.L.fbn_plan_create(C.byref(d), C.byref(opt), C.byref(h)))
         self.h = h

@@ -216,6 +216,7 @@ extern "C" int fbn_plan_create(const fbn_tree_desc *tree, const fbn_plan_options
         if (resident * tile_bytes > budget) resident = std::max<int64_t>(1, budget / tile_bytes);
     }
     if (opt && opt->max_resident > 0) resident = std::min<int64_t>(resident, opt->max_resident);
+    if (opt && opt->cases_hint > 0) resident = std::min<int64_t>(resident, ((int64_t)opt->cases_hint + fbn::kLanes - 1) / fbn::kLanes);
     if (!level && resident >= p->n_sms) resident = resident / p->n_sms * p->n_sms;  // whole waves over the SMs
     p->grid = (int)resident;
     p->scratch_bytes = resident * tile_bytes;

@@ -11,6 +11,11 @@
 
 namespace fbn {
 
+#ifndef FBN_FUSED_STREAM
+#define FBN_FUSED_STREAM 1
+#endif
+constexpr bool kFusedStream = FBN_FUSED_STREAM != 0;
+
 struct Smem {
     uint32_t *lam;    // [sum_dims]  bit l set <=> state allowed for case l of the tile
     uint32_t *obs;    // [n_vars]    bit l set <=> variable observed in case l
@@ -39,7 +44,7 @@ __device__ __forceinline__ void collect_op(const DevPlan &P, const CollectOp &__
 #pragma unroll
             for (int c = 0; c < kColBlock; ++c) cm[c] = sm.mask[op.colmask_off + min(j0 + c, op.cols - 1)];
             RowMaskTable rm{sm.mask + op.rowmask_off};
-            collect_block_any<kColBlock>(P, op, rm, cm, S, lane, j0, nc, r0, r1, scale, acc);
+            collect_block_any<kColBlock, kFusedStream>(P, op, rm, cm, S, lane, j0, nc, r0, r1, scale, acc);
         } else {
 #pragma unroll
             for (int c = 0; c < kColBlock; ++c) {
@@ -49,7 +54,7 @@ __device__ __forceinline__ void collect_op(const DevPlan &P, const CollectOp &__
                 cm[c] = m;
             }
             RowMaskLam rm{sm.lam, P.lam16 + op.rowlam_off, op.nrest, 0u};
-            collect_block_any<kColBlock>(P, op, rm, cm, S, lane, j0, nc, r0, r1, scale, acc);
+            collect_block_any<kColBlock, kFusedStream>(P, op, rm, cm, S, lane, j0, nc, r0, r1, scale, acc);
         }
 #pragma unroll
         for (int c = 0; c < kColBlock; ++c)
@@ -72,7 +77,7 @@ __device__ __forceinline__ void pull_op(const DevPlan &P, const PullOp &__restri
         double acc[kColBlock];
 #pragma unroll
         for (int c = 0; c < kColBlock; ++c) acc[c] = 0.0;
-        pull_block<kColBlock>(P, op, S, q0, r0, r1, acc);
+        pull_block<kColBlock, kFusedStream>(P, op, S, q0, r0, r1, acc);
 #pragma unroll
         for (int c = 0; c < kColBlock; ++c)
             if (c < nq) {

@@ -55,7 +55,7 @@ __global__ void __launch_bounds__(kLevelWarps * 32, kColBlock >= 8 ? 2 : 3) lvl_
     const uint32_t *lam = lamG + (int64_t)blockIdx.y * P.lam_words;
     const Phase ph = P.phases[phase_idx];
     for (int oi = ph.op_begin; oi < ph.op_end; ++oi) {
-        const CollectOp &op = P.cops[P.oplist[oi]];
+        const CollectOp &__restrict__ op = P.cops[P.oplist[oi]];
         double scale = 1.0;
         const int32_t *__restrict__ invrows = P.idx32 + op.invrow_off;
         for (int k = 0; k < op.nchild; ++k) scale *= *row_ptr(S, __ldg(invrows + k));
@@ -77,7 +77,7 @@ __global__ void __launch_bounds__(kLevelWarps * 32, kColBlock >= 8 ? 2 : 3) lvl_
                 cm[c] = m;
             }
             RowMaskLam rm{lam, P.lam16 + op.rowlam_off, op.nrest, 0u};
-            collect_block_any<kColBlock>(P, op, rm, cm, S, lane, j0, nc, r0, r1, scale, acc);
+            collect_block_any<kColBlock, true>(P, op, rm, cm, S, lane, j0, nc, r0, r1, scale, acc);
 #pragma unroll
             for (int c = 0; c < kColBlock; ++c)
                 if (c < nc) {
@@ -107,7 +107,7 @@ __global__ void __launch_bounds__(kLevelWarps * 32, kColBlock >= 8 ? 2 : 3) lvl_
     double *S = scratch + (int64_t)blockIdx.y * P.tile_rows * kLanes + lane;
     const Phase ph = P.phases[phase_idx];
     for (int oi = ph.op_begin; oi < ph.op_end; ++oi) {
-        const PullOp &op = P.pops[P.oplist[oi]];
+        const PullOp &__restrict__ op = P.pops[P.oplist[oi]];
         const int units = (op.nT + kColBlock - 1) / kColBlock * op.chunks;
         int start = (gw - op.rot % GW) % GW;
         if (start < 0) start += GW;
@@ -117,7 +117,7 @@ __global__ void __launch_bounds__(kLevelWarps * 32, kColBlock >= 8 ? 2 : 3) lvl_
             double acc[kColBlock];
 #pragma unroll
             for (int c = 0; c < kColBlock; ++c) acc[c] = 0.0;
-            pull_block<kColBlock>(P, op, S, q0, r0, r1, acc);
+            pull_block<kColBlock, true>(P, op, S, q0, r0, r1, acc);
 #pragma unroll
             for (int c = 0; c < kColBlock; ++c)
                 if (c < nq) {

@@ -13,6 +13,23 @@ namespace fbn {
 
 __device__ __forceinline__ double *row_ptr(double *S, int32_t row) { return S + (int64_t)row * kLanes; }
 
+// Cache policy of the two big streams (clique entries written by COLLECT, read once per child by PULL). FBN_STREAM_HINTS
+// marks them evict-first so that the small, heavily re-used rows (messages, ratios, index maps, pristine potentials)
+// keep the L2.
+#ifndef FBN_STREAM_HINTS
+#define FBN_STREAM_HINTS 1
+#endif
+template <bool STREAM>
+__device__ __forceinline__ void store_clique(double *p, double v) {
+    if (STREAM && FBN_STREAM_HINTS) __stcs(p, v);
+    else *p = v;
+}
+template <bool STREAM>
+__device__ __forceinline__ double load_clique(const double *p) {
+    if (STREAM && FBN_STREAM_HINTS) return __ldcs(p);
+    return *p;
+}
+
 // ---- row evidence masks -----------------------------------------------------------------------------------------
 // mask word of clique row r: bit l set <=> case l of the tile allows that row (AND of the lambda words of the row's digits)
 struct RowMaskTable {  // fused mode, tables built once per phase in shared memory
@@ -42,7 +59,7 @@ struct RowMaskLam {  // evaluated on the fly, lane-parallel: lane i builds the w
 //   C[e] = pristine[e] * scale * mask(e) * prod_k message_k[rowpart_k(r) + colpart_k(j)];  acc[c] += C[r, j0+c]
 // NC = number of children (compile-time 0..3, -1 = generic). Loads of columns beyond nc are clamped to the last column
 // (valid addresses, results discarded), so the inner loop has no divergent control flow.
-template <int NC, int CB, class RowMask>
+template <int NC, int CB, bool STREAM, class RowMask>
 __device__ __forceinline__ void collect_block(const DevPlan &P, const CollectOp &op, RowMask &rmask, const uint32_t (&cm)[CB], double *S,
                                               int lane, int j0, int nc, int r0, int r1, double scale, double (&acc)[CB]) {
     const int nchild = NC >= 0 ? NC : op.nchild, cols = op.cols;
@@ -60,6 +77,13 @@ __device__ __forceinline__ void collect_block(const DevPlan &P, const CollectOp 
     const double *__restrict__ pot = P.pot + op.pot_off;
     double *cl = row_ptr(S, op.cl_row);
     const int32_t *__restrict__ rowpart = P.idx32 + op.rowpart_off;
+    // software pipeline: the row parts of the child maps for row r+1 are fetched while row r's message rows are in flight,
+    // so one iteration costs one memory latency (index -> data would be two)
+    int32_t rp_next[NC > 0 ? NC : 1];
+    if (NC > 0) {
+#pragma unroll
+        for (int k = 0; k < NC; ++k) rp_next[k] = __ldg(rowpart + (int64_t)r0 * NC + k);
+    }
     for (int rb = r0; rb < r1; rb += RowMask::kSpan) {
         rmask.begin(rb, r1, lane);
         const int re = RowMask::kSpan > 32 ? r1 : min(r1, rb + RowMask::kSpan);
@@ -72,8 +96,12 @@ __device__ __forceinline__ void collect_block(const DevPlan &P, const CollectOp 
             for (int c = 0; c < CB; ++c) v[c] = __ldg(pot + e + jc[c]) * scale;
             if (NC > 0) {
                 int32_t rp[NC > 0 ? NC : 1];
+                const int rn = min(r + 1, r1 - 1);
 #pragma unroll
-                for (int k = 0; k < NC; ++k) rp[k] = __ldg(rowpart + (int64_t)r * NC + k);
+                for (int k = 0; k < NC; ++k) {
+                    rp[k] = rp_next[k];
+                    rp_next[k] = __ldg(rowpart + (int64_t)rn * NC + k);
+                }
 #pragma unroll
                 for (int k = 0; k < NC; ++k)
 #pragma unroll
@@ -88,22 +116,22 @@ __device__ __forceinline__ void collect_block(const DevPlan &P, const CollectOp 
 #pragma unroll
             for (int c = 0; c < CB; ++c) {
                 const double w = (((mr & cm[c]) >> lane) & 1u) ? v[c] : 0.0;
-                if (c < nc) cl[(e + j0 + c) * kLanes] = w;
+                if (c < nc) store_clique<STREAM>(cl + (e + j0 + c) * kLanes, w);
                 acc[c] += w;
             }
         }
     }
 }
 
-template <int CB, class RowMask>
+template <int CB, bool STREAM, class RowMask>
 __device__ __forceinline__ void collect_block_any(const DevPlan &P, const CollectOp &op, RowMask &rmask, const uint32_t (&cm)[CB],
                                                   double *S, int lane, int j0, int nc, int r0, int r1, double scale, double (&acc)[CB]) {
     switch (op.nchild) {
-        case 0: collect_block<0, CB>(P, op, rmask, cm, S, lane, j0, nc, r0, r1, scale, acc); break;
-        case 1: collect_block<1, CB>(P, op, rmask, cm, S, lane, j0, nc, r0, r1, scale, acc); break;
-        case 2: collect_block<2, CB>(P, op, rmask, cm, S, lane, j0, nc, r0, r1, scale, acc); break;
-        case 3: collect_block<3, CB>(P, op, rmask, cm, S, lane, j0, nc, r0, r1, scale, acc); break;
-        default: collect_block<-1, CB>(P, op, rmask, cm, S, lane, j0, nc, r0, r1, scale, acc); break;
+        case 0: collect_block<0, CB, STREAM>(P, op, rmask, cm, S, lane, j0, nc, r0, r1, scale, acc); break;
+        case 1: collect_block<1, CB, STREAM>(P, op, rmask, cm, S, lane, j0, nc, r0, r1, scale, acc); break;
+        case 2: collect_block<2, CB, STREAM>(P, op, rmask, cm, S, lane, j0, nc, r0, r1, scale, acc); break;
+        case 3: collect_block<3, CB, STREAM>(P, op, rmask, cm, S, lane, j0, nc, r0, r1, scale, acc); break;
+        default: collect_block<-1, CB, STREAM>(P, op, rmask, cm, S, lane, j0, nc, r0, r1, scale, acc); break;
     }
 }
 
@@ -124,7 +152,7 @@ __device__ __forceinline__ void collect_unit(const CollectOp &op, int u, int &j0
 
 // ---- PULL --------------------------------------------------------------------------------------------------------
 // targets [q0, q0+nq) (nq <= QB), rest entries [r0, r1):  acc[q] += src[tbase[q].x + trest[r].x] * fac[tbase[q].y + trest[r].y]
-template <int QB>
+template <int QB, bool STREAM>
 __device__ __forceinline__ void pull_block(const DevPlan &P, const PullOp &op, double *S, int q0, int r0, int r1, double (&acc)[QB]) {
     const int2 *__restrict__ tb = reinterpret_cast<const int2 *>(P.idx32 + op.tbase_off);
     const int2 *__restrict__ tr = reinterpret_cast<const int2 *>(P.idx32 + op.trest_off);
@@ -135,11 +163,13 @@ __device__ __forceinline__ void pull_block(const DevPlan &P, const PullOp &op, d
         src[q] = row_ptr(S, op.src_row + b.x);
         fac[q] = row_ptr(S, op.fac_row + b.y);
     }
+    int2 t_next = __ldg(tr + min(r0, r1 - 1));  // index prefetch, as in collect_block
 #pragma unroll(QB >= 4 ? 2 : 4)
     for (int r = r0; r < r1; ++r) {
-        const int2 t = __ldg(tr + r);
+        const int2 t = t_next;
+        t_next = __ldg(tr + min(r + 1, r1 - 1));
 #pragma unroll
-        for (int q = 0; q < QB; ++q) acc[q] += src[q][(int64_t)t.x * kLanes] * fac[q][(int64_t)t.y * kLanes];
+        for (int q = 0; q < QB; ++q) acc[q] += load_clique<STREAM>(src[q] + (int64_t)t.x * kLanes) * fac[q][(int64_t)t.y * kLanes];
     }
 }
 

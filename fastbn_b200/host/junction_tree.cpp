@@ -5,6 +5,7 @@
 #include <algorithm>
 #include <array>
 #include <chrono>
+#include <climits>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -282,6 +283,7 @@ vector<int> JunctionTree::PredictUseJTInfer(int) {
         fbn_plan_options opt;
         memset(&opt, 0, sizeof(opt));
         opt.device = devices[di];
+        opt.cases_hint = (int32_t)std::min<int64_t>(c1 - c0, INT32_MAX);
         fbn_plan *plan = nullptr;
         if (fbn_plan_create(&flat.desc, &opt, &plan) != FBN_OK) { errors[di] = fbn_last_error(); return; }
         // slice-local CSR offsets are absolute into ev_vars/ev_vals (fbn_run rebases them per chunk)

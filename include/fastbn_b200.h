@@ -69,7 +69,8 @@ typedef struct fbn_plan_options {
                               level mode: nominal warps per tile over all CTAs of a phase launch; 0 = choose */
     int32_t max_resident;  /* cap on resident tiles (scratch = max_resident x tile bytes); 0 = choose */
     int32_t mode;          /* FBN_MODE_AUTO / FBN_MODE_FUSED / FBN_MODE_LEVEL */
-    int32_t reserved[4];
+    int32_t cases_hint;    /* > 0: the caller will run about this many cases per call; scratch is sized for no more tiles */
+    int32_t reserved[3];
 } fbn_plan_options;
 
 typedef struct fbn_plan_info {
