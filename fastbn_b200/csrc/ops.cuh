@@ -63,6 +63,37 @@ template <int NC, int CB, bool STREAM, class RowMask>
 __device__ __forceinline__ void collect_block(const DevPlan &P, const CollectOp &op, RowMask &rmask, const uint32_t (&cm)[CB], double *S,
                                               int lane, int j0, int nc, int r0, int r1, double scale, double (&acc)[CB]) {
     const int nchild = NC >= 0 ? NC : op.nchild, cols = op.cols;
+    if constexpr (CB == 1 && RowMask::kSpan > 32) {
+        // one column, mask tables in shared memory: the small-tree path (ALARM-size, one warp per tile). Kept as the plain
+        // loop — with 2-4 rows per column the blocking / shuffle / prefetch machinery below costs more than it saves.
+        const int32_t *__restrict__ cpart = P.idx32 + op.colpart_off + (int64_t)j0 * nchild;
+        int32_t cp1[NC > 0 ? NC : 1];
+        if (NC > 0) {
+#pragma unroll
+            for (int k = 0; k < NC; ++k) cp1[k] = __ldg(cpart + k);
+        }
+        const int32_t *__restrict__ rp = P.idx32 + op.rowpart_off + (int64_t)r0 * nchild;
+        const double *__restrict__ pot1 = P.pot + op.pot_off + j0;
+        double *cl1 = row_ptr(S, op.cl_row + j0);
+        double a = 0.0;
+#pragma unroll 2
+        for (int r = r0; r < r1; ++r, rp += nchild) {
+            const uint32_t m = cm[0] & rmask.get(r, r0);
+            const int64_t e = (int64_t)r * cols;
+            double v = __ldg(pot1 + e) * scale;
+            if (NC > 0) {
+#pragma unroll
+                for (int k = 0; k < NC; ++k) v *= *row_ptr(S, __ldg(rp + k) + cp1[k]);
+            } else if (NC < 0) {
+                for (int k = 0; k < nchild; ++k) v *= *row_ptr(S, __ldg(rp + k) + __ldg(cpart + k));
+            }
+            v = ((m >> lane) & 1u) ? v : 0.0;
+            store_clique<STREAM>(cl1 + e * kLanes, v);
+            a += v;
+        }
+        acc[0] += a;
+        return;
+    }
     int jc[CB];
 #pragma unroll
     for (int c = 0; c < CB; ++c) jc[c] = min(j0 + c, cols - 1);
@@ -84,40 +115,50 @@ __device__ __forceinline__ void collect_block(const DevPlan &P, const CollectOp 
 #pragma unroll
         for (int k = 0; k < NC; ++k) rp_next[k] = __ldg(rowpart + (int64_t)r0 * NC + k);
     }
+    // pristine potentials: ONE coalesced load serves RPL rows x CB columns (lane = row-in-group * CB + column), the row
+    // loop picks its values by shuffle; a warp-uniform 8-byte load per entry would cost a load instruction (and a
+    // scoreboard stall) per entry
+    constexpr int RPL = 32 / CB;
+    const int lane_c = lane % CB, lane_r = lane / CB;
+    const int jl = min(j0 + lane_c, cols - 1);
     for (int rb = r0; rb < r1; rb += RowMask::kSpan) {
         rmask.begin(rb, r1, lane);
         const int re = RowMask::kSpan > 32 ? r1 : min(r1, rb + RowMask::kSpan);
+        for (int rg = rb; rg < re; rg += RPL) {
+            const double potv = __ldg(pot + (int64_t)min(rg + lane_r, r1 - 1) * cols + jl);
+            const int rge = min(re, rg + RPL);
 #pragma unroll(CB >= 4 ? 1 : 2)
-        for (int r = rb; r < re; ++r) {
-            const uint32_t mr = rmask.get(r, rb);
-            const int64_t e = (int64_t)r * cols;
-            double v[CB];
+            for (int r = rg; r < rge; ++r) {
+                const uint32_t mr = rmask.get(r, rb);
+                const int64_t e = (int64_t)r * cols;
+                double v[CB];
 #pragma unroll
-            for (int c = 0; c < CB; ++c) v[c] = __ldg(pot + e + jc[c]) * scale;
-            if (NC > 0) {
-                int32_t rp[NC > 0 ? NC : 1];
-                const int rn = min(r + 1, r1 - 1);
+                for (int c = 0; c < CB; ++c) v[c] = __shfl_sync(0xffffffffu, potv, (r - rg) * CB + c) * scale;
+                if (NC > 0) {
+                    int32_t rp[NC > 0 ? NC : 1];
+                    const int rn = min(r + 1, r1 - 1);
 #pragma unroll
-                for (int k = 0; k < NC; ++k) {
-                    rp[k] = rp_next[k];
-                    rp_next[k] = __ldg(rowpart + (int64_t)rn * NC + k);
+                    for (int k = 0; k < NC; ++k) {
+                        rp[k] = rp_next[k];
+                        rp_next[k] = __ldg(rowpart + (int64_t)rn * NC + k);
+                    }
+#pragma unroll
+                    for (int k = 0; k < NC; ++k)
+#pragma unroll
+                        for (int c = 0; c < CB; ++c) v[c] *= *row_ptr(S, rp[k] + cp[k][c]);
+                } else if (NC < 0) {
+                    for (int k = 0; k < nchild; ++k) {
+                        const int32_t rpk = __ldg(rowpart + (int64_t)r * nchild + k);
+#pragma unroll
+                        for (int c = 0; c < CB; ++c) v[c] *= *row_ptr(S, rpk + __ldg(colpart + (int64_t)jc[c] * nchild + k));
+                    }
                 }
 #pragma unroll
-                for (int k = 0; k < NC; ++k)
-#pragma unroll
-                    for (int c = 0; c < CB; ++c) v[c] *= *row_ptr(S, rp[k] + cp[k][c]);
-            } else if (NC < 0) {
-                for (int k = 0; k < nchild; ++k) {
-                    const int32_t rpk = __ldg(rowpart + (int64_t)r * nchild + k);
-#pragma unroll
-                    for (int c = 0; c < CB; ++c) v[c] *= *row_ptr(S, rpk + __ldg(colpart + (int64_t)jc[c] * nchild + k));
+                for (int c = 0; c < CB; ++c) {
+                    const double w = (((mr & cm[c]) >> lane) & 1u) ? v[c] : 0.0;
+                    if (c < nc) store_clique<STREAM>(cl + (e + j0 + c) * kLanes, w);
+                    acc[c] += w;
                 }
-            }
-#pragma unroll
-            for (int c = 0; c < CB; ++c) {
-                const double w = (((mr & cm[c]) >> lane) & 1u) ? v[c] : 0.0;
-                if (c < nc) store_clique<STREAM>(cl + (e + j0 + c) * kLanes, w);
-                acc[c] += w;
             }
         }
     }
@@ -156,6 +197,18 @@ template <int QB, bool STREAM>
 __device__ __forceinline__ void pull_block(const DevPlan &P, const PullOp &op, double *S, int q0, int r0, int r1, double (&acc)[QB]) {
     const int2 *__restrict__ tb = reinterpret_cast<const int2 *>(P.idx32 + op.tbase_off);
     const int2 *__restrict__ tr = reinterpret_cast<const int2 *>(P.idx32 + op.trest_off);
+    if constexpr (QB == 1) {  // small-tree path: plain loop, four rest entries in flight
+        const int2 b = __ldg(tb + q0);
+        const double *src1 = row_ptr(S, op.src_row + b.x), *fac1 = row_ptr(S, op.fac_row + b.y);
+        double a = 0.0;
+#pragma unroll 4
+        for (int r = r0; r < r1; ++r) {
+            const int2 t = __ldg(tr + r);
+            a += load_clique<STREAM>(src1 + (int64_t)t.x * kLanes) * fac1[(int64_t)t.y * kLanes];
+        }
+        acc[0] += a;
+        return;
+    }
     const double *src[QB], *fac[QB];
 #pragma unroll
     for (int q = 0; q < QB; ++q) {

@@ -46,6 +46,24 @@ def test_level_mode_matches_reference(name, team, max_resident):
     assert st.n_launches >= p.info.launches_per_wave
 
 
+@pytest.mark.parametrize("name", ["munin_small", "munin"])
+def test_munin_shape_auto_level_mode(name):
+    """BASELINE.json config 5: max clique 5^9 / 5^10 entries, intra-table multi-CTA split. Expected values: the unmodified
+    reference's posteriors for the committed cases (0 % evidence + cases with 24 evidence variables)."""
+    t, g = _shape(name)
+    p = capi.Plan(t, device=0)
+    assert p.info.mode == capi.MODE_LEVEL
+    labels, post, st = p.run(g["ev_off"], g["ev_vars"], g["ev_vals"])
+    assert np.nanmax(np.abs(post - g["post"])) <= TOL
+    assert np.array_equal(labels, g["labels"])
+    # 0 % evidence: many identical cases (several tiles) must give identical rows, equal to the reference's
+    n = 100
+    labels2, post2, _ = p.run(np.zeros(n + 1, np.int64), np.zeros(0, np.int32), np.zeros(0, np.int32))
+    p.close()
+    assert np.all(post2 == post2[0]) and np.all(labels2 == labels2[0])
+    assert np.max(np.abs(post2[0] - g["post"][0])) <= TOL
+
+
 def test_level_mode_alarm_fixtures_and_nan(alarm_tree):
     p = capi.Plan(alarm_tree, device=0, mode=capi.MODE_LEVEL)
     for name in ["alarm_1k_ref", "alarm_edge_ref"]:
