@@ -35,7 +35,7 @@ __device__ __forceinline__ void collect_op(const DevPlan &P, const CollectOp &__
     double nacc = 0.0;
     for (int u = (warp - op.rot) & (TEAM - 1); u < units; u += TEAM) {
         int j0, nc, ck, r0, r1;
-        collect_unit<kColBlock>(op, u, j0, nc, ck, r0, r1);
+        collect_unit<kColBlock>(P, op, u, j0, nc, ck, r0, r1);
         uint32_t cm[kColBlock];
         double acc[kColBlock];
 #pragma unroll

@@ -65,7 +65,7 @@ __global__ void __launch_bounds__(kLevelWarps * 32, kColBlock >= 8 ? 2 : 3) lvl_
         double nacc = 0.0;
         for (int u = start; u < units; u += GW) {
             int j0, nc, ck, r0, r1;
-            collect_unit<kColBlock>(op, u, j0, nc, ck, r0, r1);
+            collect_unit<kColBlock>(P, op, u, j0, nc, ck, r0, r1);
             uint32_t cm[kColBlock];
             double acc[kColBlock];
 #pragma unroll

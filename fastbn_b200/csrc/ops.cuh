@@ -59,6 +59,92 @@ struct RowMaskLam {  // evaluated on the fly, lane-parallel: lane i builds the w
 //   C[e] = pristine[e] * scale * mask(e) * prod_k message_k[rowpart_k(r) + colpart_k(j)];  acc[c] += C[r, j0+c]
 // NC = number of children (compile-time 0..3, -1 = generic). Loads of columns beyond nc are clamped to the last column
 // (valid addresses, results discarded), so the inner loop has no divergent control flow.
+// Row loop of collect_block. UMASK (compile time): children whose message row is the same for all CB columns of the block.
+// Per row ALL gathers are issued before the first use (one memory latency per row), the clique row pointer advances by a
+// 64-bit add (stores at immediate offsets c * 256 B), the row parts of the child maps are fetched one row ahead.
+template <int NC, int UMASK, int CB, bool STREAM, class RowMask>
+__device__ __forceinline__ void collect_rows(const DevPlan &P, const CollectOp &op, RowMask &rmask, const uint32_t (&cm)[CB], double *S,
+                                             int lane, int j0, int nc, int r0, int r1, double scale, const int32_t (&cp)[NC > 0 ? NC : 1][CB],
+                                             double (&acc)[CB]) {
+    const int nchild = NC >= 0 ? NC : op.nchild, cols = op.cols;
+    const double *__restrict__ pot = P.pot + op.pot_off;
+    const int32_t *__restrict__ rowpart = P.idx32 + op.rowpart_off;
+    const int32_t *__restrict__ colpart = P.idx32 + op.colpart_off;
+    const int64_t rstride = (int64_t)cols * kLanes;
+    double *clp = row_ptr(S, op.cl_row) + ((int64_t)r0 * cols + j0) * kLanes;
+    const uint32_t lanebit = 1u << lane;
+    int32_t rp_next[NC > 0 ? NC : 1];
+    if (NC > 0) {
+#pragma unroll
+        for (int k = 0; k < NC; ++k) rp_next[k] = __ldg(rowpart + (int64_t)r0 * NC + k);
+    }
+    // pristine potentials: ONE coalesced load serves RPL rows x CB columns (lane = row-in-group * CB + column), the row
+    // loop picks its values by shuffle; a warp-uniform 8-byte load per entry would cost a load instruction (and a
+    // scoreboard stall) per entry
+    constexpr int RPL = 32 / CB;
+    const int lane_c = lane % CB, lane_r = lane / CB;
+    const int jl = min(j0 + lane_c, cols - 1);
+    for (int rb = r0; rb < r1; rb += RowMask::kSpan) {
+        rmask.begin(rb, r1, lane);
+        const int re = RowMask::kSpan > 32 ? r1 : min(r1, rb + RowMask::kSpan);
+        for (int rg = rb; rg < re; rg += RPL) {
+            const double potv = __ldg(pot + (int64_t)min(rg + lane_r, r1 - 1) * cols + jl);
+            const int rge = min(re, rg + RPL);
+#pragma unroll(CB >= 4 ? 1 : 2)
+            for (int r = rg; r < rge; ++r, clp += rstride) {
+                const bool rowon = (rmask.get(r, rb) & lanebit) != 0;
+                double m[NC > 0 ? NC : 1][CB];
+                double u = scale;
+                if (NC > 0) {
+                    const double *mb[NC > 0 ? NC : 1];
+                    const int rn = min(r + 1, r1 - 1);
+#pragma unroll
+                    for (int k = 0; k < NC; ++k) {
+                        mb[k] = S + (int64_t)rp_next[k] * kLanes;
+                        rp_next[k] = __ldg(rowpart + (int64_t)rn * NC + k);
+                    }
+#pragma unroll
+                    for (int k = 0; k < NC; ++k) {
+                        if ((UMASK >> k) & 1) {
+                            m[k][0] = mb[k][(int64_t)cp[k][0] * kLanes];
+                        } else {
+#pragma unroll
+                            for (int c = 0; c < CB; ++c) m[k][c] = mb[k][(int64_t)cp[k][c] * kLanes];
+                        }
+                    }
+#pragma unroll
+                    for (int k = 0; k < NC; ++k)
+                        if ((UMASK >> k) & 1) u *= m[k][0];
+                }
+                double v[CB];
+#pragma unroll
+                for (int c = 0; c < CB; ++c) v[c] = __shfl_sync(0xffffffffu, potv, (r - rg) * CB + c) * u;
+                if (NC > 0) {
+#pragma unroll
+                    for (int k = 0; k < NC; ++k)
+                        if (!((UMASK >> k) & 1)) {
+#pragma unroll
+                            for (int c = 0; c < CB; ++c) v[c] *= m[k][c];
+                        }
+                } else if (NC < 0) {
+                    for (int k = 0; k < nchild; ++k) {
+                        const int32_t rpk = __ldg(rowpart + (int64_t)r * nchild + k);
+#pragma unroll
+                        for (int c = 0; c < CB; ++c)
+                            v[c] *= *row_ptr(S, rpk + __ldg(colpart + (int64_t)min(j0 + c, cols - 1) * nchild + k));
+                    }
+                }
+#pragma unroll
+                for (int c = 0; c < CB; ++c) {
+                    const double w = (rowon && (cm[c] & lanebit)) ? v[c] : 0.0;
+                    if (c < nc) store_clique<STREAM>(clp + c * kLanes, w);
+                    acc[c] += w;
+                }
+            }
+        }
+    }
+}
+
 template <int NC, int CB, bool STREAM, class RowMask>
 __device__ __forceinline__ void collect_block(const DevPlan &P, const CollectOp &op, RowMask &rmask, const uint32_t (&cm)[CB], double *S,
                                               int lane, int j0, int nc, int r0, int r1, double scale, double (&acc)[CB]) {
@@ -99,68 +185,33 @@ __device__ __forceinline__ void collect_block(const DevPlan &P, const CollectOp 
     for (int c = 0; c < CB; ++c) jc[c] = min(j0 + c, cols - 1);
     int32_t cp[NC > 0 ? NC : 1][CB];
     const int32_t *__restrict__ colpart = P.idx32 + op.colpart_off;
+    // umask bit k: all CB columns of the block read the SAME message row of child k (the block's column variables are
+    // outside separator k) -> one gather per row instead of CB, folded into the row's scalar factor
+    int umask = 0;
     if (NC > 0) {
 #pragma unroll
-        for (int k = 0; k < NC; ++k)
+        for (int k = 0; k < NC; ++k) {
+            bool u = true;
 #pragma unroll
-            for (int c = 0; c < CB; ++c) cp[k][c] = __ldg(colpart + (int64_t)jc[c] * NC + k);
-    }
-    const double *__restrict__ pot = P.pot + op.pot_off;
-    double *cl = row_ptr(S, op.cl_row);
-    const int32_t *__restrict__ rowpart = P.idx32 + op.rowpart_off;
-    // software pipeline: the row parts of the child maps for row r+1 are fetched while row r's message rows are in flight,
-    // so one iteration costs one memory latency (index -> data would be two)
-    int32_t rp_next[NC > 0 ? NC : 1];
-    if (NC > 0) {
-#pragma unroll
-        for (int k = 0; k < NC; ++k) rp_next[k] = __ldg(rowpart + (int64_t)r0 * NC + k);
-    }
-    // pristine potentials: ONE coalesced load serves RPL rows x CB columns (lane = row-in-group * CB + column), the row
-    // loop picks its values by shuffle; a warp-uniform 8-byte load per entry would cost a load instruction (and a
-    // scoreboard stall) per entry
-    constexpr int RPL = 32 / CB;
-    const int lane_c = lane % CB, lane_r = lane / CB;
-    const int jl = min(j0 + lane_c, cols - 1);
-    for (int rb = r0; rb < r1; rb += RowMask::kSpan) {
-        rmask.begin(rb, r1, lane);
-        const int re = RowMask::kSpan > 32 ? r1 : min(r1, rb + RowMask::kSpan);
-        for (int rg = rb; rg < re; rg += RPL) {
-            const double potv = __ldg(pot + (int64_t)min(rg + lane_r, r1 - 1) * cols + jl);
-            const int rge = min(re, rg + RPL);
-#pragma unroll(CB >= 4 ? 1 : 2)
-            for (int r = rg; r < rge; ++r) {
-                const uint32_t mr = rmask.get(r, rb);
-                const int64_t e = (int64_t)r * cols;
-                double v[CB];
-#pragma unroll
-                for (int c = 0; c < CB; ++c) v[c] = __shfl_sync(0xffffffffu, potv, (r - rg) * CB + c) * scale;
-                if (NC > 0) {
-                    int32_t rp[NC > 0 ? NC : 1];
-                    const int rn = min(r + 1, r1 - 1);
-#pragma unroll
-                    for (int k = 0; k < NC; ++k) {
-                        rp[k] = rp_next[k];
-                        rp_next[k] = __ldg(rowpart + (int64_t)rn * NC + k);
-                    }
-#pragma unroll
-                    for (int k = 0; k < NC; ++k)
-#pragma unroll
-                        for (int c = 0; c < CB; ++c) v[c] *= *row_ptr(S, rp[k] + cp[k][c]);
-                } else if (NC < 0) {
-                    for (int k = 0; k < nchild; ++k) {
-                        const int32_t rpk = __ldg(rowpart + (int64_t)r * nchild + k);
-#pragma unroll
-                        for (int c = 0; c < CB; ++c) v[c] *= *row_ptr(S, rpk + __ldg(colpart + (int64_t)jc[c] * nchild + k));
-                    }
-                }
-#pragma unroll
-                for (int c = 0; c < CB; ++c) {
-                    const double w = (((mr & cm[c]) >> lane) & 1u) ? v[c] : 0.0;
-                    if (c < nc) store_clique<STREAM>(cl + (e + j0 + c) * kLanes, w);
-                    acc[c] += w;
-                }
+            for (int c = 0; c < CB; ++c) {
+                cp[k][c] = __ldg(colpart + (int64_t)jc[c] * NC + k);
+                u = u && cp[k][c] == cp[k][0];
             }
+            if (u) umask |= 1 << k;
         }
+    }
+    if constexpr (NC > 0 && NC <= 2 && CB >= 4) {
+        switch (umask) {
+            case 0: collect_rows<NC, 0, CB, STREAM>(P, op, rmask, cm, S, lane, j0, nc, r0, r1, scale, cp, acc); break;
+            case 1: collect_rows<NC, 1, CB, STREAM>(P, op, rmask, cm, S, lane, j0, nc, r0, r1, scale, cp, acc); break;
+            case 2: collect_rows<NC, 2 % (1 << NC), CB, STREAM>(P, op, rmask, cm, S, lane, j0, nc, r0, r1, scale, cp, acc); break;
+            default: collect_rows<NC, (1 << NC) - 1, CB, STREAM>(P, op, rmask, cm, S, lane, j0, nc, r0, r1, scale, cp, acc); break;
+        }
+    } else if constexpr (NC == 3 && CB >= 4) {
+        if (umask == 7) collect_rows<NC, 7, CB, STREAM>(P, op, rmask, cm, S, lane, j0, nc, r0, r1, scale, cp, acc);
+        else collect_rows<NC, 0, CB, STREAM>(P, op, rmask, cm, S, lane, j0, nc, r0, r1, scale, cp, acc);
+    } else {
+        collect_rows<NC, 0, CB, STREAM>(P, op, rmask, cm, S, lane, j0, nc, r0, r1, scale, cp, acc);
     }
 }
 
@@ -178,7 +229,7 @@ __device__ __forceinline__ void collect_block_any(const DevPlan &P, const Collec
 
 // unit u of a collect op -> column block + row range
 template <int CB>
-__device__ __forceinline__ void collect_unit(const CollectOp &op, int u, int &j0, int &nc, int &ck, int &r0, int &r1) {
+__device__ __forceinline__ void collect_unit(const DevPlan &P, const CollectOp &op, int u, int &j0, int &nc, int &ck, int &r0, int &r1) {
     int jb = u;
     ck = 0; r0 = 0; r1 = op.rows;
     if (op.chunks > 1) {
@@ -187,6 +238,7 @@ __device__ __forceinline__ void collect_unit(const CollectOp &op, int u, int &j0
         r0 = ck * op.rows_per_chunk;
         r1 = min(op.rows, r0 + op.rows_per_chunk);
     }
+    if (op.perm_off >= 0) jb = __ldg(P.idx32 + op.perm_off + jb);  // planner's visiting order of the column blocks
     j0 = jb * CB;
     nc = min(CB, op.cols - j0);
 }
@@ -210,13 +262,26 @@ __device__ __forceinline__ void pull_block(const DevPlan &P, const PullOp &op, d
         return;
     }
     const double *src[QB], *fac[QB];
+    bool uni = true;  // all QB targets share the factor row (their variables are outside the source's column variables)
 #pragma unroll
     for (int q = 0; q < QB; ++q) {
         const int2 b = __ldg(tb + min(q0 + q, op.nT - 1));
         src[q] = row_ptr(S, op.src_row + b.x);
         fac[q] = row_ptr(S, op.fac_row + b.y);
+        uni = uni && fac[q] == fac[0];
     }
     int2 t_next = __ldg(tr + min(r0, r1 - 1));  // index prefetch, as in collect_block
+    if (uni) {
+#pragma unroll(QB >= 4 ? 2 : 4)
+        for (int r = r0; r < r1; ++r) {
+            const int2 t = t_next;
+            t_next = __ldg(tr + min(r + 1, r1 - 1));
+            const double f = fac[0][(int64_t)t.y * kLanes];
+#pragma unroll
+            for (int q = 0; q < QB; ++q) acc[q] += load_clique<STREAM>(src[q] + (int64_t)t.x * kLanes) * f;
+        }
+        return;
+    }
 #pragma unroll(QB >= 4 ? 2 : 4)
     for (int r = r0; r < r1; ++r) {
         const int2 t = t_next;

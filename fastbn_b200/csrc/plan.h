@@ -37,6 +37,9 @@ struct CollectOp {
     int64_t rowpart_off;  // into idx32[]: rows*nchild  (absolute scratch row of child k's message, row part)
     int64_t colpart_off;  // into idx32[]: cols*nchild  (column part)
     int64_t invrow_off;   // into idx32[]: nchild absolute scratch rows holding 1/norm of each child clique
+    int64_t perm_off;     // into idx32[]: visiting order of the column blocks (unit u works on block perm[u / chunks]), -1 =
+                          //   storage order. The planner orders blocks so that blocks visited together gather the same child
+                          //   message rows (column variables outside the child separators vary fastest): keeps the gathers in L2.
     int32_t cl_row;       // scratch row of entry 0 of this clique
     int32_t mup_row;      // scratch row of entry 0 of this clique's upward message (root: dummy row)
     int32_t inv_row;      // scratch row receiving 1/sum(clique)

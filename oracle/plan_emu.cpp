@@ -51,7 +51,9 @@ extern "C" int emu_run(const fbn_tree_desc *tree, int team, int64_t n_cases, con
                 const int units = (ncolsop + kColBlock - 1) / kColBlock * chunks;
                 for (int u = 0; u < units; ++u)
                   for (int cc = 0; cc < kColBlock; ++cc) {  // the columns / targets of the unit's block
-                    const int jb = u / chunks, ck = u - jb * chunks;
+                    int jb = u / chunks;
+                    const int ck = u - jb * chunks;
+                    if (ph.kind == 0 && P.cops[o].perm_off >= 0) jb = P.idx32[P.cops[o].perm_off + jb];  // visiting order
                     if (jb * kColBlock + cc >= ncolsop) break;
                     if (ph.kind == 0) {
                         const CollectOp &op = P.cops[o];

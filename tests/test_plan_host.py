@@ -77,3 +77,19 @@ def test_no_cpu_fallback_without_device(alarm_tree):
     with pytest.raises(capi.FastBNError) as ei:
         capi.Plan(alarm_tree)
     assert "no CUDA device" in str(ei.value)
+
+
+@pytest.mark.parametrize("team", [32, -64])
+def test_plan_with_permuted_block_order_on_pigs_shape(team):
+    """PIGS-shape (max clique 3^10): the planner visits the column blocks of big cliques in a locality order
+    (CollectOp::perm_off); the emulated plan must still reproduce the unmodified reference (fused team 32 and level mode)."""
+    from fastbn_b200 import hostapi
+    m = hostapi.HostModel(os.path.join(ROOT, "tests", "golden", "synth", "pigs.xml"))
+    t = m.tree()
+    m.close()
+    g = load_golden(os.path.join("synth", "pigs_ref"))
+    n = 6
+    k = g["ev_off"][n]
+    post, lab, info = emu.run(t, team, g["ev_off"][:n + 1], g["ev_vars"][:k], g["ev_vals"][:k])
+    assert np.nanmax(np.abs(post - g["post"][:n])) <= 1e-9
+    assert np.array_equal(lab, g["labels"][:n])
