@@ -17,6 +17,10 @@
 
 namespace fbn {
 
+#ifndef FBN_LVL_OCC4
+#define FBN_LVL_OCC4 3   // resident CTAs per SM the cb = 4 collect kernel is register-bounded for
+#endif
+
 namespace {
 
 // evidence -> per-tile lambda bit words in global memory (LoadDiscreteEvidence, src/JunctionTree.cpp:316-383, mask form
@@ -46,7 +50,7 @@ __global__ void __launch_bounds__(128) lvl_evidence_kernel(const DevPlan P, uint
 // child messages, column sums into the upstream separator (see CollectOp in plan.h). Row masks are evaluated
 // lane-parallel from the tile's lambda words (RowMaskLam, ops.cuh).
 template <int kColBlock>
-__global__ void __launch_bounds__(kLevelWarps * 32, kColBlock >= 8 ? 2 : 3) lvl_collect_kernel(const DevPlan P, double *__restrict__ scratch,
+__global__ void __launch_bounds__(kLevelWarps * 32, kColBlock >= 8 ? 2 : FBN_LVL_OCC4) lvl_collect_kernel(const DevPlan P, double *__restrict__ scratch,
                                                                        const uint32_t *__restrict__ lamG, int phase_idx) {
     __shared__ double red[kLevelWarps][kLanes];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;

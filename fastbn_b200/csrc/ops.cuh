@@ -59,13 +59,21 @@ struct RowMaskLam {  // evaluated on the fly, lane-parallel: lane i builds the w
 //   C[e] = pristine[e] * scale * mask(e) * prod_k message_k[rowpart_k(r) + colpart_k(j)];  acc[c] += C[r, j0+c]
 // NC = number of children (compile-time 0..3, -1 = generic). Loads of columns beyond nc are clamped to the last column
 // (valid addresses, results discarded), so the inner loop has no divergent control flow.
-// Row loop of collect_block. UMASK (compile time): children whose message row is the same for all CB columns of the block.
-// Per row ALL gathers are issued before the first use (one memory latency per row), the clique row pointer advances by a
-// 64-bit add (stores at immediate offsets c * 256 B), the row parts of the child maps are fetched one row ahead.
+// Row loop of collect_block. UMASK (compile time): children whose message row is the same for all CB columns of the block
+// (one gather per row, folded into the row's scalar factor).
+// Software pipeline: the gathers of row r+1 are issued BEFORE row r is multiplied, masked and stored (two register sets,
+// used alternately), so the memory latency of a row overlaps the arithmetic and the stores of the previous one; the row parts
+// of the child maps are fetched two rows ahead, the coalesced pristine-potential load one group ahead. Rows that need more
+// than 9 gathers keep one register set (gathers issued together at the top of the row). The clique row pointer advances by
+// a 64-bit add, stores go to immediate offsets c * 256 B.
 template <int NC, int UMASK, int CB, bool STREAM, class RowMask>
 __device__ __forceinline__ void collect_rows(const DevPlan &P, const CollectOp &op, RowMask &rmask, const uint32_t (&cm)[CB], double *S,
                                              int lane, int j0, int nc, int r0, int r1, double scale, const int32_t (&cp)[NC > 0 ? NC : 1][CB],
                                              double (&acc)[CB]) {
+    constexpr int NCC = NC > 0 ? NC : 1;
+    constexpr int NU = (UMASK & 1) + ((UMASK >> 1) & 1) + ((UMASK >> 2) & 1);
+    constexpr int kGathers = NC > 0 ? (NC - NU) * CB + NU : 0;  // per row
+    constexpr bool kTwoSets = NC > 0 && CB >= 4 && kGathers <= 9;
     const int nchild = NC >= 0 ? NC : op.nchild, cols = op.cols;
     const double *__restrict__ pot = P.pot + op.pot_off;
     const int32_t *__restrict__ rowpart = P.idx32 + op.rowpart_off;
@@ -73,74 +81,113 @@ __device__ __forceinline__ void collect_rows(const DevPlan &P, const CollectOp &
     const int64_t rstride = (int64_t)cols * kLanes;
     double *clp = row_ptr(S, op.cl_row) + ((int64_t)r0 * cols + j0) * kLanes;
     const uint32_t lanebit = 1u << lane;
-    int32_t rp_next[NC > 0 ? NC : 1];
-    if (NC > 0) {
+    uint32_t colon = 0;  // bit c: this lane's case allows column j0+c
 #pragma unroll
-        for (int k = 0; k < NC; ++k) rp_next[k] = __ldg(rowpart + (int64_t)r0 * NC + k);
-    }
+    for (int c = 0; c < CB; ++c)
+        if (cm[c] & lanebit) colon |= 1u << c;
     // pristine potentials: ONE coalesced load serves RPL rows x CB columns (lane = row-in-group * CB + column), the row
     // loop picks its values by shuffle; a warp-uniform 8-byte load per entry would cost a load instruction (and a
     // scoreboard stall) per entry
     constexpr int RPL = 32 / CB;
     const int lane_c = lane % CB, lane_r = lane / CB;
-    const int jl = min(j0 + lane_c, cols - 1);
-    for (int rb = r0; rb < r1; rb += RowMask::kSpan) {
-        rmask.begin(rb, r1, lane);
-        const int re = RowMask::kSpan > 32 ? r1 : min(r1, rb + RowMask::kSpan);
-        for (int rg = rb; rg < re; rg += RPL) {
-            const double potv = __ldg(pot + (int64_t)min(rg + lane_r, r1 - 1) * cols + jl);
-            const int rge = min(re, rg + RPL);
-#pragma unroll(CB >= 4 ? 1 : 2)
-            for (int r = rg; r < rge; ++r, clp += rstride) {
-                const bool rowon = (rmask.get(r, rb) & lanebit) != 0;
-                double m[NC > 0 ? NC : 1][CB];
-                double u = scale;
-                if (NC > 0) {
-                    const double *mb[NC > 0 ? NC : 1];
-                    const int rn = min(r + 1, r1 - 1);
+    const double *potl = pot + min(j0 + lane_c, cols - 1);
+    double potv = 0.0, potv_next = __ldg(potl + (int64_t)min(r0 + lane_r, r1 - 1) * cols);
+    int rb = r0;
+
+    auto load_parts = [&](int rr, int32_t (&rp)[NCC]) {
+        if (NC > 0) {
+            const int32_t *q = rowpart + (int64_t)min(rr, r1 - 1) * NC;
 #pragma unroll
-                    for (int k = 0; k < NC; ++k) {
-                        mb[k] = S + (int64_t)rp_next[k] * kLanes;
-                        rp_next[k] = __ldg(rowpart + (int64_t)rn * NC + k);
-                    }
+            for (int k = 0; k < NC; ++k) rp[k] = __ldg(q + k);
+        }
+    };
+    auto gather = [&](const int32_t (&rp)[NCC], double (&m)[NCC][CB]) {
+        if (NC > 0) {
 #pragma unroll
-                    for (int k = 0; k < NC; ++k) {
-                        if ((UMASK >> k) & 1) {
-                            m[k][0] = mb[k][(int64_t)cp[k][0] * kLanes];
-                        } else {
+            for (int k = 0; k < NC; ++k) {
+                const double *mb = S + (int64_t)rp[k] * kLanes;
+                if ((UMASK >> k) & 1) {
+                    m[k][0] = mb[(int64_t)cp[k][0] * kLanes];
+                } else {
 #pragma unroll
-                            for (int c = 0; c < CB; ++c) m[k][c] = mb[k][(int64_t)cp[k][c] * kLanes];
-                        }
-                    }
-#pragma unroll
-                    for (int k = 0; k < NC; ++k)
-                        if ((UMASK >> k) & 1) u *= m[k][0];
-                }
-                double v[CB];
-#pragma unroll
-                for (int c = 0; c < CB; ++c) v[c] = __shfl_sync(0xffffffffu, potv, (r - rg) * CB + c) * u;
-                if (NC > 0) {
-#pragma unroll
-                    for (int k = 0; k < NC; ++k)
-                        if (!((UMASK >> k) & 1)) {
-#pragma unroll
-                            for (int c = 0; c < CB; ++c) v[c] *= m[k][c];
-                        }
-                } else if (NC < 0) {
-                    for (int k = 0; k < nchild; ++k) {
-                        const int32_t rpk = __ldg(rowpart + (int64_t)r * nchild + k);
-#pragma unroll
-                        for (int c = 0; c < CB; ++c)
-                            v[c] *= *row_ptr(S, rpk + __ldg(colpart + (int64_t)min(j0 + c, cols - 1) * nchild + k));
-                    }
-                }
-#pragma unroll
-                for (int c = 0; c < CB; ++c) {
-                    const double w = (rowon && (cm[c] & lanebit)) ? v[c] : 0.0;
-                    if (c < nc) store_clique<STREAM>(clp + c * kLanes, w);
-                    acc[c] += w;
+                    for (int c = 0; c < CB; ++c) m[k][c] = mb[(int64_t)cp[k][c] * kLanes];
                 }
             }
+        }
+    };
+    auto finish = [&](int r, const double (&m)[NCC][CB]) {
+        if (RowMask::kSpan <= 32 && ((r - r0) & 31) == 0) {
+            rb = r;
+            rmask.begin(rb, r1, lane);
+        }
+        const int rg = (r - r0) & (RPL - 1);  // row inside its group of RPL
+        if (rg == 0) {
+            potv = potv_next;
+            potv_next = __ldg(potl + (int64_t)min(r + RPL + lane_r, r1 - 1) * cols);
+        }
+        const uint32_t on = (rmask.get(r, rb) & lanebit) ? colon : 0u;
+        double u = scale;
+        if (NC > 0) {
+#pragma unroll
+            for (int k = 0; k < NC; ++k)
+                if ((UMASK >> k) & 1) u *= m[k][0];
+        }
+        double v[CB];
+#pragma unroll
+        for (int c = 0; c < CB; ++c) v[c] = __shfl_sync(0xffffffffu, potv, rg * CB + c) * u;
+        if (NC > 0) {
+#pragma unroll
+            for (int k = 0; k < NC; ++k)
+                if (!((UMASK >> k) & 1)) {
+#pragma unroll
+                    for (int c = 0; c < CB; ++c) v[c] *= m[k][c];
+                }
+        } else if (NC < 0) {
+            for (int k = 0; k < nchild; ++k) {
+                const int32_t rpk = __ldg(rowpart + (int64_t)r * nchild + k);
+#pragma unroll
+                for (int c = 0; c < CB; ++c) v[c] *= *row_ptr(S, rpk + __ldg(colpart + (int64_t)min(j0 + c, cols - 1) * nchild + k));
+            }
+        }
+#pragma unroll
+        for (int c = 0; c < CB; ++c) {
+            const double w = ((on >> c) & 1u) ? v[c] : 0.0;
+            if (c < nc) store_clique<STREAM>(clp + c * kLanes, w);
+            acc[c] += w;
+        }
+        clp += rstride;
+    };
+
+    if (RowMask::kSpan > 32) rmask.begin(r0, r1, lane);
+    if constexpr (kTwoSets) {
+        int32_t rp0[NCC], rp1[NCC];
+        double m0[NCC][CB], m1[NCC][CB];
+        load_parts(r0, rp0);
+        load_parts(r0 + 1, rp1);
+        gather(rp0, m0);          // row r0
+        load_parts(r0 + 2, rp0);  // parts of row r0 + 2
+        for (int r = r0; r < r1; r += 2) {
+            // here: m0 = row r (in flight), rp1 = parts of row r+1, rp0 = parts of row r+2 (in flight)
+            gather(rp1, m1);
+            load_parts(r + 3, rp1);
+            finish(r, m0);
+            if (r + 1 < r1) {
+                gather(rp0, m0);
+                load_parts(r + 4, rp0);
+                finish(r + 1, m1);
+            }
+        }
+    } else {
+        int32_t rp[NCC], rpn[NCC];
+        double m[NCC][CB];
+        load_parts(r0, rpn);
+#pragma unroll(CB >= 4 ? 1 : 2)
+        for (int r = r0; r < r1; ++r) {
+#pragma unroll
+            for (int k = 0; k < NCC; ++k) rp[k] = rpn[k];
+            gather(rp, m);
+            load_parts(r + 1, rpn);
+            finish(r, m);
         }
     }
 }

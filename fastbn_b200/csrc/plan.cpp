@@ -262,20 +262,32 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
         op.invrow_off = (int64_t)P.idx32.size();
         for (int k = 0; k < op.nchild; ++k) P.idx32.push_back(P.inv_row0 + t.sep_child[kids[c][k]]);
         // Visiting order of the column blocks. Child k's message row of entry (r, j) depends only on the digits of the
-        // variables in separator k; a block order in which the column variables that belong to NO child separator vary
-        // fastest, then those of one child, ... makes the blocks that are in flight together gather the same few message
-        // rows (L1/L2 hits) instead of sweeping every child message table once per slow digit.
+        // variables in separator k. Consecutive units run on the warps of one CTA at the same time, so the order decides
+        // which gathers they share: column variables that belong only to children whose row is the SAME for a whole block
+        // (one gather per row) vary fastest, variables of children that need one gather per column vary slower (the warps
+        // of a CTA then read the same rows -> L1 hits), variables shared by several children slowest.
         op.perm_off = -1;
         const int64_t nblk = (op.cols + kColBlock - 1) / kColBlock;
         if (op.nchild > 0 && nblk > 1 && C.size >= 32768 && !getenv("FBN_NO_PERM")) {
             std::vector<int> order(op.ncolv);  // column variables, slowest first
             std::iota(order.begin(), order.end(), 0);
-            std::vector<int> cnt(op.ncolv, 0), first(op.ncolv, op.nchild);
+            std::vector<int> cnt(op.ncolv, 0), first(op.ncolv, op.nchild), tier(op.ncolv, 3);
+            std::vector<char> in_block(op.ncolv, 0), child_uniform(op.nchild, 1);
+            {
+                int64_t span = 1;  // the fastest column variables, up to a product >= the block width, vary inside a block
+                for (int i = op.ncolv; i-- > 0 && span < kColBlock;) { in_block[i] = 1; span *= C.dims[cpos[i]]; }
+            }
             for (int i = 0; i < op.ncolv; ++i)
                 for (int k = op.nchild; k-- > 0;)
-                    if (sep[kids[c][k]].find(C.vars[cpos[i]]) >= 0) { ++cnt[i]; first[i] = k; }
+                    if (sep[kids[c][k]].find(C.vars[cpos[i]]) >= 0) {
+                        ++cnt[i]; first[i] = k;
+                        if (in_block[i]) child_uniform[k] = 0;
+                    }
+            const bool old_rule = getenv("FBN_PERM_OLD") != nullptr;
+            for (int i = 0; i < op.ncolv; ++i)
+                tier[i] = cnt[i] >= 2 ? 0 : cnt[i] == 0 ? 3 : (old_rule || !child_uniform[first[i]]) ? 1 : 2;
             std::stable_sort(order.begin(), order.end(), [&](int a, int b) {
-                if (cnt[a] != cnt[b]) return cnt[a] > cnt[b];
+                if (tier[a] != tier[b]) return tier[a] < tier[b];
                 return first[a] < first[b];
             });
             bool identity = true;
