@@ -391,11 +391,11 @@ static int run_impl(fbn_plan *p, int64_t n_cases, const int64_t *ev_offsets, con
     int rc;
     if (want_gold && (rc = ensure_score(p, n_cases)) != FBN_OK) return rc;
     const bool stage_gold = want_gold && !(is_pinned(golden) && is_pinned(truths));
-    // chunking: ~128 MB of posteriors per chunk, at least one full wave of resident tiles
-    double chunk_mb = 128.0;
+    // chunking: ~96 MB of posteriors per chunk, at least half a wave of resident tiles
+    double chunk_mb = 96.0;  // measured on B200 (tools/e2e_sweep.py): 96 MB chunks give the shortest pipeline for 1M ALARM cases
     if (const char *e = getenv("FBN_CHUNK_MB")) chunk_mb = std::max(1.0, atof(e));
     int64_t chunk = (int64_t)(chunk_mb * 1048576.0 / (8.0 * sd));
-    if (!getenv("FBN_CHUNK_MB")) chunk = std::max<int64_t>(chunk, (int64_t)p->grid * fbn::kLanes);
+    if (!getenv("FBN_CHUNK_MB")) chunk = std::max<int64_t>(chunk, (int64_t)p->grid * fbn::kLanes / 2);  // at least half a wave of tiles
     chunk = std::min<int64_t>(chunk, std::max<int64_t>(fbn::kLanes, (int64_t)(1024.0 * 1048576.0 / (8.0 * sd))));
     chunk = (chunk + fbn::kLanes - 1) / fbn::kLanes * fbn::kLanes;
     chunk = std::min<int64_t>(chunk, (n_cases + fbn::kLanes - 1) / fbn::kLanes * fbn::kLanes);
