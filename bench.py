@@ -309,8 +309,8 @@ def main():
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": w["desc"], "cases_per_gpu": n, "n_evidence": w["n_evidence"], "team_warps": info.team_warps,
                        "mode": "level" if info.mode == capi.MODE_LEVEL else "fused", "launches_per_step": launches_per_step,
-                       "resident_tiles": info.resident_tiles, "l2": "per-step working set (evidence + posteriors) %.0f MB > 126 MB L2"
-                       % ((off_h.nbytes + ev_h.nbytes + ew_h.nbytes + n * sd * 8 + n * 4) / 1e6),
+                       "resident_tiles": info.resident_tiles, "l2": "per-step working set (tile scratch + evidence + posteriors) %.0f MB > 126 MB L2"
+                       % ((info.scratch_bytes + off_h.nbytes + ev_h.nbytes + ew_h.nbytes + n * sd * 8 + n * 4) / 1e6),
                        "labels_e2e_equal_device": same, "labelled_cases": int(counts[0].item()), "total_cases": int(counts[1].item())},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "peak_source": peak_src,

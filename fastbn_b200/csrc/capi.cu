@@ -399,12 +399,11 @@ static int run_impl(fbn_plan *p, int64_t n_cases, const int64_t *ev_offsets, con
     chunk = std::min<int64_t>(chunk, std::max<int64_t>(fbn::kLanes, (int64_t)(1024.0 * 1048576.0 / (8.0 * sd))));
     chunk = (chunk + fbn::kLanes - 1) / fbn::kLanes * fbn::kLanes;
     chunk = std::min<int64_t>(chunk, (n_cases + fbn::kLanes - 1) / fbn::kLanes * fbn::kLanes);
-    const int64_t n_chunks = (n_cases + chunk - 1) / chunk;
+    std::vector<int64_t> bounds{0};  // chunk boundaries (a ramp of smaller first chunks was measured: no gain)
+    while (bounds.back() < n_cases) bounds.push_back(std::min(n_cases, bounds.back() + chunk));
+    const int64_t n_chunks = (int64_t)bounds.size() - 1;
     int64_t max_ev = 1;
-    for (int64_t c = 0; c < n_chunks; ++c) {
-        int64_t c0 = c * chunk, c1 = std::min(n_cases, c0 + chunk);
-        max_ev = std::max(max_ev, ev_offsets[c1] - ev_offsets[c0]);
-    }
+    for (int64_t c = 0; c < n_chunks; ++c) max_ev = std::max(max_ev, ev_offsets[bounds[c + 1]] - ev_offsets[bounds[c]]);
     const bool stage_in = !(is_pinned(ev_offsets) && is_pinned(ev_vars) && is_pinned(ev_vals));
     const bool stage_out = !(is_pinned(labels_out) && is_pinned(posteriors_out));
     struct Pending { int64_t c0 = 0, n = 0; bool active = false; } pend[kNBuf];
@@ -424,7 +423,7 @@ static int run_impl(fbn_plan *p, int64_t n_cases, const int64_t *ev_offsets, con
         const int bi = (int)(c % kNBuf);
         ChunkBuf &b = p->buf[bi];
         if ((rc = drain(bi)) != FBN_OK) return rc;
-        const int64_t c0 = c * chunk, n = std::min(n_cases, c0 + chunk) - c0;
+        const int64_t c0 = bounds[c], n = bounds[c + 1] - c0;
         const int64_t e0 = ev_offsets[c0], ne = ev_offsets[c0 + n] - e0;
         if ((rc = ensure_chunk(b, chunk, max_ev, sd, want_post, want_post_host, stage_in, stage_out, want_gold, stage_gold)) != FBN_OK) return rc;
         const int64_t *src_off = ev_offsets + c0;
