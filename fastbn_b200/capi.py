@@ -10,7 +10,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("FASTBN_B200_LIB") or os.path.join(_HERE, "libfastbn_b200.so")
 
 # every symbol include/fastbn_b200.h declares
-ABI_SYMBOLS = ["fbn_last_error", "fbn_device_count", "fbn_plan_create", "fbn_plan_destroy", "fbn_plan_get_info",
+ABI_SYMBOLS = ["fbn_last_error", "fbn_device_count", "fbn_device_warmup", "fbn_plan_create", "fbn_plan_destroy", "fbn_plan_get_info",
                "fbn_run", "fbn_run_device", "fbn_evaluate", "fbn_score_device"]
 
 

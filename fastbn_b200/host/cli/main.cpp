@@ -3,10 +3,12 @@
 // "../dataset/", same stdout lines. Algorithms other than 2 are outside this build and say so.
 // Extensions: -G <n> shards the test cases over n GPUs (or FASTBN_DEVICES=0,1,...); -o <file> writes the posteriors
 // in the reference's potential-table format (relative to ../dataset/ too); -D <dir> replaces the "../dataset/" prefix.
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <iostream>
 #include <string>
+#include <thread>
 
 #include "../fastbn_host.h"
 
@@ -63,10 +65,18 @@ int main(int argc, char **argv) {
     cout << "\treference potential table: " << pt_file << endl;
     cout << "===============================" << endl;
 
+    // FASTBN_TIMING=1: stage times on stderr (stdout stays the reference's)
+    const bool timing = getenv("FASTBN_TIMING") != nullptr;
+    auto now = [] { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    double t0 = now();
+    // CUDA contexts come up in the background while the input files are parsed
+    std::thread([n_gpus] { for (int d = 0; d < (n_gpus > 0 ? n_gpus : 1); ++d) fbn_device_warmup(d); }).detach();
     Dataset *tester = new Dataset();
     CustomNetwork *network = new CustomNetwork(true);
     network->GetNetFromXMLBIFFile(net_file);
+    double t1 = now();
     tester->LoadLIBSVMDataKnownNetwork(test_set_file, network->num_nodes);
+    double t2 = now();
 
     JunctionTree *jt = new JunctionTree(network, tester, false);
     if (n_gpus > 0) {
@@ -75,9 +85,15 @@ int main(int argc, char **argv) {
     }
     jt->keep_posteriors = !out_pt.empty();
     Inference *inference = jt;
+    double t3 = now();
     double accuracy = inference->EvaluateAccuracy(pt_file, num_threads);
+    double t4 = now();
     cout << "accuracy = " << accuracy << endl;
     if (!out_pt.empty()) jt->WritePotentialTableFile(prefix + out_pt);
+    double t5 = now();
+    if (timing)
+        fprintf(stderr, "[timing] xmlbif %.3f s, test cases %.3f s, junction tree %.3f s, potential-table file %.3f s, jt (GPU, host buffers) %.3f s, "
+                        "write -o %.3f s, total %.3f s\n", t1 - t0, t2 - t1, t3 - t2, (t4 - t3) - jt->jt_seconds, jt->jt_seconds, t5 - t4, t5 - t0);
 
     delete inference;
     delete network;

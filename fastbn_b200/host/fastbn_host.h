@@ -17,6 +17,7 @@
 #include <map>
 #include <set>
 #include <string>
+#include <thread>
 #include <utility>
 #include <vector>
 
@@ -29,6 +30,12 @@ using std::string;
 using std::vector;
 
 typedef set<pair<int, int>> DiscreteConfig;  // include/common.h:22
+
+// exact fast paths of "%.7f" formatting and decimal parsing for the potential-table files (textio.cpp)
+namespace textio {
+int FormatFixed7(double x, char *out352);
+const char *ParseDouble(const char *p, const char *e, double *out);
+}  // namespace textio
 
 // ---------------------------------------------------------------------------------------------------------------
 // A discrete variable with its CPT kept as the reference keeps it: INTEGER counts (int)(p*10000) per (value, parent
@@ -206,6 +213,7 @@ public:
     vector<int> predictions;         // labels of the last EvaluateAccuracy
     double average_mse = 0, average_hd = 0, jt_seconds = 0, kernel_ms = 0;
     bool quiet = false;
+    std::thread warmup;              // brings the CUDA contexts of `devices` up in the background (joined before the first plan)
 
     JunctionTree(Network *net, Dataset *dts, bool is_dense);
     ~JunctionTree();

@@ -10,7 +10,13 @@
 #include <cstdlib>
 #include <cstring>
 #include <iostream>
+#include <memory>
 #include <thread>
+#include <unistd.h>
+
+#ifdef _OPENMP
+#include <omp.h>
+#endif
 
 #include "fastbn_host.h"
 
@@ -97,28 +103,94 @@ void Inference::LoadGroundTruthProbabilityTable(string file_path) {
         exit(1);
     }
     std::cout << "Data file opened. Begin to load ground truth probability tables computed by JT. " << std::endl;
-    string buf;
     fseek(f, 0, SEEK_END);
     long sz = ftell(f);
     fseek(f, 0, SEEK_SET);
-    buf.resize(sz > 0 ? (size_t)sz : 0);
-    size_t got = buf.empty() ? 0 : fread(&buf[0], 1, buf.size(), f);
-    buf.resize(got);
+    // uninitialised buffer (a std::string would zero-fill ~0.9 GB first), NUL-terminated for the strtod fallback
+    struct RawBuf {
+        std::unique_ptr<char[]> p;
+        size_t n = 0;
+        size_t size() const { return n; }
+        bool empty() const { return n == 0; }
+        char &operator[](size_t i) { return p[i]; }
+        const char *data() const { return p.get(); }
+        char back() const { return p[n - 1]; }
+    } buf;
+    buf.n = sz > 0 ? (size_t)sz : 0;
+    buf.p.reset(new char[buf.n + 1]);
+    buf.p[buf.n] = 0;
+    {   // the file is read and scanned in parallel pieces (887 MB for 10^6 ALARM cases)
+        const int fd = fileno(f);
+        int nth = 1;
+#ifdef _OPENMP
+        nth = omp_get_max_threads();
+#endif
+        const int64_t piece = ((int64_t)buf.size() + nth - 1) / std::max(nth, 1);
+        bool ok = true;
+#pragma omp parallel for schedule(static, 1)
+        for (int t = 0; t < nth; ++t) {
+            int64_t o = (int64_t)t * piece, end = std::min<int64_t>((int64_t)buf.size(), o + piece);
+            while (o < end) {
+                ssize_t g = pread(fd, &buf[(size_t)o], (size_t)(end - o), (off_t)o);
+                if (g <= 0) { ok = false; break; }
+                o += g;
+            }
+        }
+        if (!ok) {
+            fprintf(stderr, "Error in function %s!Unable to read file %s!", __FUNCTION__, file_path.c_str());
+            exit(1);
+        }
+    }
     fclose(f);
     const int n_nodes = network->num_nodes, sd = var_offsets[n_nodes];
     ground_truth_probability_tables.assign((size_t)num_instances * sd, 0.0);
-    // line starts (sequential scan), then parallel numeric parsing
+    // line starts (newlines counted per piece, then placed), then parallel numeric parsing
     const int64_t want = (int64_t)num_instances * n_nodes;
+    const char *base = buf.data();
     vector<int64_t> line_at;
-    line_at.reserve((size_t)want + 1);
-    const char *base = buf.data(), *end = base + buf.size();
-    for (const char *p = base; p < end && (int64_t)line_at.size() < want;) {
-        line_at.push_back(p - base);
-        const char *nl = (const char *)memchr(p, '\n', (size_t)(end - p));
-        p = nl ? nl + 1 : end;
+    {
+        int nth = 1;
+#ifdef _OPENMP
+        nth = omp_get_max_threads();
+#endif
+        const int64_t piece = ((int64_t)buf.size() + nth - 1) / std::max(nth, 1);
+        vector<int64_t> cnt((size_t)nth + 1, 0);
+#pragma omp parallel for schedule(static, 1)
+        for (int t = 0; t < nth; ++t) {
+            const char *p = base + std::min<int64_t>((int64_t)buf.size(), (int64_t)t * piece);
+            const char *pe = base + std::min<int64_t>((int64_t)buf.size(), (int64_t)(t + 1) * piece);
+            int64_t c = 0;
+            while (p < pe) {
+                const char *nl = (const char *)memchr(p, '\n', (size_t)(pe - p));
+                if (!nl) break;
+                ++c;
+                p = nl + 1;
+            }
+            cnt[(size_t)t + 1] = c;
+        }
+        for (int t = 0; t < nth; ++t) cnt[(size_t)t + 1] += cnt[(size_t)t];
+        // line k+1 starts after the k-th newline; line 0 starts at 0; a last piece without '\n' is a line too
+        const int64_t n_nl = cnt[(size_t)nth];
+        const bool tail = !buf.empty() && buf.back() != '\n';
+        const int64_t n_lines = buf.empty() ? 0 : n_nl + (tail ? 1 : 0);
+        line_at.assign((size_t)std::min(want, n_lines) + 1, 0);
+        const int64_t keep = (int64_t)line_at.size() - 1;  // lines used
+#pragma omp parallel for schedule(static, 1)
+        for (int t = 0; t < nth; ++t) {
+            const char *p = base + std::min<int64_t>((int64_t)buf.size(), (int64_t)t * piece);
+            const char *pe = base + std::min<int64_t>((int64_t)buf.size(), (int64_t)(t + 1) * piece);
+            int64_t k = cnt[(size_t)t];  // newlines before this piece
+            while (p < pe) {
+                const char *nl = (const char *)memchr(p, '\n', (size_t)(pe - p));
+                if (!nl) break;
+                ++k;
+                if (k <= keep) line_at[(size_t)k] = nl + 1 - base;  // start of line k == end of line k-1
+                p = nl + 1;
+            }
+        }
+        if (keep > n_nl) line_at[(size_t)keep] = (int64_t)buf.size();  // the last used line is the unterminated tail
     }
-    const int64_t have = (int64_t)line_at.size();
-    line_at.push_back((int64_t)buf.size());
+    const int64_t have = (int64_t)line_at.size() - 1;
 #pragma omp parallel for schedule(static)
     for (int64_t ln = 0; ln < want; ++ln) {
         const int64_t i = ln / n_nodes;
@@ -127,12 +199,12 @@ void Inference::LoadGroundTruthProbabilityTable(string file_path) {
         const int dim = var_offsets[j + 1] - var_offsets[j];
         if (ln >= have) { dst[0] = -1; continue; }
         const char *p = base + line_at[ln];
-        const char *e = (ln + 1 < have) ? base + line_at[ln + 1] : end;
+        const char *e = base + line_at[ln + 1];
         while (e > p && (unsigned char)e[-1] < 33) --e;
         if (p == e) { dst[0] = -1; continue; }
         for (int k = 0; k < dim && p < e; ++k) {
-            char *q = nullptr;
-            dst[k] = strtod(p, &q);
+            const char *q = textio::ParseDouble(p, e, &dst[k]);
+            if (q == p) break;  // not a number: the rest of the block stays 0, like a short line
             p = q;
             while (p < e && *p == ' ') ++p;
         }
@@ -164,11 +236,19 @@ JunctionTree::JunctionTree(Network *net, Dataset *dts, bool is_dense) : Inferenc
         }
     }
     if (devices.empty()) devices.push_back(0);
+    // the CUDA contexts come up (about a second each) while the caller goes on to read the potential-table file
+    {
+        vector<int> devs = devices;
+        warmup = std::thread([devs] { for (int d : devs) fbn_device_warmup(d); });
+    }
     std::cout << "==================================================" << std::endl;
     std::cout << "construct jt: " << now_s() - t0 << " s " << std::endl;
 }
 
-JunctionTree::~JunctionTree() { delete tree; }
+JunctionTree::~JunctionTree() {
+    if (warmup.joinable()) warmup.join();
+    delete tree;
+}
 
 // number of alternating clique / separator levels when `root` is the root: 2 * eccentricity + 1
 int JunctionTree::GetMaxLevel(Clique *root) {
@@ -266,6 +346,7 @@ void JunctionTree::Flatten(FlatTree &o) const {
 // {n_correct, n_total, sum_mse, sum_hd}.
 vector<int> JunctionTree::PredictUseJTInfer(int) {
     if (!quiet) std::cout << "Progress indicator: " << std::endl;
+    if (warmup.joinable()) warmup.join();
     FlatTree flat;
     Flatten(flat);
     const int sd = var_offsets[network->num_nodes];
@@ -285,7 +366,9 @@ vector<int> JunctionTree::PredictUseJTInfer(int) {
         opt.device = devices[di];
         opt.cases_hint = (int32_t)std::min<int64_t>(c1 - c0, INT32_MAX);
         fbn_plan *plan = nullptr;
+        const double tw0 = now_s();
         if (fbn_plan_create(&flat.desc, &opt, &plan) != FBN_OK) { errors[di] = fbn_last_error(); return; }
+        const double tw1 = now_s();
         // slice-local CSR offsets are absolute into ev_vars/ev_vals (fbn_run rebases them per chunk)
         fbn_stats st;
         const bool need_last = (di == nd - 1) && c1 > c0;
@@ -295,6 +378,9 @@ vector<int> JunctionTree::PredictUseJTInfer(int) {
                               predictions.data() + c0, post_out, part[di].data(), &st);
         if (rc != FBN_OK) errors[di] = fbn_last_error();
         kms[di] = st.kernel_ms;
+        if (getenv("FASTBN_TIMING"))
+            fprintf(stderr, "[timing] device %d: plan %.3f s, fbn_evaluate %.3f s (compute stream %.3f s) for %lld cases\n", devices[di],
+                    tw1 - tw0, now_s() - tw1, st.kernel_ms * 1e-3, (long long)(c1 - c0));
         if (rc == FBN_OK && need_last) {  // probs_one_sample holds the last case, as after the reference's loop
             if (keep_posteriors) {
                 memcpy(last_post.data(), posteriors.data() + (size_t)(n - 1) * sd, sizeof(double) * sd);
@@ -359,23 +445,39 @@ void JunctionTree::WritePotentialTableFile(const string &path) const {
         fprintf(stderr, "Error in function %s!Unable to open file %s!", __FUNCTION__, path.c_str());
         exit(1);
     }
-    vector<char> is_ev(n_nodes);
-    string line;
-    char tmp[64];
-    for (int i = 0; i < num_instances; ++i) {
-        std::fill(is_ev.begin(), is_ev.end(), 0);
-        for (int64_t k = ev_offsets[i]; k < ev_offsets[i + 1]; ++k)
-            if (ev_vars[k] >= 0 && ev_vars[k] < n_nodes) is_ev[ev_vars[k]] = 1;
-        line.clear();
-        for (int v = 0; v < n_nodes; ++v) {
-            if (!is_ev[v])
-                for (int k = var_offsets[v]; k < var_offsets[v + 1]; ++k) {
-                    int len = snprintf(tmp, sizeof(tmp), "%.7f ", posteriors[(size_t)i * sd + k]);
-                    line.append(tmp, len);
+    // cases are formatted in parallel (snprintf "%.7f " is the whole cost at 10^6 cases x 105 states), block by block in
+    // file order
+    const int kBlock = 2048;
+    int nthreads = 1;
+#ifdef _OPENMP
+    nthreads = omp_get_max_threads();
+#endif
+    const int64_t super = (int64_t)kBlock * nthreads;
+    vector<string> out((size_t)nthreads);
+    for (int64_t s0 = 0; s0 < num_instances; s0 += super) {
+#pragma omp parallel for schedule(static, 1)
+        for (int t = 0; t < nthreads; ++t) {
+            string &line = out[(size_t)t];
+            line.clear();
+            vector<char> is_ev(n_nodes);
+            char tmp[360];
+            const int64_t i0 = s0 + (int64_t)t * kBlock, i1 = std::min<int64_t>(num_instances, i0 + kBlock);
+            for (int64_t i = i0; i < i1; ++i) {
+                std::fill(is_ev.begin(), is_ev.end(), 0);
+                for (int64_t k = ev_offsets[i]; k < ev_offsets[i + 1]; ++k)
+                    if (ev_vars[k] >= 0 && ev_vars[k] < n_nodes) is_ev[ev_vars[k]] = 1;
+                for (int v = 0; v < n_nodes; ++v) {
+                    if (!is_ev[v])
+                        for (int k = var_offsets[v]; k < var_offsets[v + 1]; ++k) {
+                            int len = textio::FormatFixed7(posteriors[(size_t)i * sd + k], tmp);
+                            tmp[len++] = ' ';
+                            line.append(tmp, len);
+                        }
+                    line.push_back('\n');
                 }
-            line.push_back('\n');
+            }
         }
-        fwrite(line.data(), 1, line.size(), f);
+        for (int t = 0; t < nthreads; ++t) fwrite(out[(size_t)t].data(), 1, out[(size_t)t].size(), f);
     }
     fclose(f);
 }

@@ -7,7 +7,8 @@ import numpy as np
 from . import capi
 
 HOST_ABI_SYMBOLS = ["fbn_host_model_create", "fbn_host_model_destroy", "fbn_host_model_tree", "fbn_host_model_info",
-                    "fbn_host_model_cases", "fbn_host_model_load_golden", "fbn_host_model_evaluate", "fbn_host_model_write_pt"]
+                    "fbn_host_model_cases", "fbn_host_model_load_golden", "fbn_host_model_evaluate", "fbn_host_model_write_pt",
+                    "fbn_host_format_fixed", "fbn_host_parse_double"]
 
 
 def _lib():

@@ -100,6 +100,9 @@ typedef struct fbn_stats {
 
 const char *fbn_last_error(void);
 int fbn_device_count(void);
+/* Creates the CUDA context of `device` (about a second on a B200 box) so that a caller can overlap it with its own file
+ * parsing from another thread; fbn_plan_create does the same implicitly. */
+int fbn_device_warmup(int32_t device);
 
 /* Build the device plan once per tree (replaces BackUpJunctionTree + the per-level "pre" phases,
  * src/JunctionTree.cpp:289-300, :586-639, :834-880). opt may be NULL. */

@@ -37,6 +37,12 @@ int fbn_host_model_evaluate(fbn_host_model *m, const char *pt_path, const int32_
 /* posteriors of the last evaluate (posteriors_out must have been non-NULL) in the reference's pt-file format */
 int fbn_host_model_write_pt(fbn_host_model *m, const char *path);
 
+/* Test hooks of the exact text fast paths used for the potential-table files (fastbn_b200/host/textio.cpp):
+ * "%.7f" formatting (out352: at least 352 bytes, returns the length, no terminator) and decimal parsing (returns the
+ * number of characters consumed, like strtod's end pointer). */
+int fbn_host_format_fixed(double x, char *out352);
+int fbn_host_parse_double(const char *s, int len, double *out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -120,3 +120,72 @@ def test_cli_fails_loudly_without_gpu(tmp_path):
     assert "no CUDA device" in r.stderr
     assert "number of cliques = 27, number of separators = 26" in r.stdout
     assert "maximum level of the junction tree = 15" in r.stdout
+
+
+def test_text_fast_paths_are_bit_identical_to_libc():
+    """"%.7f" writer and decimal parser of the potential-table files (fastbn_b200/host/textio.cpp) against Python's
+    correctly rounded formatting / parsing (== glibc's) on random values, exact ties, neighbours of ties and odd tokens."""
+    import ctypes as C
+    import struct
+    L = capi.load_library()
+    L.fbn_host_format_fixed.argtypes = [C.c_double, C.c_char_p]
+    L.fbn_host_parse_double.argtypes = [C.c_char_p, C.c_int, C.POINTER(C.c_double)]
+    buf = C.create_string_buffer(400)
+    rng = np.random.default_rng(11)
+    xs = list(rng.random(60000)) + list(rng.random(20000) * 1e-6) + list(rng.random(2000) * 1000)
+    xs += [0.0, 1.0, 0.5, 5e-8, 1.5e-7, 2.5e-7, 1e-8, 4.9999999e-8, 5.0000001e-8, 0.99999995, 0.99999994999, 1.5, 123.4567891,
+           float("nan"), -0.0, -1.25, 1e300, float("inf"), 1048575.99999995, 1048576.0]
+    ties = [(k + 0.5) / 1e7 for k in range(3000)]
+    xs += ties + [float(np.nextafter(t, 1)) for t in ties] + [float(np.nextafter(t, 0)) for t in ties]
+    for x in xs:
+        n = L.fbn_host_format_fixed(float(x), buf)
+        assert buf.raw[:n].decode() == "%.7f" % x, repr(x)
+    out = C.c_double()
+    toks = ["%.7f" % x for x in xs[:40000] if x == x and abs(x) < 1e200]
+    toks += ["0.1", "1", "1.", "-.5", "+3.25", "1e-3", "1.5E2", "nan", "inf", "123456789012345678", "0.123456789012345678",
+             "0.00000000000000000000000012", "12345678901234567890123", "1.7976931348623157e308", "4.9e-324", "-0.0000000"]
+    for t in toks:
+        b = t.encode()
+        n = L.fbn_host_parse_double(b, len(b), C.byref(out))
+        exp = float(t)
+        assert n == len(b), t
+        assert struct.pack("d", out.value) == struct.pack("d", exp) or (exp != exp and out.value != out.value), t
+
+
+def _parse_pt_py(path, n_cases, var_dims):
+    """straightforward restatement of Inference::LoadGroundTruthProbabilityTable (src/Inference.cpp:108-146)"""
+    lines = open(path).read().split("\n")
+    if lines and lines[-1] == "":
+        lines.pop()
+    offs = np.concatenate([[0], np.cumsum(var_dims)])
+    out = np.zeros((n_cases, offs[-1]))
+    nv = len(var_dims)
+    for ln in range(n_cases * nv):
+        i, j = divmod(ln, nv)
+        toks = lines[ln].split() if ln < len(lines) else []
+        if not toks:
+            out[i, offs[j]] = -1
+            continue
+        for k, t in enumerate(toks[:var_dims[j]]):
+            out[i, offs[j] + k] = float(t)
+    return out
+
+
+def test_potential_table_loader_matches_plain_parse(tmp_path):
+    """the parallel -f4 loader (pieces read with pread, line index built per piece, exact fast decimal parser) against a
+    line-by-line Python parse: the shipped 1000-case file, a truncated copy and a copy without the final newline"""
+    xml = os.path.join(GOLDEN, "alarm", "alarm.xml")
+    cases = os.path.join(GOLDEN, "alarm", "testing_alarm_1k_p20")
+    pt = os.path.join(GOLDEN, "alarm", "alarm_1k_pt")
+    m = hostapi.HostModel(xml, cases)
+    dims = m.tree()["var_dims"]
+    n = len(m.cases()[0]) - 1
+    raw = open(pt).read()
+    variants = {"full": raw, "truncated": raw[:len(raw) // 3], "no_final_newline": raw.rstrip("\n")}
+    for name, text in variants.items():
+        p = str(tmp_path / name)
+        open(p, "w").write(text)
+        got = m.golden(p)
+        exp = _parse_pt_py(p, n, dims)
+        assert np.array_equal(got, exp), name
+    m.close()
