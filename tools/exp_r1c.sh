@@ -1,3 +1,2 @@
-python tools/e2e_sweep.py default
-FBN_NO_RAMP=1 python tools/e2e_sweep.py default
-python -m pytest tests/test_gpu_parity.py -x -q -m gpu | tail -1
+for t in 4 8 16 32; do python tools/prof_run.py pigs 75776 $t 2 1 | tail -1; done
+for t in 2 4 8 16; do python tools/prof_run.py hepar2 265216 $t 2 1 | tail -1; done
