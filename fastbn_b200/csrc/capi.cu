@@ -194,7 +194,7 @@ extern "C" int fbn_plan_create(const fbn_tree_desc *tree, const fbn_plan_options
     fbn::DevPlan &d = p->dp;
     int rc;
 #define UP(field) if ((rc = upload(p, h.field, &d.field)) != FBN_OK) { fbn_plan_destroy(p); return rc; }
-    UP(pot) UP(lam16) UP(idx32) UP(cops) UP(pops) UP(oplist) UP(fins) UP(phases) UP(vars)
+    UP(pot) UP(lam16) UP(idx32) UP(cops) UP(pops) UP(p2ops) UP(oplist) UP(fins) UP(phases) UP(vars)
 #undef UP
     d.n_phases = (int32_t)h.phases.size();
     d.n_vars = h.n_vars; d.sum_dims = h.sum_dims; d.query_var = h.query_var;

@@ -111,7 +111,16 @@ __global__ void __launch_bounds__(kLevelWarps * 32, kColBlock >= 8 ? 2 : 3) lvl_
     double *S = scratch + (int64_t)blockIdx.y * P.tile_rows * kLanes + lane;
     const Phase ph = P.phases[phase_idx];
     for (int oi = ph.op_begin; oi < ph.op_end; ++oi) {
-        const PullOp &__restrict__ op = P.pops[P.oplist[oi]];
+        const int oidx = P.oplist[oi];
+        if (oidx < 0) {  // two children of one parent from one pass (Pull2Op, plan.h)
+            const Pull2Op &__restrict__ op2 = P.p2ops[-1 - oidx];
+            const int units2 = op2.n12 * op2.nblk1;
+            int start2 = (gw - op2.rot % GW) % GW;
+            if (start2 < 0) start2 += GW;
+            for (int u = start2; u < units2; u += GW) pull2_unit<kColBlock>(P, op2, S, u);
+            continue;
+        }
+        const PullOp &__restrict__ op = P.pops[oidx];
         const int units = (op.nT + kColBlock - 1) / kColBlock * op.chunks;
         int start = (gw - op.rot % GW) % GW;
         if (start < 0) start += GW;

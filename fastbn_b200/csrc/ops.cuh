@@ -338,6 +338,78 @@ __device__ __forceinline__ void pull_block(const DevPlan &P, const PullOp &op, d
     }
 }
 
+// ---- PULL2 (level mode) ----------------------------------------------------------------------------------------------
+// Unit u = (G12 configuration a, block b of QB configurations of G1) of a Pull2Op (plan.h): one pass over the G2
+// configurations gives QB complete entries of separator A and one partial row per G2 configuration for separator B.
+template <int QB>
+__device__ __forceinline__ void pull2_unit(const DevPlan &P, const Pull2Op &op, double *S, int u) {
+    const int4 *__restrict__ ta = reinterpret_cast<const int4 *>(P.idx32 + op.a_off);
+    const int4 *__restrict__ t1 = reinterpret_cast<const int4 *>(P.idx32 + op.g1_off);
+    const int4 *__restrict__ t2 = reinterpret_cast<const int4 *>(P.idx32 + op.g2_off);
+    const int a = u / op.nblk1, b = u - a * op.nblk1;
+    const int4 A = __ldg(ta + a);
+    const int g0 = b * QB, nq = min(QB, op.n1 - g0);
+    const double *src[QB], *fac[QB];
+    int32_t qa[QB];
+    double acc[QB];
+#pragma unroll
+    for (int c = 0; c < QB; ++c) {
+        const int4 G = __ldg(t1 + min(g0 + c, op.n1 - 1));
+        src[c] = row_ptr(S, op.src_row + A.x + G.x);
+        fac[c] = row_ptr(S, op.fac_row + A.y + G.y);
+        qa[c] = A.z + G.z;
+        acc[c] = 0.0;
+    }
+    double *part = row_ptr(S, P.part_row0 + op.pslot0) + ((int64_t)A.w * op.nblk1 + b) * kLanes;
+    const int64_t pstride = (int64_t)op.nblk1 * kLanes;
+    // software pipeline, two register sets: the 2*QB loads of configuration r+1 are issued before configuration r is
+    // multiplied, accumulated and its partial row stored; the index entries are fetched two configurations ahead
+    auto loads = [&](const int4 &R, double (&sv)[QB], double (&fv)[QB]) {
+#pragma unroll
+        for (int c = 0; c < QB; ++c) {
+            sv[c] = load_clique<true>(src[c] + (int64_t)R.x * kLanes);
+            fv[c] = fac[c][(int64_t)R.y * kLanes];
+        }
+    };
+    auto finish = [&](const int4 &R, const double (&sv)[QB], const double (&fv)[QB]) {
+        double prod[QB];
+#pragma unroll
+        for (int c = 0; c < QB; ++c) {
+            prod[c] = sv[c] * fv[c];
+            acc[c] += prod[c];
+            if (c >= nq) prod[c] = 0.0;  // clamped duplicates of a ragged last block do not belong to the partial
+        }
+        // fixed pairwise order (deterministic)
+#pragma unroll
+        for (int w = 1; w < QB; w *= 2)
+#pragma unroll
+            for (int c = 0; c + w < QB; c += 2 * w) prod[c] += prod[c + w];
+        part[(int64_t)R.z * pstride] = prod[0];
+    };
+    double s0[QB], f0[QB], s1[QB], f1[QB];
+    int4 Ra = __ldg(t2), Rb = __ldg(t2 + min(1, op.n2 - 1));
+    loads(Ra, s0, f0);
+    for (int r = 0; r < op.n2; r += 2) {
+        // here: (s0, f0) = configuration r (in flight), Ra its index entry, Rb the entry of r+1
+        loads(Rb, s1, f1);
+        const int4 Rc = __ldg(t2 + min(r + 2, op.n2 - 1));
+        finish(Ra, s0, f0);
+        if (r + 1 < op.n2) {
+            loads(Rc, s0, f0);
+            const int4 Rd = __ldg(t2 + min(r + 3, op.n2 - 1));
+            finish(Rb, s1, f1);
+            Rb = Rd;
+        }
+        Ra = Rc;
+    }
+#pragma unroll
+    for (int c = 0; c < QB; ++c)
+        if (c < nq) {
+            const double m = *row_ptr(S, op.mupA_row + qa[c]);
+            *row_ptr(S, op.dstA_row + qa[c]) = (m == 0.0) ? 0.0 : acc[c] / m;  // TableDivision 0-guard, PotentialTable.cpp:718-734
+        }
+}
+
 template <int CB>
 __device__ __forceinline__ void pull_unit(const PullOp &op, int u, int &q0, int &nq, int &ck, int &r0, int &r1) {
     int qb = u;

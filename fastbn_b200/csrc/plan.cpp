@@ -391,7 +391,9 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
     // fused mode keeps partial sums and mask tables in shared memory; level mode keeps partials in scratch rows
     const int64_t kMaxPslots = level ? std::max<int64_t>(192, std::min<int64_t>(1 << 16, P.clique_entries / 8)) : 192;
     const int kMaxMaskWords = (level || getenv("FBN_NO_TABLES")) ? 0 : 6144;
-    auto emit_phase = [&](int kind, const std::vector<int> &ops) {
+    struct P2Host { int32_t dstB_row, mupB_row; int64_t sizeB; };  // host-only facts of a Pull2Op: separator B's rows
+    std::vector<P2Host> p2host;
+    auto emit_phase = [&](int kind, const std::vector<int> &ops, const std::vector<int> &p2 = std::vector<int>()) {
         Phase ph = Phase();
         ph.kind = kind;
         ph.op_begin = (int32_t)P.oplist.size();
@@ -460,6 +462,23 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
                 P.fins.push_back(f);
             }
         }
+        for (int x : p2) {  // fused two-children pulls: their own partial slots (one per entry of separator B and block)
+            Pull2Op &op = P.p2ops[x];
+            op.pslot0 = pslots;
+            op.rot = (int32_t)units;
+            units += (int64_t)op.n12 * op.nblk1;
+            P.oplist.push_back(-1 - x);
+            for (int64_t tB = 0; tB < p2host[x].sizeB; ++tB) {
+                FinItem f = FinItem();
+                f.type = FIN_D;
+                f.dst_row = p2host[x].dstB_row + (int32_t)tB;
+                f.aux_row = p2host[x].mupB_row + (int32_t)tB;
+                f.slot0 = op.pslot0 + (int32_t)(tB * op.nblk1);
+                f.nslots = op.nblk1;
+                P.fins.push_back(f);
+            }
+            pslots += (int)(p2host[x].sizeB * op.nblk1);
+        }
         P.n_units += units;
         ph.op_end = (int32_t)P.oplist.size();
         ph.fin_end = (int32_t)P.fins.size();
@@ -471,6 +490,7 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
         P.max_mask_words = std::max(P.max_mask_words, mask_words);
         P.phases.push_back(ph);
     };
+    int64_t pull2_saved_entries = 0, pull2_partial_rows = 0;
     for (int d = maxdepth; d >= 0; --d) {  // Collect: deepest cliques first (src/JunctionTree.cpp:1240-1306)
         std::vector<int> ops;
         for (int c = 0; c < nc; ++c)
@@ -478,12 +498,84 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
         emit_phase(0, ops);
     }
     for (int d = 1; d <= maxdepth + 1; ++d) {  // Distribute (src/JunctionTree.cpp:1308-1333) + marginals as soon as ready
-        std::vector<int> ops;
+        std::vector<int> ops, p2;
+        std::vector<char> fused(nc, 0);
+        if (level && !getenv("FBN_NO_PULL2")) {
+            // two children A, B of one big parent whose separators cover every parent variable: one pass over the parent
+            for (int p = 0; p < nc; ++p) {
+                if (depth[p] != d - 1 || kids[p].size() < 2 || clq[p].size < 32768) continue;
+                const Table &X = clq[p];
+                int bestA = -1, bestB = -1;
+                int64_t best_slots = INT64_MAX;
+                for (int sa : kids[p])
+                    for (int sb : kids[p]) {
+                        if (sa == sb || fused[t.sep_child[sa]] || fused[t.sep_child[sb]]) continue;
+                        bool cover = true;
+                        int64_t n1 = 1, n2 = 1;
+                        for (size_t i = 0; i < X.vars.size(); ++i) {
+                            const bool a = sep[sa].find(X.vars[i]) >= 0, b = sep[sb].find(X.vars[i]) >= 0;
+                            if (!a && !b) cover = false;
+                            if (a && !b) n1 *= X.dims[i];
+                            if (b && !a) n2 *= X.dims[i];
+                        }
+                        if (!cover || n1 < 2 || n2 < 8) continue;
+                        const int64_t slots = sep[sb].size * ((n1 + kColBlock - 1) / kColBlock);
+                        if (slots < best_slots) { best_slots = slots; bestA = sa; bestB = sb; }
+                    }
+                if (bestA < 0 || best_slots > X.size / 3 || best_slots > ((int64_t)1 << 26)) continue;  // partials cost 2 rows each
+                std::vector<int> g12, g1, g2;
+                for (int i = 0; i < (int)X.vars.size(); ++i) {
+                    const bool a = sep[bestA].find(X.vars[i]) >= 0, b = sep[bestB].find(X.vars[i]) >= 0;
+                    (a && b ? g12 : a ? g1 : g2).push_back(i);
+                }
+                Table VA = X, VB = X;  // parent shape with the strides of separator A / B (0 outside)
+                for (size_t i = 0; i < X.vars.size(); ++i) {
+                    int pa = sep[bestA].find(X.vars[i]), pb = sep[bestB].find(X.vars[i]);
+                    VA.stride[i] = pa < 0 ? 0 : sep[bestA].stride[pa];
+                    VB.stride[i] = pb < 0 ? 0 : sep[bestB].stride[pb];
+                }
+                const int64_t xcols = ncols(p);
+                auto emit_tab = [&](const std::vector<int> &pos, const Table *T3, const Table *T4) {
+                    while (P.idx32.size() & 3) P.idx32.push_back(0);  // int4 alignment
+                    const int64_t off = (int64_t)P.idx32.size();
+                    std::vector<int32_t> x = enumerate_offsets(X, pos);
+                    std::vector<int32_t> e3 = T3 ? enumerate_offsets(*T3, pos) : std::vector<int32_t>(x.size(), 0);
+                    std::vector<int32_t> e4 = T4 ? enumerate_offsets(*T4, pos) : std::vector<int32_t>(x.size(), 0);
+                    for (size_t i = 0; i < x.size(); ++i) {
+                        P.idx32.push_back(x[i]);
+                        P.idx32.push_back((int32_t)(x[i] % xcols));
+                        P.idx32.push_back(e3[i]);
+                        P.idx32.push_back(e4[i]);
+                    }
+                    return off;
+                };
+                Pull2Op op = Pull2Op();
+                op.a_off = emit_tab(g12, &VA, &VB);
+                op.g1_off = emit_tab(g1, &VA, nullptr);
+                op.g2_off = emit_tab(g2, &VB, nullptr);
+                op.n12 = 1; op.n1 = 1; op.n2 = 1;
+                for (int i : g12) op.n12 *= X.dims[i];
+                for (int i : g1) op.n1 *= X.dims[i];
+                for (int i : g2) op.n2 *= X.dims[i];
+                op.nblk1 = (int32_t)((op.n1 + kColBlock - 1) / kColBlock);
+                op.src_row = cl_row(p);
+                op.fac_row = fac_row(p);
+                const int cA = t.sep_child[bestA], cB = t.sep_child[bestB];
+                op.mupA_row = mup_row(cA);
+                op.dstA_row = P.dn_row0 + (int32_t)sep_off[bestA];
+                p2host.push_back({P.dn_row0 + (int32_t)sep_off[bestB], mup_row(cB), sep[bestB].size});
+                p2.push_back((int)P.p2ops.size());
+                P.p2ops.push_back(op);
+                fused[cA] = fused[cB] = 1;
+                pull2_saved_entries += X.size;
+                pull2_partial_rows += best_slots;
+            }
+        }
         for (int c = 0; c < nc; ++c)
-            if (depth[c] == d) ops.push_back(dist_op[c]);
+            if (depth[c] == d && !fused[c]) ops.push_back(dist_op[c]);
         for (int v = 0; v < nv; ++v)
             if (marg_avail[v] == d - 1) ops.push_back(marg_op[v]);
-        if (!ops.empty()) emit_phase(1, ops);
+        if (!ops.empty() || !p2.empty()) emit_phase(1, ops, p2);
     }
 
     if (level) {  // partial-sum rows and per-CTA norm rows are appended to the tile
@@ -502,7 +594,7 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
                            24.0 * (double)P.parent_entries + 32.0 * (double)P.sep_entries + 8.0 * ref_marg_entries + 8.0 * (double)sd;
     // what the fused kernel must move per case: clique write (collect) + parent reads (distribute) + marginal reads
     // + separator up/down rows written once and read once + posterior/label output
-    P.kernel_bytes_per_case = 8.0 * (double)(P.clique_entries + P.parent_entries + P.marginal_entries) +
+    P.kernel_bytes_per_case = 8.0 * (double)(P.clique_entries + P.parent_entries - pull2_saved_entries + 2 * pull2_partial_rows + P.marginal_entries) +
                               32.0 * (double)P.sep_entries + 8.0 * (double)sd + 4.0;
     return "";
 }

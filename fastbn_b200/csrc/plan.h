@@ -75,6 +75,26 @@ struct PullOp {
 };
 
 
+// PULL2 (level mode): the distribute messages of TWO children A and B of one parent clique from ONE pass over the parent, when
+// every parent variable belongs to separator A or B. Parent variables split into G12 (in both), G1 (A only), G2 (B only).
+// Unit (a, b): G12 configuration a, block b of QB configurations of G1. The warp loops over the G2 configurations r:
+//   prod = src[x12[a] + x1[g] + x2[r]] * fac[col...]      (QB values g of the block)
+//   accA[g] += prod                      -> complete sums of QB entries of separator A (divided by mup, written to dn)
+//   partB(a, r, b) = sum_g prod          -> ONE partial row per r; separator B's entry (a, r) = sum over the blocks b, by a
+//                                           FIN_D item (reads nblk1 adjacent partial rows)
+// The parent is read once instead of twice; the partials add 2/QB of a read.
+struct Pull2Op {
+    int64_t a_off;    // idx32 (int4 per G12 configuration): {src row offset, fac row offset, A entry offset, B entry offset}
+    int64_t g1_off;   // idx32 (int4 per G1 configuration):  {src row offset, fac row offset, A entry offset, 0}
+    int64_t g2_off;   // idx32 (int4 per G2 configuration):  {src row offset, fac row offset, B entry offset, 0}
+    int32_t src_row, fac_row;
+    int32_t mupA_row, dstA_row;
+    int32_t n12, n1, n2, nblk1;
+    int32_t pslot0;   // partial slot of (B entry t, block b) = pslot0 + t * nblk1 + b
+    int32_t rot;
+    int32_t pad0, pad1;
+};
+
 enum FinType : int32_t { FIN_MUP = 0, FIN_NORM = 1, FIN_D = 2, FIN_MARG = 3 };
 struct FinItem {
     int32_t type;
@@ -87,7 +107,7 @@ struct FinItem {
 
 struct Phase {
     int32_t kind;  // 0 = collect ops, 1 = pull ops
-    int32_t op_begin, op_end;  // into oplist[] (indices into cops[] / pops[])
+    int32_t op_begin, op_end;  // into oplist[] (indices into cops[] / pops[]; < 0 in a pull phase: p2ops[-1 - entry])
     int32_t fin_begin, fin_end;
     int32_t n_normslots;
     int32_t mask_words;        // shared-memory words of evidence mask tables this phase builds
@@ -106,6 +126,7 @@ struct DevPlan {
     const int32_t *idx32;
     const CollectOp *cops;
     const PullOp *pops;
+    const Pull2Op *p2ops;   // oplist entries < 0 of a pull phase: p2ops[-1 - entry]
     const int32_t *oplist;
     const FinItem *fins;
     const Phase *phases;
@@ -132,6 +153,7 @@ struct HostPlan {
     std::vector<int32_t> idx32;
     std::vector<CollectOp> cops;
     std::vector<PullOp> pops;
+    std::vector<Pull2Op> p2ops;
     std::vector<int32_t> oplist;
     std::vector<FinItem> fins;
     std::vector<Phase> phases;

@@ -46,6 +46,34 @@ extern "C" int emu_run(const fbn_tree_desc *tree, int team, int64_t n_cases, con
             if (ph.kind == 0) std::fill(normacc.begin(), normacc.end(), 0.0);
             for (int oi = ph.op_begin; oi < ph.op_end; ++oi) {
                 const int o = P.oplist[oi];
+                if (ph.kind == 1 && o < 0) {  // PULL2: two children of one parent from one pass (plan.h)
+                    const Pull2Op &op = P.p2ops[-1 - o];
+                    const int32_t *A = &P.idx32[op.a_off], *G1 = &P.idx32[op.g1_off], *G2 = &P.idx32[op.g2_off];
+                    for (int a = 0; a < op.n12; ++a)
+                        for (int b = 0; b < op.nblk1; ++b) {
+                            std::vector<double> acc(kColBlock, 0.0);
+                            for (int r = 0; r < op.n2; ++r) {
+                                double pb = 0.0;
+                                for (int c = 0; c < kColBlock; ++c) {
+                                    const int g = b * kColBlock + c;
+                                    if (g >= op.n1) break;
+                                    const double prod = S[op.src_row + A[4 * a] + G1[4 * g] + G2[4 * r]] *
+                                                        S[op.fac_row + A[4 * a + 1] + G1[4 * g + 1] + G2[4 * r + 1]];
+                                    acc[c] += prod;
+                                    pb += prod;
+                                }
+                                part[op.pslot0 + (int64_t)(A[4 * a + 3] + G2[4 * r + 2]) * op.nblk1 + b] = pb;
+                            }
+                            for (int c = 0; c < kColBlock; ++c) {
+                                const int g = b * kColBlock + c;
+                                if (g >= op.n1) break;
+                                const int q = A[4 * a + 2] + G1[4 * g + 2];
+                                const double m = S[op.mupA_row + q];
+                                S[op.dstA_row + q] = m == 0.0 ? 0.0 : acc[c] / m;
+                            }
+                        }
+                    continue;
+                }
                 const int ncolsop = ph.kind == 0 ? P.cops[o].cols : P.pops[o].nT;
                 const int chunks = ph.kind == 0 ? P.cops[o].chunks : P.pops[o].chunks;
                 const int units = (ncolsop + kColBlock - 1) / kColBlock * chunks;
