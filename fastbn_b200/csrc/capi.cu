@@ -420,6 +420,10 @@ static int run_impl(fbn_plan *p, int64_t n_cases, const int64_t *ev_offsets, con
     int64_t chunk = (int64_t)(chunk_mb * 1048576.0 / (8.0 * sd));
     if (!getenv("FBN_CHUNK_MB")) chunk = std::max<int64_t>(chunk, (int64_t)p->grid * fbn::kLanes / 2);  // at least half a wave of tiles
     chunk = std::min<int64_t>(chunk, std::max<int64_t>(fbn::kLanes, (int64_t)(1024.0 * 1048576.0 / (8.0 * sd))));
+    {   // whole waves of resident tiles per chunk when a chunk holds more than one (a ragged last wave runs nearly empty)
+        const int64_t wave = (int64_t)p->grid * fbn::kLanes;
+        if (chunk > wave) chunk = chunk / wave * wave;
+    }
     chunk = (chunk + fbn::kLanes - 1) / fbn::kLanes * fbn::kLanes;
     chunk = std::min<int64_t>(chunk, (n_cases + fbn::kLanes - 1) / fbn::kLanes * fbn::kLanes);
     std::vector<int64_t> bounds{0};  // chunk boundaries (a ramp of smaller first chunks was measured: no gain)
