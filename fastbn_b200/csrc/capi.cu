@@ -234,17 +234,27 @@ extern "C" int fbn_plan_create(const fbn_tree_desc *tree, const fbn_plan_options
         fbn_plan_destroy(p);
         return fail(FBN_ERR_NOMEM, "cannot allocate tile scratch");
     }
-    CK(cudaMemset(p->scratch, 0, (size_t)p->scratch_bytes));
+    // from here on a failing CUDA call must release the half-built plan
+#define CKP(call)                                                                                      \
+    do {                                                                                               \
+        cudaError_t e__ = (call);                                                                      \
+        if (e__ != cudaSuccess) {                                                                      \
+            fbn_plan_destroy(p);                                                                       \
+            return fail(FBN_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e__));            \
+        }                                                                                              \
+    } while (0)
+    CKP(cudaMemset(p->scratch, 0, (size_t)p->scratch_bytes));
     if (level) {
-        CK(cudaMalloc((void **)&p->lamG, (size_t)resident * d.lam_words * 4));
+        CKP(cudaMalloc((void **)&p->lamG, (size_t)resident * d.lam_words * 4));
         p->plan_bytes += resident * (int64_t)d.lam_words * 4;
     }
-    CK(cudaStreamCreateWithFlags(&p->s_in, cudaStreamNonBlocking));
-    CK(cudaStreamCreateWithFlags(&p->s_k, cudaStreamNonBlocking));
-    CK(cudaStreamCreateWithFlags(&p->s_out, cudaStreamNonBlocking));
-    CK(cudaEventCreate(&p->ev0));
-    CK(cudaEventCreate(&p->ev1));
-    CK(cudaMalloc((void **)&p->score_out4, 4 * sizeof(double)));
+    CKP(cudaStreamCreateWithFlags(&p->s_in, cudaStreamNonBlocking));
+    CKP(cudaStreamCreateWithFlags(&p->s_k, cudaStreamNonBlocking));
+    CKP(cudaStreamCreateWithFlags(&p->s_out, cudaStreamNonBlocking));
+    CKP(cudaEventCreate(&p->ev0));
+    CKP(cudaEventCreate(&p->ev1));
+    CKP(cudaMalloc((void **)&p->score_out4, 4 * sizeof(double)));
+#undef CKP
     *out = p;
     return FBN_OK;
 }
