@@ -316,7 +316,7 @@ def main():
                          "traffic": traffic, "peak_source": peak_src,
                          "moved_gbs": info.kernel_bytes_per_case * n / (kern_ms * 1e-3) / 1e9, "alg_bytes_per_case": info.alg_bytes_per_case,
                          "kernel_bytes_per_case": info.kernel_bytes_per_case, "kernel_ms": kern_ms,
-                         "kernel": "jt_fused_kernel" if info.mode == capi.MODE_FUSED else "lvl_collect_kernel+lvl_pull_kernel (all launches of a step)"},
+                         "kernel": ("jt_flat_kernel" if info.flat_records else "jt_fused_kernel") if info.mode == capi.MODE_FUSED else "lvl_collect_kernel+lvl_pull_kernel (all launches of a step)"},
             "e2e": {"value": e2e_value, "unit": "cases/s", "h2d_bytes_per_step": int(st.h2d_bytes), "d2h_bytes_per_step": int(st.d2h_bytes),
                     "steps": e2e_steps, "launches_per_step": int(st.n_launches)},
             "gpu_launches": args.steps * launches_per_step,

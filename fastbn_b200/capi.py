@@ -37,7 +37,8 @@ class PlanInfo(C.Structure):
                 ("mode", C.c_int32), ("launches_per_wave", C.c_int32),
                 ("clique_entries", C.c_int64), ("separator_entries", C.c_int64), ("parent_entries", C.c_int64),
                 ("marginal_entries", C.c_int64), ("scratch_bytes", C.c_int64), ("plan_bytes", C.c_int64),
-                ("alg_bytes_per_case", C.c_double), ("kernel_bytes_per_case", C.c_double)]
+                ("alg_bytes_per_case", C.c_double), ("kernel_bytes_per_case", C.c_double),
+                ("flat_records", C.c_int32), ("reserved", C.c_int32)]
 
 
 class Stats(C.Structure):

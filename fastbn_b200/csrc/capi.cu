@@ -16,6 +16,10 @@ size_t fused_smem_bytes(const DevPlan &P);
 cudaError_t fused_prepare(const DevPlan &P, int *blocks_per_sm);
 cudaError_t fused_launch(const DevPlan &P, int grid, double *scratch, int64_t n_cases, const int64_t *ev_off, int64_t ev_base,
                          const int32_t *ev_vars, const int32_t *ev_vals, int32_t *labels, double *post, cudaStream_t st);
+size_t flat_smem_bytes(const DevPlan &P);
+cudaError_t flat_prepare(const DevPlan &P, int *blocks_per_sm);
+cudaError_t flat_launch(const DevPlan &P, int grid, double *scratch, int64_t n_cases, const int64_t *ev_off, int64_t ev_base,
+                        const int32_t *ev_vars, const int32_t *ev_vals, int32_t *labels, double *post, cudaStream_t st);
 cudaError_t level_launch(const DevPlan &P, const std::vector<Phase> &phases, int resident, double *scratch, uint32_t *lamG,
                          int64_t n_cases, const int64_t *ev_off, int64_t ev_base, const int32_t *ev_vars, const int32_t *ev_vals,
                          int32_t *labels, double *post, cudaStream_t st, int64_t *n_launch);
@@ -136,6 +140,8 @@ static cudaError_t launch_inference(fbn_plan *p, int64_t n_cases, const int64_t 
         return fbn::level_launch(p->dp, p->hp.phases, p->grid, p->scratch, p->lamG, n_cases, ev_off, ev_base, ev_vars, ev_vals,
                                  labels, post, st, n_launch);
     *n_launch = 1;
+    if (p->dp.flat)
+        return fbn::flat_launch(p->dp, p->grid, p->scratch, n_cases, ev_off, ev_base, ev_vars, ev_vals, labels, post, st);
     return fbn::fused_launch(p->dp, p->grid, p->scratch, n_cases, ev_off, ev_base, ev_vars, ev_vals, labels, post, st);
 }
 
@@ -194,12 +200,13 @@ extern "C" int fbn_plan_create(const fbn_tree_desc *tree, const fbn_plan_options
     fbn::DevPlan &d = p->dp;
     int rc;
 #define UP(field) if ((rc = upload(p, h.field, &d.field)) != FBN_OK) { fbn_plan_destroy(p); return rc; }
-    UP(pot) UP(lam16) UP(idx32) UP(cops) UP(pops) UP(p2ops) UP(oplist) UP(fins) UP(phases) UP(vars)
+    UP(pot) UP(lam16) UP(idx32) UP(flatc) UP(flatp) UP(cops) UP(pops) UP(p2ops) UP(oplist) UP(fins) UP(phases) UP(vars)
 #undef UP
     d.n_phases = (int32_t)h.phases.size();
     d.n_vars = h.n_vars; d.sum_dims = h.sum_dims; d.query_var = h.query_var;
     d.tile_rows = h.tile_rows; d.mg_row0 = h.mg_row0;
     d.max_normslots = h.max_normslots; d.max_pslots = h.max_pslots; d.max_mask_words = h.max_mask_words; d.team = h.team; d.cb = h.cb;
+    d.flat = h.flat ? 1 : 0;
     d.part_row0 = h.part_row0; d.normpart_row0 = h.normpart_row0; d.nb_max = h.nb_max; d.lam_words = h.sum_dims + h.n_vars;
 
     p->n_sms = prop.multiProcessorCount;
@@ -211,11 +218,11 @@ extern "C" int fbn_plan_create(const fbn_tree_desc *tree, const fbn_plan_options
         p->launches_per_wave = 2;
         for (const fbn::Phase &ph : h.phases) p->launches_per_wave += 1 + (ph.fin_end > ph.fin_begin ? 1 : 0);
     } else {
-        if (fbn::fused_smem_bytes(d) > (size_t)prop.sharedMemPerBlockOptin) {
+        if ((d.flat ? fbn::flat_smem_bytes(d) : fbn::fused_smem_bytes(d)) > (size_t)prop.sharedMemPerBlockOptin) {
             fbn_plan_destroy(p);
             return fail(FBN_ERR_INVALID, "tree needs more shared memory per tile than the device has");
         }
-        ce = fbn::fused_prepare(d, &p->blocks_per_sm);
+        ce = d.flat ? fbn::flat_prepare(d, &p->blocks_per_sm) : fbn::fused_prepare(d, &p->blocks_per_sm);
         if (ce != cudaSuccess) {
             fbn_plan_destroy(p);
             return fail(FBN_ERR_CUDA, std::string("kernel setup failed (is this an sm_100 device?): ") + cudaGetErrorString(ce));
@@ -298,6 +305,7 @@ extern "C" int fbn_plan_get_info(const fbn_plan *p, fbn_plan_info *o) {
     o->clique_entries = h.clique_entries; o->separator_entries = h.sep_entries; o->parent_entries = h.parent_entries;
     o->marginal_entries = h.marginal_entries; o->scratch_bytes = p->scratch_bytes; o->plan_bytes = p->plan_bytes;
     o->alg_bytes_per_case = h.alg_bytes_per_case; o->kernel_bytes_per_case = h.kernel_bytes_per_case;
+    o->flat_records = p->dp.flat;
     return FBN_OK;
 }
 

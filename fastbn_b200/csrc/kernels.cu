@@ -74,9 +74,14 @@ __device__ __forceinline__ void pull_op(const DevPlan &P, const PullOp &__restri
     for (int u = (warp - op.rot) & (TEAM - 1); u < units; u += TEAM) {
         int q0, nq, ck, r0, r1;
         pull_unit<kColBlock>(op, u, q0, nq, ck, r0, r1);
-        double acc[kColBlock];
+        double acc[kColBlock], mup[kColBlock];
+        const bool divide = op.chunks == 1 && op.kind == 1;
 #pragma unroll
-        for (int c = 0; c < kColBlock; ++c) acc[c] = 0.0;
+        for (int c = 0; c < kColBlock; ++c) {
+            acc[c] = 0.0;
+            // the divisor is requested before the sum is formed: one memory latency less on the unit's critical path
+            mup[c] = divide ? *row_ptr(S, op.mup_row + min(q0 + c, op.nT - 1)) : 1.0;
+        }
         pull_block<kColBlock, kFusedStream>(P, op, S, q0, r0, r1, acc);
 #pragma unroll
         for (int c = 0; c < kColBlock; ++c)
@@ -85,7 +90,7 @@ __device__ __forceinline__ void pull_op(const DevPlan &P, const PullOp &__restri
                 if (op.chunks > 1) {
                     sm.part[(op.pslot0 + q * op.chunks + ck) * kLanes + lane] = acc[c];
                 } else if (op.kind == 1) {
-                    const double m = *row_ptr(S, op.mup_row + q);
+                    const double m = mup[c];
                     *row_ptr(S, op.dst_row + q) = (m == 0.0) ? 0.0 : acc[c] / m;  // TableDivision 0-guard, PotentialTable.cpp:718-734
                 } else {
                     *row_ptr(S, op.dst_row + q) = acc[c];

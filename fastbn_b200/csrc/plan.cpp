@@ -7,6 +7,7 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <numeric>
 #include <string>
 
@@ -585,6 +586,44 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
         int64_t rows = (int64_t)P.normpart_row0 + (int64_t)P.max_normslots * P.nb_max;
         if (rows > ((int64_t)1 << 30)) return "tree too large: more than 2^30 scratch rows per tile";
         P.tile_rows = (int32_t)rows;
+    }
+
+    // ---- flat records (small trees run by one warp per tile, jt_flat_kernel): one record per clique entry / per (target, rest)
+    //      pair with ABSOLUTE scratch rows, so the kernel's inner loops are a record load, the data loads and the arithmetic
+    for (auto &op : P.cops) op.flat_off = -1;
+    for (auto &op : P.pops) op.flat_off = -1;
+    if (!level && team == 1 && !getenv("FBN_NO_FLAT")) {
+        bool ok = true;
+        for (const auto &op : P.cops) ok = ok && op.nchild <= 4 && op.rowmask_off >= 0 && op.chunks == 1;
+        for (const auto &op : P.pops) ok = ok && op.chunks == 1;
+        if (ok) {
+            for (auto &op : P.cops) {
+                while (P.flatc.size() & 3) P.flatc.push_back(0);
+                op.flat_off = (int64_t)P.flatc.size();
+                const int nk = op.nchild;
+                for (int64_t j = 0; j < op.cols; ++j)
+                    for (int64_t r = 0; r < op.rows; ++r) {
+                        int32_t m[4] = {0, 0, 0, 0};
+                        for (int k = 0; k < nk; ++k)
+                            m[k] = P.idx32[(size_t)(op.rowpart_off + r * nk + k)] + P.idx32[(size_t)(op.colpart_off + j * nk + k)];
+                        const double pv = P.pot[(size_t)(op.pot_off + r * op.cols + j)];
+                        int32_t bits[2];
+                        memcpy(bits, &pv, 8);
+                        P.flatc.push_back(bits[0]); P.flatc.push_back(bits[1]); P.flatc.push_back(m[0]); P.flatc.push_back(m[1]);
+                        if (nk > 2) { P.flatc.push_back(m[2]); P.flatc.push_back(m[3]); P.flatc.push_back(0); P.flatc.push_back(0); }
+                    }
+            }
+            for (auto &op : P.pops) {
+                if (P.flatp.size() & 1) P.flatp.push_back(0);
+                op.flat_off = (int64_t)P.flatp.size();
+                for (int64_t q = 0; q < op.nT; ++q)
+                    for (int64_t r = 0; r < op.nR; ++r) {
+                        P.flatp.push_back(op.src_row + P.idx32[(size_t)(op.tbase_off + 2 * q)] + P.idx32[(size_t)(op.trest_off + 2 * r)]);
+                        P.flatp.push_back(op.fac_row + P.idx32[(size_t)(op.tbase_off + 2 * q + 1)] + P.idx32[(size_t)(op.trest_off + 2 * r + 1)]);
+                    }
+            }
+            P.flat = true;
+        }
     }
 
     // ---- byte accounting ----

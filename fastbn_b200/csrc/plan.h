@@ -37,6 +37,10 @@ struct CollectOp {
     int64_t rowpart_off;  // into idx32[]: rows*nchild  (absolute scratch row of child k's message, row part)
     int64_t colpart_off;  // into idx32[]: cols*nchild  (column part)
     int64_t invrow_off;   // into idx32[]: nchild absolute scratch rows holding 1/norm of each child clique
+    int64_t flat_off;     // flat plans (small trees, one warp per tile): into flatc[] (int4 records), -1 = none. One record per
+                          //   entry, COLUMN-major (all rows of column 0, then column 1, ...): {pristine potential (2 x 32 bit),
+                          //   absolute scratch row of child 0's message entry, of child 1's}; ops with 3-4 children use two
+                          //   int4 per entry, the second = {child 2's row, child 3's row, 0, 0}
     int64_t perm_off;     // into idx32[]: visiting order of the column blocks (unit u works on block perm[u / chunks]), -1 =
                           //   storage order. The planner orders blocks so that blocks visited together gather the same child
                           //   message rows (column variables outside the child separators vary fastest): keeps the gathers in L2.
@@ -64,6 +68,8 @@ struct CollectOp {
 struct PullOp {
     int64_t tbase_off;  // into idx32[] (int2 pairs): nT pairs
     int64_t trest_off;  // into idx32[] (int2 pairs): nR pairs
+    int64_t flat_off;   // flat plans: into flatp[] (int2 records), -1 = none: nT x nR pairs {absolute src row, absolute fac row},
+                        //   target-major
     int32_t src_row;
     int32_t fac_row;
     int32_t mup_row;    // kind 1 only
@@ -124,6 +130,8 @@ struct DevPlan {
     const double *pot;
     const uint16_t *lam16;
     const int32_t *idx32;
+    const int32_t *flatc;   // flat plans: COLLECT entry records (int4 aligned)
+    const int32_t *flatp;   // flat plans: PULL pair records (int2 aligned)
     const CollectOp *cops;
     const PullOp *pops;
     const Pull2Op *p2ops;   // oplist entries < 0 of a pull phase: p2ops[-1 - entry]
@@ -144,6 +152,7 @@ struct DevPlan {
     int32_t normpart_row0;  // first of max_normslots * nb_max rows: row (normslot * nb_max + cta)
     int32_t nb_max;         // CTAs per tile a phase may be launched with
     int32_t lam_words;      // sum_dims + n_vars
+    int32_t flat;           // 1: every op has flat records (jt_flat_kernel)
 };
 
 // --- host-side plan ----------------------------------------------------------------------------------------------
@@ -151,6 +160,8 @@ struct HostPlan {
     std::vector<double> pot;
     std::vector<uint16_t> lam16;
     std::vector<int32_t> idx32;
+    std::vector<int32_t> flatc, flatp;
+    bool flat = false;
     std::vector<CollectOp> cops;
     std::vector<PullOp> pops;
     std::vector<Pull2Op> p2ops;

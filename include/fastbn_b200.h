@@ -89,6 +89,8 @@ typedef struct fbn_plan_info {
     int64_t plan_bytes;          /* device bytes of per-tree constants */
     double alg_bytes_per_case;   /* SURVEY.md 8(d) algorithmic bytes per case (fixed-shape fp64 tables), evidence excluded */
     double kernel_bytes_per_case;/* bytes the fused kernel itself moves per case (scratch r/w + output) */
+    int32_t flat_records;        /* 1: small tree run by jt_flat_kernel (one warp per tile, per-entry records), else 0 */
+    int32_t reserved;
 } fbn_plan_info;
 
 typedef struct fbn_stats {

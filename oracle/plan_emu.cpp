@@ -28,6 +28,7 @@ extern "C" int emu_run(const fbn_tree_desc *tree, int team, int64_t n_cases, con
         info[3] = P.max_pslots; info[4] = P.max_normslots; info[5] = P.tile_rows; info[6] = P.n_levels; info[7] = P.parent_entries;
     }
     const int kColBlock = P.cb;
+    const bool use_flat = P.flat;  // team 1 fused plans of small trees carry flat records: interpret those
     std::vector<double> S((size_t)P.tile_rows);
     std::vector<char> lam((size_t)P.sum_dims), obs((size_t)P.n_vars);
     std::vector<double> normacc((size_t)std::max(1, P.max_normslots) * team), part((size_t)std::max(1, P.max_pslots));
@@ -98,9 +99,18 @@ extern "C" int emu_run(const fbn_tree_desc *tree, int team, int64_t n_cases, con
                             bool m = cm;
                             for (int i = 0; i < op.nrest; ++i) m = m && lam[P.lam16[op.rowlam_off + (int64_t)r * op.nrest + i]];
                             const int64_t e = (int64_t)r * op.cols + j;
-                            double v = P.pot[op.pot_off + e] * scale;
-                            for (int k = 0; k < op.nchild; ++k)
-                                v *= S[P.idx32[op.rowpart_off + (int64_t)r * op.nchild + k] + P.idx32[op.colpart_off + (int64_t)j * op.nchild + k]];
+                            double v;
+                            if (use_flat) {  // the flat records of jt_flat_kernel (column-major, absolute message rows)
+                                const int64_t x = op.flat_off + ((int64_t)j * op.rows + r) * (op.nchild > 2 ? 8 : 4);
+                                double pv;
+                                memcpy(&pv, &P.flatc[x], 8);
+                                v = pv * scale;
+                                for (int k = 0; k < op.nchild; ++k) v *= S[P.flatc[x + 2 + k]];  // {pot, m0, m1} {m2, m3, 0, 0}
+                            } else {
+                                v = P.pot[op.pot_off + e] * scale;
+                                for (int k = 0; k < op.nchild; ++k)
+                                    v *= S[P.idx32[op.rowpart_off + (int64_t)r * op.nchild + k] + P.idx32[op.colpart_off + (int64_t)j * op.nchild + k]];
+                            }
                             if (!m) v = 0.0;
                             S[op.cl_row + e] = v;
                             acc += v;
@@ -115,8 +125,14 @@ extern "C" int emu_run(const fbn_tree_desc *tree, int team, int64_t n_cases, con
                         if (op.chunks > 1) { r0 = ck * op.rows_per_chunk; r1 = std::min(op.nR, r0 + op.rows_per_chunk); }
                         const int32_t bx = P.idx32[op.tbase_off + 2 * q], by = P.idx32[op.tbase_off + 2 * q + 1];
                         double acc = 0.0;
-                        for (int r = r0; r < r1; ++r)
-                            acc += S[op.src_row + bx + P.idx32[op.trest_off + 2 * r]] * S[op.fac_row + by + P.idx32[op.trest_off + 2 * r + 1]];
+                        for (int r = r0; r < r1; ++r) {
+                            if (use_flat) {
+                                const int64_t x = op.flat_off + 2 * ((int64_t)q * op.nR + r);
+                                acc += S[P.flatp[x]] * S[P.flatp[x + 1]];
+                            } else {
+                                acc += S[op.src_row + bx + P.idx32[op.trest_off + 2 * r]] * S[op.fac_row + by + P.idx32[op.trest_off + 2 * r + 1]];
+                            }
+                        }
                         if (op.chunks > 1) part[op.pslot0 + q * op.chunks + ck] = acc;
                         else if (op.kind == 1) { double m = S[op.mup_row + q]; S[op.dst_row + q] = m == 0.0 ? 0.0 : acc / m; }
                         else S[op.dst_row + q] = acc;

@@ -93,3 +93,17 @@ def test_plan_with_permuted_block_order_on_pigs_shape(team):
     post, lab, info = emu.run(t, team, g["ev_off"][:n + 1], g["ev_vars"][:k], g["ev_vals"][:k])
     assert np.nanmax(np.abs(post - g["post"][:n])) <= 1e-9
     assert np.array_equal(lab, g["labels"][:n])
+
+
+@pytest.mark.parametrize("no_flat", [False, True])
+def test_flat_records_of_small_trees(alarm_tree, no_flat, monkeypatch):
+    """team 1 plans of small trees carry flat per-entry records (jt_flat_kernel); the emulator interprets them when present.
+    Both forms of the plan must reproduce the reference."""
+    if no_flat:
+        monkeypatch.setenv("FBN_NO_FLAT", "1")
+    for name in ["alarm_1k_ref", "alarm_edge_ref"]:
+        g = load_golden(name)
+        post, lab, _ = emu.run(alarm_tree, 1, g["ev_off"], g["ev_vars"], g["ev_vals"])
+        assert np.array_equal(np.isnan(post), np.isnan(g["post"]))
+        assert np.nanmax(np.abs(post - g["post"])) <= 1e-9
+        assert np.array_equal(lab, g["labels"])
