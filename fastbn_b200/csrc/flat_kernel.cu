@@ -7,6 +7,8 @@
 // column, end of a target's sum) are warp-uniform counters. ~2.5x fewer instructions per case than the generic kernel, and
 // four independent entries in flight per warp instead of one dependent chain per column.
 #include <cstdint>
+#include <type_traits>
+
 #include <cuda_runtime.h>
 
 #include "ops.cuh"
@@ -44,11 +46,12 @@ __device__ __forceinline__ void flat_collect(const DevPlan &P, const CollectOp &
     int r = 0, j = 0;
     bool con = (cmt[0] & lanebit) != 0;
     double acc = 0.0, nacc = 0.0;
-    for (int e0 = 0; e0 < n; e0 += kBatchC) {
+    auto batch = [&](int e0, auto full) {
+        constexpr bool kFull = decltype(full)::value;  // full batch: no bounds checks
         int4 A[kBatchC], B[kBatchC];
 #pragma unroll
         for (int i = 0; i < kBatchC; ++i) {
-            const int e = min(e0 + i, n - 1);
+            const int e = kFull ? e0 + i : min(e0 + i, n - 1);
             A[i] = __ldg(rec + (int64_t)e * kStride);
             if (NC > 2) B[i] = __ldg(rec + (int64_t)e * kStride + 1);
         }
@@ -62,7 +65,7 @@ __device__ __forceinline__ void flat_collect(const DevPlan &P, const CollectOp &
         }
 #pragma unroll
         for (int i = 0; i < kBatchC; ++i) {
-            if (e0 + i < n) {
+            if (kFull || e0 + i < n) {
                 double v = __hiloint2double(A[i].y, A[i].x) * scale;
 #pragma unroll
                 for (int k = 0; k < NC; ++k) v *= m[i][k];
@@ -81,7 +84,10 @@ __device__ __forceinline__ void flat_collect(const DevPlan &P, const CollectOp &
                 }
             }
         }
-    }
+    };
+    int e0 = 0;
+    for (; e0 + kBatchC <= n; e0 += kBatchC) batch(e0, std::true_type());
+    if (e0 < n) batch(e0, std::false_type());
     *row_ptr(S, op.inv_row) = 1.0 / nacc;  // PotentialTableBase::Normalize as a scalar applied by the consumers
 }
 
@@ -92,10 +98,11 @@ __device__ __forceinline__ void flat_pull(const DevPlan &P, const PullOp &__rest
     double *dst = row_ptr(S, op.dst_row);
     int r = 0, q = 0;
     double acc = 0.0;
-    for (int e0 = 0; e0 < n; e0 += kBatchP) {
+    auto batch = [&](int e0, auto full) {
+        constexpr bool kFull = decltype(full)::value;  // full batch: no bounds checks
         int2 t[kBatchP];
 #pragma unroll
-        for (int i = 0; i < kBatchP; ++i) t[i] = __ldg(rec + min(e0 + i, n - 1));
+        for (int i = 0; i < kBatchP; ++i) t[i] = __ldg(rec + (kFull ? e0 + i : min(e0 + i, n - 1)));
         double s[kBatchP], f[kBatchP];
 #pragma unroll
         for (int i = 0; i < kBatchP; ++i) {
@@ -104,7 +111,7 @@ __device__ __forceinline__ void flat_pull(const DevPlan &P, const PullOp &__rest
         }
 #pragma unroll
         for (int i = 0; i < kBatchP; ++i) {
-            if (e0 + i < n) {
+            if (kFull || e0 + i < n) {
                 acc += s[i] * f[i];
                 if (++r == nR) {
                     dst[(int64_t)q * kLanes] = acc;
@@ -114,7 +121,10 @@ __device__ __forceinline__ void flat_pull(const DevPlan &P, const PullOp &__rest
                 }
             }
         }
-    }
+    };
+    int e0 = 0;
+    for (; e0 + kBatchP <= n; e0 += kBatchP) batch(e0, std::true_type());
+    if (e0 < n) batch(e0, std::false_type());
     if (op.kind == 1) {  // m_down = sum / m_up with the reference's 0 guard (TableDivision, PotentialTable.cpp:718-734)
         const double *mup = row_ptr(S, op.mup_row);
         for (int q0 = 0; q0 < nT; q0 += kBatchP) {
@@ -134,18 +144,28 @@ __device__ __forceinline__ void flat_pull(const DevPlan &P, const PullOp &__rest
 
 }  // namespace
 
-__global__ void __launch_bounds__(32, 32) jt_flat_kernel(const DevPlan P, double *__restrict__ scratch, int64_t n_cases,
+#ifndef FBN_FLAT_OCC
+#define FBN_FLAT_OCC 32   // resident warps per SM the register allocation is bounded for
+#endif
+#ifndef FBN_FLAT_WPC
+#define FBN_FLAT_WPC 1    // warps per CTA; every warp runs its own tiles (an SM holds at most 32 CTAs, so > 32 warps need WPC > 1)
+#endif
+constexpr int kWpc = FBN_FLAT_WPC;
+__global__ void __launch_bounds__(32 * kWpc, FBN_FLAT_OCC / kWpc) jt_flat_kernel(const DevPlan P, double *__restrict__ scratch, int64_t n_cases,
                                                          const int64_t *__restrict__ ev_off, int64_t ev_base,
                                                          const int32_t *__restrict__ ev_vars, const int32_t *__restrict__ ev_vals,
                                                          int32_t *__restrict__ labels, double *__restrict__ post, int64_t n_tiles) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    uint32_t *lam = reinterpret_cast<uint32_t *>(smem_raw);  // [sum_dims] bit l: state allowed for case l; then [n_vars] observed
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const size_t lam_bytes = ((size_t)(P.sum_dims + P.n_vars) * 4 + 15) & ~(size_t)15;
+    const size_t warp_bytes = lam_bytes + (((size_t)P.max_mask_words * 4 + 15) & ~(size_t)15);
+    uint32_t *lam = reinterpret_cast<uint32_t *>(smem_raw + warp * warp_bytes);  // [sum_dims] bit l: state allowed for case l; then [n_vars] observed
     uint32_t *obs = lam + P.sum_dims;
-    uint32_t *mask = reinterpret_cast<uint32_t *>(smem_raw + (((size_t)(P.sum_dims + P.n_vars) * 4 + 15) & ~(size_t)15));
-    const int lane = threadIdx.x;
-    double *S = scratch + (int64_t)blockIdx.x * P.tile_rows * kLanes + lane;  // lane-private column of this warp's tile
+    uint32_t *mask = reinterpret_cast<uint32_t *>(smem_raw + warp * warp_bytes + lam_bytes);
+    const int64_t slot = (int64_t)blockIdx.x * kWpc + warp;  // this warp's resident tile
+    double *S = scratch + slot * P.tile_rows * kLanes + lane;  // lane-private column of this warp's tile
 
-    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    for (int64_t tile = slot; tile < n_tiles; tile += (int64_t)gridDim.x * kWpc) {
         // ---- evidence -> lambda bit words (LoadDiscreteEvidence, src/JunctionTree.cpp:316-383, mask form :386-457)
         __syncwarp();
         for (int i = lane; i < P.sum_dims + P.n_vars; i += 32) lam[i] = i < P.sum_dims ? 0xffffffffu : 0u;
@@ -227,11 +247,15 @@ size_t flat_smem_bytes(const DevPlan &P) {
     return o + (((size_t)P.max_mask_words * 4 + 15) & ~(size_t)15);
 }
 
-cudaError_t flat_prepare(const DevPlan &P, int *blocks_per_sm) {
-    const size_t smem = flat_smem_bytes(P);
+// *tiles_per_sm = resident warps (tiles) per SM
+cudaError_t flat_prepare(const DevPlan &P, int *tiles_per_sm) {
+    const size_t smem = flat_smem_bytes(P) * kWpc;
     cudaError_t e = cudaFuncSetAttribute(jt_flat_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, jt_flat_kernel, 32, smem);
+    int blocks = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks, jt_flat_kernel, 32 * kWpc, smem);
+    *tiles_per_sm = blocks * kWpc;
+    return e;
 }
 
 cudaError_t flat_launch(const DevPlan &P, int grid, double *scratch, int64_t n_cases, const int64_t *ev_off, int64_t ev_base,
@@ -239,7 +263,8 @@ cudaError_t flat_launch(const DevPlan &P, int grid, double *scratch, int64_t n_c
     const int64_t n_tiles = (n_cases + kLanes - 1) / kLanes;
     if (n_tiles == 0) return cudaSuccess;
     if (grid > n_tiles) grid = (int)n_tiles;
-    jt_flat_kernel<<<grid, 32, flat_smem_bytes(P), st>>>(P, scratch, n_cases, ev_off, ev_base, ev_vars, ev_vals, labels, post, n_tiles);
+    grid = (grid + kWpc - 1) / kWpc;  // `grid` counts resident tiles (warps)
+    jt_flat_kernel<<<grid, 32 * kWpc, flat_smem_bytes(P) * kWpc, st>>>(P, scratch, n_cases, ev_off, ev_base, ev_vars, ev_vals, labels, post, n_tiles);
     return cudaGetLastError();
 }
 
