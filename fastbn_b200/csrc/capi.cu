@@ -170,7 +170,9 @@ extern "C" int fbn_plan_create(const fbn_tree_desc *tree, const fbn_plan_options
     CK(cudaGetDeviceProperties(&prop, dev));
     size_t free_b = 0, total_b = 0;
     CK(cudaMemGetInfo(&free_b, &total_b));
-    const int64_t budget = (int64_t)(free_b * 0.45);  // leave room for the caller's evidence / posterior buffers
+    double frac = 0.45;  // of the free device memory for the tile scratch: leaves room for the caller's evidence / posterior buffers
+    if (const char *e = getenv("FBN_SCRATCH_FRAC")) frac = std::min(0.9, std::max(0.05, atof(e)));
+    const int64_t budget = (int64_t)(free_b * frac);
     const double entries = tree_entries(tree);
     int mode = opt ? opt->mode : FBN_MODE_AUTO;
     if (const char *e = getenv("FBN_MODE")) mode = atoi(e);
