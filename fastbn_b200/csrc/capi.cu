@@ -425,9 +425,15 @@ static int run_impl(fbn_plan *p, int64_t n_cases, const int64_t *ev_offsets, con
     if (stats) memset(stats, 0, sizeof(*stats));
     if (out4) { out4[0] = out4[1] = out4[2] = out4[3] = 0.0; }
     if (n_cases == 0) return FBN_OK;
-    for (int64_t i = 0; i < n_cases; ++i)
-        if (ev_offsets[i + 1] < ev_offsets[i]) return fail(FBN_ERR_INVALID, "ev_offsets must be non-decreasing");
+    if (ev_offsets[n_cases] < ev_offsets[0]) return fail(FBN_ERR_INVALID, "ev_offsets must be non-decreasing");
     if (ev_offsets[n_cases] > ev_offsets[0] && (!ev_vars || !ev_vals)) return fail(FBN_ERR_INVALID, "null evidence arrays");
+    // the per-case monotonicity check runs chunk by chunk inside the pipeline (a 10^6-entry scan up front would delay the
+    // first copy by ~1 ms); chunk c is checked before anything of it is enqueued
+    auto offsets_ok = [&](int64_t c0, int64_t c1) {
+        for (int64_t i = c0; i < c1; ++i)
+            if (ev_offsets[i + 1] < ev_offsets[i]) return false;
+        return true;
+    };
     const int sd = p->hp.sum_dims;
     const bool want_post_host = posteriors_out != nullptr;
     const bool want_post = want_post_host || want_gold;  // scoring reads the posteriors on the device
@@ -450,7 +456,8 @@ static int run_impl(fbn_plan *p, int64_t n_cases, const int64_t *ev_offsets, con
     while (bounds.back() < n_cases) bounds.push_back(std::min(n_cases, bounds.back() + chunk));
     const int64_t n_chunks = (int64_t)bounds.size() - 1;
     int64_t max_ev = 1;
-    for (int64_t c = 0; c < n_chunks; ++c) max_ev = std::max(max_ev, ev_offsets[bounds[c + 1]] - ev_offsets[bounds[c]]);
+    if (!offsets_ok(0, bounds[1])) return fail(FBN_ERR_INVALID, "ev_offsets must be non-decreasing");
+    for (int64_t c = 0; c < n_chunks; ++c) max_ev = std::max(max_ev, std::max<int64_t>(0, ev_offsets[bounds[c + 1]] - ev_offsets[bounds[c]]));
     const bool stage_in = !(is_pinned(ev_offsets) && is_pinned(ev_vars) && is_pinned(ev_vals));
     const bool stage_out = !(is_pinned(labels_out) && is_pinned(posteriors_out));
     struct Pending { int64_t c0 = 0, n = 0; bool active = false; } pend[kNBuf];
@@ -471,6 +478,11 @@ static int run_impl(fbn_plan *p, int64_t n_cases, const int64_t *ev_offsets, con
         ChunkBuf &b = p->buf[bi];
         if ((rc = drain(bi)) != FBN_OK) return rc;
         const int64_t c0 = bounds[c], n = bounds[c + 1] - c0;
+        if (c > 0 && !offsets_ok(c0, c0 + n)) {  // earlier chunks are in flight: let them finish, then report
+            for (int b2 = 0; b2 < kNBuf; ++b2) drain(b2);
+            cudaStreamSynchronize(p->s_k);
+            return fail(FBN_ERR_INVALID, "ev_offsets must be non-decreasing");
+        }
         const int64_t e0 = ev_offsets[c0], ne = ev_offsets[c0 + n] - e0;
         if ((rc = ensure_chunk(b, chunk, max_ev, sd, want_post, want_post_host, stage_in, stage_out, want_gold, stage_gold)) != FBN_OK) return rc;
         const int64_t *src_off = ev_offsets + c0;

@@ -77,6 +77,20 @@ def test_empty_batch_and_labels_only(plan):
     assert post is None and np.array_equal(labels, g["labels"])
 
 
+def test_decreasing_offsets_are_rejected_in_any_chunk(plan, monkeypatch):
+    """ev_offsets are checked chunk by chunk inside the pipeline: a bad entry in the first or in a later chunk fails
+    the call with FBN_ERR_INVALID, and the plan stays usable."""
+    g = load_golden("alarm_synth_4k_ref")
+    monkeypatch.setenv("FBN_CHUNK_MB", "1")  # ~1.2k ALARM cases per chunk -> several chunks
+    for where in (3, len(g["ev_off"]) - 5):
+        off = g["ev_off"].copy()
+        off[where] = off[where + 1] + 1
+        with pytest.raises(capi.FastBNError, match="non-decreasing"):
+            plan.run(off, g["ev_vars"], g["ev_vals"])
+    labels, post, _ = plan.run(g["ev_off"], g["ev_vars"], g["ev_vals"])
+    assert np.array_equal(labels, g["labels"]) and np.nanmax(np.abs(post - g["post"])) <= TOL
+
+
 def test_impossible_evidence_gives_nan_like_reference(plan, alarm_tree):
     """value >= dim wipes every table: the reference's Normalize divides 0/0 -> NaN (no zero guard)."""
     off = np.array([0, 1], np.int64)
