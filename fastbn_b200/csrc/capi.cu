@@ -129,6 +129,9 @@ static int pick_team(double entries) {
     if (entries <= 8192) return 1;
     if (entries <= 32768) return 4;
     if (entries <= 131072) return 8;
+    // PIGS shape (265 k entries): 2 CTAs x 16 warps per SM, 472 k cases/s against 452 k with 1 x 32 (round 1f; possible since the
+    // clique-norm shares moved from shared memory to scratch rows); bigger tiles: few fit, so all 32 warps work on one
+    if (entries <= 524288) return 16;
     return 32;
 }
 

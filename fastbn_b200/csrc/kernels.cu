@@ -15,18 +15,24 @@ namespace fbn {
 #define FBN_FUSED_STREAM 1
 #endif
 constexpr bool kFusedStream = FBN_FUSED_STREAM != 0;
+// tuning experiments: ops as separate functions (own register allocation) instead of inlined into the phase loop
+#ifdef FBN_OPS_NOINLINE
+#define FBN_OP_INLINE __noinline__
+#else
+#define FBN_OP_INLINE __forceinline__
+#endif
 
 struct Smem {
     uint32_t *lam;    // [sum_dims]  bit l set <=> state allowed for case l of the tile
     uint32_t *obs;    // [n_vars]    bit l set <=> variable observed in case l
     uint32_t *mask;   // [max_mask_words] per-phase evidence mask tables: one word per clique row / column
-    double *normacc;  // [max_normslots][TEAM][32]
+    double *normacc;  // TEAM == 1: [max_normslots][32]; TEAM > 1: unused (norm shares live in scratch rows, normpart_row0)
     double *part;     // [max_pslots][32]
 };
 
 // COLLECT op: all units (column block x row chunk) of one clique that this warp owns.
 template <int TEAM, int kColBlock>
-__device__ __forceinline__ void collect_op(const DevPlan &P, const CollectOp &__restrict__ op, double *S, const Smem &sm, int lane, int warp) {
+__device__ FBN_OP_INLINE void collect_op(const DevPlan &P, const CollectOp &__restrict__ op, double *S, const Smem &sm, int lane, int warp) {
     double scale = 1.0;
     const int32_t *__restrict__ invrows = P.idx32 + op.invrow_off;
     for (int k = 0; k < op.nchild; ++k) scale *= *row_ptr(S, __ldg(invrows + k));
@@ -64,12 +70,13 @@ __device__ __forceinline__ void collect_op(const DevPlan &P, const CollectOp &__
                 nacc += acc[c];
             }
     }
-    sm.normacc[(op.normslot * TEAM + warp) * kLanes + lane] = nacc;
+    if (TEAM == 1) sm.normacc[op.normslot * kLanes + lane] = nacc;
+    else *row_ptr(S, P.normpart_row0 + op.normslot * TEAM + warp) = nacc;
 }
 
 // PULL op: out[q] = sum_r src[base_q + rest_r] * fac[basecol_q + restcol_r]
 template <int TEAM, int kColBlock>
-__device__ __forceinline__ void pull_op(const DevPlan &P, const PullOp &__restrict__ op, double *S, const Smem &sm, int lane, int warp) {
+__device__ FBN_OP_INLINE void pull_op(const DevPlan &P, const PullOp &__restrict__ op, double *S, const Smem &sm, int lane, int warp) {
     const int units = (op.nT + kColBlock - 1) / kColBlock * op.chunks;
     for (int u = (warp - op.rot) & (TEAM - 1); u < units; u += TEAM) {
         int q0, nq, ck, r0, r1;
@@ -100,10 +107,23 @@ __device__ __forceinline__ void pull_op(const DevPlan &P, const PullOp &__restri
 }
 
 template <int TEAM>
-__device__ __forceinline__ void fin_item(const FinItem &F, double *S, const Smem &sm, int lane) {
+__device__ __forceinline__ void fin_item(const DevPlan &P, const FinItem &F, double *S, const Smem &sm, int lane) {
     double s = 0.0;
     if (F.type == FIN_NORM) {
-        for (int w = 0; w < TEAM; ++w) s += sm.normacc[(F.slot0 * TEAM + w) * kLanes + lane];
+        if (TEAM == 1) {
+            s = sm.normacc[F.slot0 * kLanes + lane];
+        } else {
+            const double *np = row_ptr(S, P.normpart_row0 + F.slot0 * TEAM);
+            constexpr int G = TEAM < 8 ? TEAM : 8;  // independent loads in flight; summed in warp order
+#pragma unroll 1
+            for (int w0 = 0; w0 < TEAM; w0 += G) {
+                double v[G];
+#pragma unroll
+                for (int w = 0; w < G; ++w) v[w] = np[(w0 + w) * kLanes];
+#pragma unroll
+                for (int w = 0; w < G; ++w) s += v[w];
+            }
+        }
         *row_ptr(S, F.dst_row) = 1.0 / s;
         return;
     }
@@ -129,7 +149,7 @@ __global__ void __launch_bounds__(TEAM * 32, (FBN_OCC / TEAM) > 0 ? (FBN_OCC / T
     sm.mask = reinterpret_cast<uint32_t *>(smem_raw + o);
     o += ((size_t)P.max_mask_words * 4 + 15) & ~(size_t)15;
     sm.normacc = reinterpret_cast<double *>(smem_raw + o);
-    sm.part = sm.normacc + (size_t)P.max_normslots * TEAM * kLanes;
+    sm.part = sm.normacc + (size_t)P.max_normslots * (TEAM == 1 ? kLanes : 0);
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     double *S = scratch + (int64_t)blockIdx.x * P.tile_rows * kLanes + lane;  // lane-private column of this CTA's tile
@@ -186,7 +206,7 @@ __global__ void __launch_bounds__(TEAM * 32, (FBN_OCC / TEAM) > 0 ? (FBN_OCC / T
             }
             if (p.fin_end > p.fin_begin) {
                 if (TEAM > 1) __syncthreads();
-                for (int f = p.fin_begin + warp; f < p.fin_end; f += TEAM) fin_item<TEAM>(P.fins[f], S, sm, lane);
+                for (int f = p.fin_begin + warp; f < p.fin_end; f += TEAM) fin_item<TEAM>(P, P.fins[f], S, sm, lane);
             }
             if (TEAM > 1) __syncthreads(); else __syncwarp();  // the next phase overwrites the mask tables / partial slots
         }
@@ -278,7 +298,7 @@ __global__ void score_reduce_kernel(int64_t n_cases, const double *__restrict__ 
 size_t fused_smem_bytes(const DevPlan &P) {
     size_t o = ((size_t)(P.sum_dims + P.n_vars) * 4 + 15) & ~(size_t)15;
     o += ((size_t)P.max_mask_words * 4 + 15) & ~(size_t)15;
-    return o + ((size_t)P.max_normslots * P.team + (size_t)P.max_pslots) * kLanes * sizeof(double);
+    return o + ((size_t)(P.team == 1 ? P.max_normslots : 0) + (size_t)P.max_pslots) * kLanes * sizeof(double);
 }
 
 template <int TEAM>

@@ -5,11 +5,21 @@
 // warp-uniform index loads; all scratch accesses are coalesced 256-byte rows.
 #pragma once
 #include <cstdint>
+#include <type_traits>
 #include <cuda_runtime.h>
 
 #include "plan.h"
 
 namespace fbn {
+
+// rest entries per batch of the QB = 2 PULL loop (fused kernel, >= 2 warps per tile); 1 = plain loop
+#ifndef FBN_PULL_BATCH
+#define FBN_PULL_BATCH 8
+#endif
+// two register sets in the COLLECT row loop of the CB = 2 (fused, >= 2 warps per tile) kernels too
+#ifndef FBN_TWOSETS_CB2
+#define FBN_TWOSETS_CB2 0
+#endif
 
 __device__ __forceinline__ double *row_ptr(double *S, int32_t row) { return S + (int64_t)row * kLanes; }
 
@@ -73,7 +83,7 @@ __device__ __forceinline__ void collect_rows(const DevPlan &P, const CollectOp &
     constexpr int NCC = NC > 0 ? NC : 1;
     constexpr int NU = (UMASK & 1) + ((UMASK >> 1) & 1) + ((UMASK >> 2) & 1);
     constexpr int kGathers = NC > 0 ? (NC - NU) * CB + NU : 0;  // per row
-    constexpr bool kTwoSets = NC > 0 && CB >= 4 && kGathers <= 9;
+    constexpr bool kTwoSets = NC > 0 && ((CB >= 4 && kGathers <= 9) || (FBN_TWOSETS_CB2 != 0 && CB == 2 && kGathers <= 6));
     const int nchild = NC >= 0 ? NC : op.nchild, cols = op.cols;
     const double *__restrict__ pot = P.pot + op.pot_off;
     const int32_t *__restrict__ rowpart = P.idx32 + op.rowpart_off;
@@ -316,6 +326,46 @@ __device__ __forceinline__ void pull_block(const DevPlan &P, const PullOp &op, d
         src[q] = row_ptr(S, op.src_row + b.x);
         fac[q] = row_ptr(S, op.fac_row + b.y);
         uni = uni && fac[q] == fac[0];
+    }
+    if constexpr (QB == 2 && FBN_PULL_BATCH > 1) {
+        // fused kernel, several warps per tile: batches of RB rest entries. The index entries of batch b+1 are fetched while
+        // batch b is in flight, ALL data loads of a batch (RB x QB source rows + RB or RB x QB factor rows) are issued before
+        // the first multiply-add, and the sums run in rest order (same rounding as the plain loop). One memory latency per
+        // RB rest entries instead of one per entry of a dependent index -> address -> data chain.
+        constexpr int RB = FBN_PULL_BATCH;
+        int r = r0;
+        auto batches = [&](auto uni_c) {
+            constexpr bool UNI = decltype(uni_c)::value;
+            constexpr int NF = UNI ? 1 : QB;
+            for (; r + RB <= r1; r += RB) {
+                int2 t[RB];
+#pragma unroll
+                for (int i = 0; i < RB; ++i) t[i] = __ldg(tr + r + i);
+                double s[RB][QB], f[RB][NF];
+#pragma unroll
+                for (int i = 0; i < RB; ++i) {
+#pragma unroll
+                    for (int q = 0; q < QB; ++q) s[i][q] = load_clique<STREAM>(src[q] + (int64_t)t[i].x * kLanes);
+#pragma unroll
+                    for (int q = 0; q < NF; ++q) f[i][q] = fac[q][(int64_t)t[i].y * kLanes];
+                }
+#pragma unroll
+                for (int i = 0; i < RB; ++i) {
+#pragma unroll
+                    for (int q = 0; q < QB; ++q) acc[q] += s[i][q] * f[i][UNI ? 0 : q];
+                }
+            }
+        };
+        if (r + RB <= r1) {
+            if (uni) batches(std::true_type{});
+            else batches(std::false_type{});
+        }
+        for (; r < r1; ++r) {  // < RB left
+            const int2 t = __ldg(tr + r);
+#pragma unroll
+            for (int q = 0; q < QB; ++q) acc[q] += load_clique<STREAM>(src[q] + (int64_t)t.x * kLanes) * fac[q][(int64_t)t.y * kLanes];
+        }
+        return;
     }
     int2 t_next = __ldg(tr + min(r0, r1 - 1));  // index prefetch, as in collect_block
     if (uni) {

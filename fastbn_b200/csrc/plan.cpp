@@ -401,7 +401,8 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
         ph.fin_begin = (int32_t)P.fins.size();
         int64_t work = 0;
         for (int o : ops) work += kind == 0 ? (int64_t)P.cops[o].rows * P.cops[o].cols : (int64_t)P.pops[o].nT * P.pops[o].nR;
-        int64_t target = std::max<int64_t>(128, work / (4 * (int64_t)team));  // table entries per unit
+        static const int kSplit = getenv("FBN_SPLIT") ? atoi(getenv("FBN_SPLIT")) : 4;
+        int64_t target = std::max<int64_t>(128, work / (kSplit * (int64_t)team));  // table entries per unit
         auto chunks_of = [&](int64_t rows, int64_t cols, int64_t tgt) {
             if (team == 1) return (int64_t)1;
             tgt = std::max<int64_t>(8, tgt / std::min<int64_t>(cols, kColBlock));  // rows per unit
@@ -419,9 +420,21 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
             if (pslots <= kMaxPslots) break;
             target *= 4;
         }
+        // fused mode deals the units of a phase round-robin to the warps of the tile's CTA: ops with the most expensive units
+        // first, so that the small units at the end even out the load (longest-processing-time order)
+        std::vector<int> ordered(ops);
+        if (!level && team > 1 && !getenv("FBN_NO_LPT")) {
+            auto unit_cost = [&](int o) {
+                int64_t rows = kind == 0 ? P.cops[o].rows : P.pops[o].nR, cols = kind == 0 ? P.cops[o].cols : P.pops[o].nT;
+                int64_t ch = chunks_of(rows, cols, target);
+                int64_t per = (rows + ch - 1) / ch;
+                return per * std::min<int64_t>(cols, kColBlock) * (kind == 0 ? 1 + P.cops[o].nchild : 2);
+            };
+            std::stable_sort(ordered.begin(), ordered.end(), [&](int a, int b) { return unit_cost(a) > unit_cost(b); });
+        }
         int pslots = 0, normslots = 0, mask_words = 0;
         int64_t units = 0;
-        for (int o : ops) {
+        for (int o : ordered) {
             int64_t rows = kind == 0 ? P.cops[o].rows : P.pops[o].nR, cols = kind == 0 ? P.cops[o].cols : P.pops[o].nT;
             int64_t chunks = chunks_of(rows, cols, target);
             if (chunks > 1 && pslots + chunks * cols > kMaxPslots) chunks = 1;
@@ -584,6 +597,16 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
         P.part_row0 = P.tile_rows;
         P.normpart_row0 = P.part_row0 + P.max_pslots;
         int64_t rows = (int64_t)P.normpart_row0 + (int64_t)P.max_normslots * P.nb_max;
+        if (rows > ((int64_t)1 << 30)) return "tree too large: more than 2^30 scratch rows per tile";
+        P.tile_rows = (int32_t)rows;
+    } else if (team > 1) {
+        // fused mode, several warps per tile: the per-warp shares of every clique norm of a phase go to scratch rows (written
+        // once, read once by the phase's FIN_NORM items, L2-resident) instead of max_normslots x team x 256 B of shared
+        // memory, which was what kept big trees (PIGS shape: 15 cliques per phase) at one CTA per SM
+        P.nb_max = team;
+        P.part_row0 = 0;
+        P.normpart_row0 = P.tile_rows;
+        int64_t rows = (int64_t)P.normpart_row0 + (int64_t)P.max_normslots * team;
         if (rows > ((int64_t)1 << 30)) return "tree too large: more than 2^30 scratch rows per tile";
         P.tile_rows = (int32_t)rows;
     }
