@@ -328,43 +328,46 @@ __device__ __forceinline__ void pull_block(const DevPlan &P, const PullOp &op, d
         uni = uni && fac[q] == fac[0];
     }
     if constexpr (QB == 2 && FBN_PULL_BATCH > 1) {
-        // fused kernel, several warps per tile: batches of RB rest entries. The index entries of batch b+1 are fetched while
-        // batch b is in flight, ALL data loads of a batch (RB x QB source rows + RB or RB x QB factor rows) are issued before
-        // the first multiply-add, and the sums run in rest order (same rounding as the plain loop). One memory latency per
-        // RB rest entries instead of one per entry of a dependent index -> address -> data chain.
+        // fused kernel, several warps per tile: batches of RB rest entries. The RB index entries come first (L1-resident,
+        // warp-uniform), then ALL data loads of the batch (RB x QB source rows + RB or RB x QB factor rows) are issued before
+        // the first multiply-add; the sums run in rest order (same rounding as the plain loop). One DRAM latency per batch
+        // instead of one per dependent index -> address -> data chain (measured on B200: RB 4 / 6 / 8 / 12 / 16 -> PIGS-shape
+        // 423 / 428 / 440 / 434 / 435 k cases/s; fetching the next batch's indices ahead costs 8 registers and loses).
         constexpr int RB = FBN_PULL_BATCH;
         int r = r0;
-        auto batches = [&](auto uni_c) {
+        auto batch = [&](auto uni_c, auto n_c) {  // N rest entries starting at r
             constexpr bool UNI = decltype(uni_c)::value;
-            constexpr int NF = UNI ? 1 : QB;
-            for (; r + RB <= r1; r += RB) {
-                int2 t[RB];
+            constexpr int N = decltype(n_c)::value, NF = UNI ? 1 : QB;
+            int2 t[N];
 #pragma unroll
-                for (int i = 0; i < RB; ++i) t[i] = __ldg(tr + r + i);
-                double s[RB][QB], f[RB][NF];
+            for (int i = 0; i < N; ++i) t[i] = __ldg(tr + r + i);
+            double s[N][QB], f[N][NF];
 #pragma unroll
-                for (int i = 0; i < RB; ++i) {
+            for (int i = 0; i < N; ++i) {
 #pragma unroll
-                    for (int q = 0; q < QB; ++q) s[i][q] = load_clique<STREAM>(src[q] + (int64_t)t[i].x * kLanes);
+                for (int q = 0; q < QB; ++q) s[i][q] = load_clique<STREAM>(src[q] + (int64_t)t[i].x * kLanes);
 #pragma unroll
-                    for (int q = 0; q < NF; ++q) f[i][q] = fac[q][(int64_t)t[i].y * kLanes];
-                }
-#pragma unroll
-                for (int i = 0; i < RB; ++i) {
-#pragma unroll
-                    for (int q = 0; q < QB; ++q) acc[q] += s[i][q] * f[i][UNI ? 0 : q];
-                }
+                for (int q = 0; q < NF; ++q) f[i][q] = fac[q][(int64_t)t[i].y * kLanes];
             }
-        };
-        if (r + RB <= r1) {
-            if (uni) batches(std::true_type{});
-            else batches(std::false_type{});
-        }
-        for (; r < r1; ++r) {  // < RB left
-            const int2 t = __ldg(tr + r);
 #pragma unroll
-            for (int q = 0; q < QB; ++q) acc[q] += load_clique<STREAM>(src[q] + (int64_t)t.x * kLanes) * fac[q][(int64_t)t.y * kLanes];
-        }
+            for (int i = 0; i < N; ++i) {
+#pragma unroll
+                for (int q = 0; q < QB; ++q) acc[q] += s[i][q] * f[i][UNI ? 0 : q];
+            }
+            r += N;
+        };
+        auto batches = [&](auto uni_c) {
+            while (r + RB <= r1) batch(uni_c, std::integral_constant<int, RB>{});
+            // the last < RB rest entries in batches of 4, 2, 1 (table sizes are rarely multiples of RB)
+            if constexpr (RB > 4) {
+                while (r + 4 <= r1) batch(uni_c, std::integral_constant<int, 4>{});
+            }
+            if (r + 2 <= r1) batch(uni_c, std::integral_constant<int, 2>{});
+            if (r + 2 <= r1) batch(uni_c, std::integral_constant<int, 2>{});
+            if (r < r1) batch(uni_c, std::integral_constant<int, 1>{});
+        };
+        if (uni) batches(std::true_type{});
+        else batches(std::false_type{});
         return;
     }
     int2 t_next = __ldg(tr + min(r0, r1 - 1));  // index prefetch, as in collect_block
