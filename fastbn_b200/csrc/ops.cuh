@@ -20,6 +20,11 @@ namespace fbn {
 #ifndef FBN_TWOSETS_CB2
 #define FBN_TWOSETS_CB2 0
 #endif
+// unroll factor of the single-register-set COLLECT row loop of the CB = 2 kernels
+#ifndef FBN_COLLECT_UNROLL_CB2
+#define FBN_COLLECT_UNROLL_CB2 2
+#endif
+constexpr int kCollectUnrollCB2 = FBN_COLLECT_UNROLL_CB2;
 
 __device__ __forceinline__ double *row_ptr(double *S, int32_t row) { return S + (int64_t)row * kLanes; }
 
@@ -191,7 +196,7 @@ __device__ __forceinline__ void collect_rows(const DevPlan &P, const CollectOp &
         int32_t rp[NCC], rpn[NCC];
         double m[NCC][CB];
         load_parts(r0, rpn);
-#pragma unroll(CB >= 4 ? 1 : 2)
+#pragma unroll(CB >= 4 ? 1 : kCollectUnrollCB2)
         for (int r = r0; r < r1; ++r) {
 #pragma unroll
             for (int k = 0; k < NCC; ++k) rp[k] = rpn[k];
