@@ -22,7 +22,7 @@ def _shape(name):
     return t, load_golden(os.path.join("synth", name + "_ref"))
 
 
-@pytest.mark.parametrize("name,team", [("hepar2", 0), ("hepar2", 1), ("hepar2", 8), ("pigs", 0), ("pigs", 2), ("pigs", 32)])
+@pytest.mark.parametrize("name,team", [("hepar2", 0), ("hepar2", 1), ("hepar2", 4), ("hepar2", 8), ("hepar2", 16), ("pigs", 0), ("pigs", 2), ("pigs", 8), ("pigs", 16), ("pigs", 32)])
 def test_shape_matches_reference(name, team):
     t, g = _shape(name)
     p = capi.Plan(t, device=0, team_warps=team)

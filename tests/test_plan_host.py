@@ -107,3 +107,29 @@ def test_flat_records_of_small_trees(alarm_tree, no_flat, monkeypatch):
         assert np.array_equal(np.isnan(post), np.isnan(g["post"]))
         assert np.nanmax(np.abs(post - g["post"])) <= 1e-9
         assert np.array_equal(lab, g["labels"])
+
+
+@pytest.mark.parametrize("team", [8, 16])
+def test_unit_order_of_a_phase_does_not_change_results(team, monkeypatch):
+    """Fused plans deal the most expensive units of a phase first (longest-processing-time order, plan.cpp emit_phase) and keep
+    the per-warp shares of the clique norms in max_normslots x team scratch rows appended to the tile. Ops of one phase are
+    independent; only the grouping of a clique norm's per-warp shares follows the rotation, so the plan with the ops in storage
+    order (FBN_NO_LPT) must give the same posteriors up to fp64 re-association (1e-13), identical labels, and both must
+    reproduce the unmodified reference (PIGS shape, 16 warps per tile is what AUTO picks)."""
+    from fastbn_b200 import hostapi
+    m = hostapi.HostModel(os.path.join(ROOT, "tests", "golden", "synth", "pigs.xml"))
+    t = m.tree()
+    m.close()
+    g = load_golden(os.path.join("synth", "pigs_ref"))
+    n = 4
+    k = g["ev_off"][n]
+    args = (g["ev_off"][:n + 1], g["ev_vars"][:k], g["ev_vals"][:k])
+    post, lab, info = emu.run(t, team, *args)
+    monkeypatch.setenv("FBN_NO_LPT", "1")
+    post0, lab0, info0 = emu.run(t, team, *args)
+    assert np.nanmax(np.abs(post - post0)) <= 1e-13 and np.array_equal(lab, lab0)
+    assert np.nanmax(np.abs(post - g["post"][:n])) <= 1e-9
+    assert np.array_equal(lab, g["labels"][:n])
+    assert info[1] == info0[1] and info[3] == info0[3]  # same units and partial slots, only their order differs
+    t1 = emu.run(t, 1, *args)[2]
+    assert info[5] >= t1[5] + info[4] * team  # tile rows: tables + messages + one norm row per (clique of a phase, warp)
