@@ -11,10 +11,14 @@ LIB_PATH = os.environ.get("FASTBN_B200_LIB") or os.path.join(_HERE, "libfastbn_b
 
 # every symbol include/fastbn_b200.h declares
 ABI_SYMBOLS = ["fbn_last_error", "fbn_device_count", "fbn_device_warmup", "fbn_plan_create", "fbn_plan_destroy", "fbn_plan_get_info",
-               "fbn_run", "fbn_run_device", "fbn_evaluate", "fbn_score_device"]
+               "fbn_run", "fbn_run_device", "fbn_evaluate", "fbn_score_device",
+               "fbn_comm_unique_id", "fbn_comm_create", "fbn_comm_create_all", "fbn_reduce", "fbn_reduce_device", "fbn_comm_info",
+               "fbn_comm_destroy"]
 
 
 MODE_AUTO, MODE_FUSED, MODE_LEVEL = 0, 1, 2
+TILE_CASES = 32      # test cases per tile (fastbn_b200/csrc/plan.h)
+COMM_ID_BYTES = 128  # FBN_COMM_ID_BYTES
 
 
 class FastBNError(RuntimeError):
@@ -38,7 +42,7 @@ class PlanInfo(C.Structure):
                 ("clique_entries", C.c_int64), ("separator_entries", C.c_int64), ("parent_entries", C.c_int64),
                 ("marginal_entries", C.c_int64), ("scratch_bytes", C.c_int64), ("plan_bytes", C.c_int64),
                 ("alg_bytes_per_case", C.c_double), ("kernel_bytes_per_case", C.c_double),
-                ("flat_records", C.c_int32), ("reserved", C.c_int32)]
+                ("flat_records", C.c_int32), ("kernel_rev", C.c_int32)]
 
 
 class Stats(C.Structure):
@@ -67,6 +71,13 @@ def load_library():
     L.fbn_run_device.argtypes = [C.c_void_p, C.c_int64] + [C.c_void_p] * 6 + [C.POINTER(Stats)]
     L.fbn_evaluate.argtypes = [C.c_void_p, C.c_int64] + [C.c_void_p] * 8 + [C.POINTER(Stats)]
     L.fbn_score_device.argtypes = [C.c_void_p, C.c_int64] + [C.c_void_p] * 6
+    L.fbn_comm_unique_id.argtypes = [C.c_void_p]
+    L.fbn_comm_create.argtypes = [C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.POINTER(C.c_void_p)]
+    L.fbn_comm_create_all.argtypes = [C.c_int32, C.c_void_p, C.POINTER(C.c_void_p)]
+    L.fbn_reduce.argtypes = [C.c_void_p, C.c_void_p]
+    L.fbn_reduce_device.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    L.fbn_comm_info.argtypes = [C.c_void_p] + [C.POINTER(C.c_int32)] * 3
+    L.fbn_comm_destroy.argtypes = [C.c_void_p]
     _lib = L
     return L
 
@@ -108,6 +119,13 @@ class Plan:
         _check(self.L, self.L.fbn_plan_get_info(self.h, C.byref(info)))
         self.info = info
         self.sum_dims = info.sum_dims
+
+    @property
+    def kernel_name(self):
+        """Name of the kernel a fused-mode plan launches (level mode launches one kernel per tree level)."""
+        if self.info.mode == MODE_LEVEL:
+            return "lvl_collect_kernel+lvl_pull_kernel"
+        return "jt_flat_kernel" if self.info.flat_records else "jt_fused_kernel<%d>" % self.info.team_warps
 
     def close(self):
         if getattr(self, "h", None):
@@ -159,3 +177,46 @@ class Plan:
         out = np.zeros(4, np.float64)
         _check(self.L, self.L.fbn_score_device(self.h, n_cases, post_ptr, labels_ptr, golden_ptr, truths_ptr, _ptr(out), stream))
         return dict(n_correct=int(out[0]), n_total=int(out[1]), sum_mse=float(out[2]), sum_hd=float(out[3]))
+
+
+def comm_unique_id():
+    """fbn_comm_unique_id: 128 bytes rank 0 hands to the other ranks."""
+    L = load_library()
+    buf = (C.c_ubyte * COMM_ID_BYTES)()
+    _check(L, L.fbn_comm_unique_id(buf))
+    return bytes(buf)
+
+
+class Comm:
+    """fbn_comm: NCCL communicator of the path's one exchange step (sum of the four scores over the ranks)."""
+
+    def __init__(self, device, rank, world, unique_id):
+        self.L = load_library()
+        h = C.c_void_p()
+        idbuf = (C.c_ubyte * COMM_ID_BYTES).from_buffer_copy(unique_id)
+        _check(self.L, self.L.fbn_comm_create(device, rank, world, idbuf, C.byref(h)))
+        self.h = h
+        self.rank, self.world = rank, world
+
+    def reduce(self, v4):
+        """In-place sum over all ranks of four doubles (collective). Returns a list of four floats."""
+        a = np.ascontiguousarray(v4, np.float64).copy()
+        assert a.shape == (4,)
+        _check(self.L, self.L.fbn_reduce(self.h, _ptr(a)))
+        return [float(x) for x in a]
+
+    def nccl_version(self):
+        v = C.c_int32()
+        _check(self.L, self.L.fbn_comm_info(self.h, None, None, C.byref(v)))
+        return int(v.value)
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.fbn_comm_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

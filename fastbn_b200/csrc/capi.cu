@@ -3,6 +3,7 @@
 #include <chrono>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -13,11 +14,11 @@
 
 namespace fbn {
 size_t fused_smem_bytes(const DevPlan &P);
-cudaError_t fused_prepare(const DevPlan &P, int *blocks_per_sm);
+cudaError_t fused_prepare(const DevPlan &P, int smem_optin, int *blocks_per_sm);
 cudaError_t fused_launch(const DevPlan &P, int grid, double *scratch, int64_t n_cases, const int64_t *ev_off, int64_t ev_base,
                          const int32_t *ev_vars, const int32_t *ev_vals, int32_t *labels, double *post, cudaStream_t st);
 size_t flat_smem_bytes(const DevPlan &P);
-cudaError_t flat_prepare(const DevPlan &P, int *blocks_per_sm);
+cudaError_t flat_prepare(const DevPlan &P, int smem_optin, int *blocks_per_sm);
 cudaError_t flat_launch(const DevPlan &P, int grid, double *scratch, int64_t n_cases, const int64_t *ev_off, int64_t ev_base,
                         const int32_t *ev_vars, const int32_t *ev_vals, int32_t *labels, double *post, cudaStream_t st);
 cudaError_t level_launch(const DevPlan &P, const std::vector<Phase> &phases, int resident, double *scratch, uint32_t *lamG,
@@ -33,6 +34,11 @@ static int fail(int code, const std::string &msg) {
     g_err = msg;
     return code;
 }
+int fbn_set_error(int code, const std::string &msg) { return fail(code, msg); }  // for comm.cu
+
+// Revision of the kernels' memory behaviour. bench.py attaches an ncu traffic figure (profiles/traffic.json) to a run only
+// when it was captured at the same revision: bump on every change that alters what the kernels read or write.
+static const int kKernelRev = 1;
 #define CK(call)                                                                                       \
     do {                                                                                               \
         cudaError_t e__ = (call);                                                                      \
@@ -41,6 +47,12 @@ static int fail(int code, const std::string &msg) {
     } while (0)
 
 namespace {
+// every entry point switches to the plan's device and puts the caller's current device back on return
+struct DeviceGuard {
+    int prev = -1;
+    DeviceGuard() { if (cudaGetDevice(&prev) != cudaSuccess) { prev = -1; cudaGetLastError(); } }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
 constexpr int kNBuf = 3;            // pipeline depth of fbn_run
 struct ChunkBuf {                   // device + pinned staging for one in-flight chunk
     int64_t *d_off = nullptr;
@@ -74,6 +86,7 @@ struct fbn_plan {
     double *score_case = nullptr;
     int64_t score_cap = 0;
     double *score_out4 = nullptr;
+    std::mutex mu;              // serialises the calls that use the plan's scratch and buffers
 };
 
 extern "C" const char *fbn_last_error(void) { return g_err.c_str(); }
@@ -91,6 +104,7 @@ extern "C" int fbn_device_warmup(int32_t device) {
     int ndev = fbn_device_count();
     if (ndev <= 0) return fail(FBN_ERR_NO_DEVICE, "no CUDA device: fastbn_b200 has no CPU fallback");
     if (device < 0 || device >= ndev) return fail(FBN_ERR_INVALID, "device ordinal out of range");
+    DeviceGuard guard;
     CK(cudaSetDevice(device));
     CK(cudaFree(nullptr));
     return FBN_OK;
@@ -156,6 +170,7 @@ extern "C" int fbn_plan_create(const fbn_tree_desc *tree, const fbn_plan_options
     int dev = opt && opt->device >= 0 ? opt->device : -1;
     if (dev < 0) CK(cudaGetDevice(&dev));
     if (dev >= ndev) return fail(FBN_ERR_INVALID, "device ordinal out of range");
+    DeviceGuard guard;
     CK(cudaSetDevice(dev));
     if (!tree->table_nvars || !tree->table_vars || !tree->var_dims) return fail(FBN_ERR_INVALID, "null array in fbn_tree_desc");
     for (int v = 0; v < tree->n_vars; ++v)
@@ -227,7 +242,8 @@ extern "C" int fbn_plan_create(const fbn_tree_desc *tree, const fbn_plan_options
             fbn_plan_destroy(p);
             return fail(FBN_ERR_INVALID, "tree needs more shared memory per tile than the device has");
         }
-        ce = d.flat ? fbn::flat_prepare(d, &p->blocks_per_sm) : fbn::fused_prepare(d, &p->blocks_per_sm);
+        ce = d.flat ? fbn::flat_prepare(d, (int)prop.sharedMemPerBlockOptin, &p->blocks_per_sm)
+                    : fbn::fused_prepare(d, (int)prop.sharedMemPerBlockOptin, &p->blocks_per_sm);
         if (ce != cudaSuccess) {
             fbn_plan_destroy(p);
             return fail(FBN_ERR_CUDA, std::string("kernel setup failed (is this an sm_100 device?): ") + cudaGetErrorString(ce));
@@ -283,6 +299,7 @@ static void free_chunk(ChunkBuf &b) {
 
 extern "C" void fbn_plan_destroy(fbn_plan *p) {
     if (!p) return;
+    DeviceGuard guard;
     cudaSetDevice(p->device);
     cudaDeviceSynchronize();
     for (void *d : p->dev_allocs) cudaFree(d);
@@ -311,6 +328,7 @@ extern "C" int fbn_plan_get_info(const fbn_plan *p, fbn_plan_info *o) {
     o->marginal_entries = h.marginal_entries; o->scratch_bytes = p->scratch_bytes; o->plan_bytes = p->plan_bytes;
     o->alg_bytes_per_case = h.alg_bytes_per_case; o->kernel_bytes_per_case = h.kernel_bytes_per_case;
     o->flat_records = p->dp.flat;
+    o->kernel_rev = kKernelRev;
     return FBN_OK;
 }
 
@@ -319,6 +337,8 @@ extern "C" int fbn_run_device(fbn_plan *p, int64_t n_cases, const int64_t *ev_of
                               fbn_stats *stats) {
     if (!p) return fail(FBN_ERR_INVALID, "null plan");
     if (n_cases < 0 || (n_cases > 0 && !ev_offsets)) return fail(FBN_ERR_INVALID, "bad n_cases / ev_offsets");
+    std::lock_guard<std::mutex> lock(p->mu);
+    DeviceGuard guard;
     CK(cudaSetDevice(p->device));
     cudaStream_t st = (cudaStream_t)stream;
     if (stats) CK(cudaEventRecord(p->ev0, st));
@@ -373,6 +393,8 @@ static int ensure_chunk(ChunkBuf &b, int64_t cases, int64_t ev, int sum_dims, bo
         cudaFreeHost(b.h_off); cudaFreeHost(b.h_labels); cudaFreeHost(b.h_post); cudaFreeHost(b.h_gold); cudaFreeHost(b.h_truth);
         b.h_off = nullptr; b.h_labels = nullptr; b.h_post = nullptr; b.d_post = nullptr;
         b.d_gold = nullptr; b.h_gold = nullptr; b.d_truth = nullptr; b.h_truth = nullptr;
+        b.d_off = nullptr; b.d_labels = nullptr;
+        b.cap_cases = 0;   // a failing allocation below must not leave dangling pointers behind a stale capacity
         CK(cudaMalloc((void **)&b.d_off, (size_t)(cases + 1) * 8));
         CK(cudaMalloc((void **)&b.d_labels, (size_t)cases * 4));
         b.cap_cases = cases;
@@ -388,7 +410,8 @@ static int ensure_chunk(ChunkBuf &b, int64_t cases, int64_t ev, int sum_dims, bo
     }
     if (ev > b.cap_ev) {
         cudaFree(b.d_vars); cudaFree(b.d_vals); cudaFreeHost(b.h_vars); cudaFreeHost(b.h_vals);
-        b.h_vars = nullptr; b.h_vals = nullptr;
+        b.h_vars = nullptr; b.h_vals = nullptr; b.d_vars = nullptr; b.d_vals = nullptr;
+        b.cap_ev = 0;
         CK(cudaMalloc((void **)&b.d_vars, (size_t)ev * 4));
         CK(cudaMalloc((void **)&b.d_vals, (size_t)ev * 4));
         b.cap_ev = ev;
@@ -416,10 +439,35 @@ static int ensure_score(fbn_plan *p, int64_t n_cases) {
 }
 
 // Chunked, triple-buffered pipeline H2D -> fused kernel (-> scoring kernel) -> D2H shared by fbn_run and fbn_evaluate.
+static int run_pipeline(fbn_plan *p, int64_t n_cases, const int64_t *ev_offsets, const int32_t *ev_vars, const int32_t *ev_vals,
+                        const double *golden, const int32_t *truths, int32_t *labels_out, double *posteriors_out, double *out4,
+                        fbn_stats *stats);
+
+// A plan owns ONE tile scratch and one set of chunk buffers: calls on the same plan are serialised here. When the pipeline
+// fails half-way, earlier chunks may still have copies in flight that target the caller's buffers and the pinned staging
+// areas, so the streams are drained before the error is returned.
 static int run_impl(fbn_plan *p, int64_t n_cases, const int64_t *ev_offsets, const int32_t *ev_vars, const int32_t *ev_vals,
                     const double *golden, const int32_t *truths, int32_t *labels_out, double *posteriors_out, double *out4,
                     fbn_stats *stats) {
     if (!p) return fail(FBN_ERR_INVALID, "null plan");
+    std::lock_guard<std::mutex> lock(p->mu);
+    DeviceGuard guard;
+    const int rc = run_pipeline(p, n_cases, ev_offsets, ev_vars, ev_vals, golden, truths, labels_out, posteriors_out, out4, stats);
+    if (rc != FBN_OK) {
+        const std::string msg = g_err;
+        cudaSetDevice(p->device);
+        cudaStreamSynchronize(p->s_in);
+        cudaStreamSynchronize(p->s_k);
+        cudaStreamSynchronize(p->s_out);
+        cudaGetLastError();
+        g_err = msg;
+    }
+    return rc;
+}
+
+static int run_pipeline(fbn_plan *p, int64_t n_cases, const int64_t *ev_offsets, const int32_t *ev_vars, const int32_t *ev_vals,
+                        const double *golden, const int32_t *truths, int32_t *labels_out, double *posteriors_out, double *out4,
+                        fbn_stats *stats) {
     if (n_cases < 0 || (n_cases > 0 && (!ev_offsets || !labels_out))) return fail(FBN_ERR_INVALID, "bad arguments");
     const bool want_gold = golden != nullptr;
     if (want_gold && (!truths || !out4)) return fail(FBN_ERR_INVALID, "fbn_evaluate needs truths and out4");
@@ -461,6 +509,8 @@ static int run_impl(fbn_plan *p, int64_t n_cases, const int64_t *ev_offsets, con
     int64_t max_ev = 1;
     if (!offsets_ok(0, bounds[1])) return fail(FBN_ERR_INVALID, "ev_offsets must be non-decreasing");
     for (int64_t c = 0; c < n_chunks; ++c) max_ev = std::max(max_ev, std::max<int64_t>(0, ev_offsets[bounds[c + 1]] - ev_offsets[bounds[c]]));
+    // later chunks are validated only when their turn comes: a corrupt offset there must not size the buffers
+    max_ev = std::min(max_ev, std::max<int64_t>(1, ev_offsets[n_cases] - ev_offsets[0]));
     const bool stage_in = !(is_pinned(ev_offsets) && is_pinned(ev_vars) && is_pinned(ev_vals));
     const bool stage_out = !(is_pinned(labels_out) && is_pinned(posteriors_out));
     struct Pending { int64_t c0 = 0, n = 0; bool active = false; } pend[kNBuf];
@@ -566,6 +616,8 @@ extern "C" int fbn_score_device(fbn_plan *p, int64_t n_cases, const double *post
                                 const double *golden, const int32_t *truths, double *out4_host, void *stream) {
     if (!p || !out4_host || n_cases < 0) return fail(FBN_ERR_INVALID, "bad arguments");
     if (n_cases > 0 && (!posteriors || !labels || !golden || !truths)) return fail(FBN_ERR_INVALID, "null device array");
+    std::lock_guard<std::mutex> lock(p->mu);
+    DeviceGuard guard;
     CK(cudaSetDevice(p->device));
     cudaStream_t st = (cudaStream_t)stream;
     int rc;

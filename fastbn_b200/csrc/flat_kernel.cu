@@ -248,9 +248,11 @@ size_t flat_smem_bytes(const DevPlan &P) {
 }
 
 // *tiles_per_sm = resident warps (tiles) per SM
-cudaError_t flat_prepare(const DevPlan &P, int *tiles_per_sm) {
+// The attribute is per function and per context, not per plan: it is raised to the device's opt-in maximum so that plans
+// with different needs never lower it for each other (a launch still asks only for what its plan needs).
+cudaError_t flat_prepare(const DevPlan &P, int smem_optin, int *tiles_per_sm) {
     const size_t smem = flat_smem_bytes(P) * kWpc;
-    cudaError_t e = cudaFuncSetAttribute(jt_flat_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(jt_flat_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin);
     if (e != cudaSuccess) return e;
     int blocks = 0;
     e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks, jt_flat_kernel, 32 * kWpc, smem);

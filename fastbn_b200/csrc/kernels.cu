@@ -302,23 +302,25 @@ size_t fused_smem_bytes(const DevPlan &P) {
 }
 
 template <int TEAM>
-static cudaError_t prep(const DevPlan &P, int *blocks_per_sm) {
+static cudaError_t prep(const DevPlan &P, int smem_optin, int *blocks_per_sm) {
     size_t smem = fused_smem_bytes(P);
     constexpr int CB = TEAM == 1 ? 1 : 2;
     if (P.cb != CB) return cudaErrorInvalidValue;
-    cudaError_t e = cudaFuncSetAttribute(jt_fused_kernel<TEAM, CB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    // per function and per context, not per plan: raised to the device's opt-in maximum so that two live plans of the same
+    // instantiation never lower it for each other (a launch still asks only for what its plan needs)
+    cudaError_t e = cudaFuncSetAttribute(jt_fused_kernel<TEAM, CB>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin);
     if (e != cudaSuccess) return e;
     return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, jt_fused_kernel<TEAM, CB>, TEAM * 32, smem);
 }
 
-cudaError_t fused_prepare(const DevPlan &P, int *blocks_per_sm) {
+cudaError_t fused_prepare(const DevPlan &P, int smem_optin, int *blocks_per_sm) {
     switch (P.team) {
-        case 1: return prep<1>(P, blocks_per_sm);
-        case 2: return prep<2>(P, blocks_per_sm);
-        case 4: return prep<4>(P, blocks_per_sm);
-        case 8: return prep<8>(P, blocks_per_sm);
-        case 16: return prep<16>(P, blocks_per_sm);
-        case 32: return prep<32>(P, blocks_per_sm);
+        case 1: return prep<1>(P, smem_optin, blocks_per_sm);
+        case 2: return prep<2>(P, smem_optin, blocks_per_sm);
+        case 4: return prep<4>(P, smem_optin, blocks_per_sm);
+        case 8: return prep<8>(P, smem_optin, blocks_per_sm);
+        case 16: return prep<16>(P, smem_optin, blocks_per_sm);
+        case 32: return prep<32>(P, smem_optin, blocks_per_sm);
     }
     return cudaErrorInvalidValue;
 }

@@ -212,6 +212,7 @@ public:
     vector<double> posteriors;       // num_instances x sum_dims when keep_posteriors
     vector<int> predictions;         // labels of the last EvaluateAccuracy
     double average_mse = 0, average_hd = 0, jt_seconds = 0, kernel_ms = 0;
+    int64_t n_correct_reduced = 0;  // correct predictions summed over the device slices (fbn_reduce when several devices)
     bool quiet = false;
     std::thread warmup;              // brings the CUDA contexts of `devices` up in the background (joined before the first plan)
 

@@ -354,6 +354,12 @@ vector<int> JunctionTree::PredictUseJTInfer(int) {
     predictions.assign(n, 0);
     if (keep_posteriors) posteriors.assign((size_t)n * sd, 0.0);
     const int nd = (int)devices.size();
+    // several devices: the four scores of the slices meet in ONE ncclAllReduce (fbn_reduce), one communicator per device
+    vector<fbn_comm *> comms(nd, nullptr);
+    if (nd > 1 && fbn_comm_create_all(nd, devices.data(), comms.data()) != FBN_OK) {
+        fprintf(stderr, "Error in function %s! %s\n", __FUNCTION__, fbn_last_error());
+        exit(1);
+    }
     vector<std::array<double, 4>> part(nd);
     vector<string> errors(nd);
     vector<double> kms(nd, 0.0);
@@ -371,6 +377,7 @@ vector<int> JunctionTree::PredictUseJTInfer(int) {
         const double tw1 = now_s();
         // slice-local CSR offsets are absolute into ev_vars/ev_vals (fbn_run rebases them per chunk)
         fbn_stats st;
+        memset(&st, 0, sizeof(st));
         const bool need_last = (di == nd - 1) && c1 > c0;
         double *post_out = keep_posteriors ? posteriors.data() + (size_t)c0 * sd : nullptr;
         int rc = fbn_evaluate(plan, c1 - c0, ev_offsets.data() + c0, ev_vars.data(), ev_vals.data(),
@@ -392,6 +399,9 @@ vector<int> JunctionTree::PredictUseJTInfer(int) {
         }
         fbn_plan_destroy(plan);
     };
+    auto reduce_worker = [&](int di) {
+        if (fbn_reduce(comms[di], part[di].data()) != FBN_OK) errors[di] = fbn_last_error();
+    };
     if (nd == 1) {
         worker(0);
     } else {
@@ -399,14 +409,25 @@ vector<int> JunctionTree::PredictUseJTInfer(int) {
         for (int di = 0; di < nd; ++di) th.emplace_back(worker, di);
         for (auto &t : th) t.join();
     }
-    for (int di = 0; di < nd; ++di)
-        if (!errors[di].empty()) {
-            fprintf(stderr, "Error in function %s! device %d: %s\n", __FUNCTION__, devices[di], errors[di].c_str());
-            exit(1);
-        }
-    double mse = 0, hd = 0;
+    auto check_errors = [&]() {
+        for (int di = 0; di < nd; ++di)
+            if (!errors[di].empty()) {
+                fprintf(stderr, "Error in function %s! device %d: %s\n", __FUNCTION__, devices[di], errors[di].c_str());
+                exit(1);
+            }
+    };
+    check_errors();  // a failed slice must not enter the collective (the other ranks would wait for it)
+    if (nd > 1) {    // every device thread contributes its slice's scores; afterwards each holds the sum over all slices
+        vector<std::thread> th;
+        for (int di = 0; di < nd; ++di) th.emplace_back(reduce_worker, di);
+        for (auto &t : th) t.join();
+        check_errors();
+        for (int di = 0; di < nd; ++di) fbn_comm_destroy(comms[di]);
+    }
+    const double mse = part[0][2], hd = part[0][3];
+    n_correct_reduced = (int64_t)(part[0][0] + 0.5);
     kernel_ms = 0;
-    for (int di = 0; di < nd; ++di) { mse += part[di][2]; hd += part[di][3]; kernel_ms = std::max(kernel_ms, kms[di]); }
+    for (int di = 0; di < nd; ++di) kernel_ms = std::max(kernel_ms, kms[di]);
     for (int v = 0; v < network->num_nodes; ++v)
         probs_one_sample[v].assign(last_post.begin() + var_offsets[v], last_post.begin() + var_offsets[v + 1]);
     average_mse = mse / n;

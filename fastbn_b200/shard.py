@@ -23,8 +23,23 @@ def slice_csr(ev_off, ev_vars, ev_vals, c0, c1):
     return ev_off[c0:c1 + 1] - e0, ev_vars[e0:e1], ev_vals[e0:e1]
 
 
-def reduce_scores(out4, device=None):
-    """Sum of the per-rank {n_correct, n_total, sum_mse, sum_hd} over the default process group (no-op without one)."""
+def comm_from_process_group(device):
+    """fbn_comm over the ranks of the default torch.distributed group: rank 0 makes the NCCL unique id (fbn_comm_unique_id),
+    the process group's store carries its 128 bytes to the other ranks, every rank calls fbn_comm_create."""
+    import torch.distributed as dist
+    from . import capi
+    rank, world = dist.get_rank(), dist.get_world_size()
+    box = [capi.comm_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(box, src=0)
+    return capi.Comm(device, rank, world, box[0])
+
+
+def reduce_scores(out4, device=None, comm=None):
+    """Sum of the per-rank {n_correct, n_total, sum_mse, sum_hd}: through fbn_reduce (one ncclAllReduce behind the C ABI) when
+    a communicator is given, else over the default torch.distributed group (gloo in the CPU tests; no-op without a group)."""
+    if comm is not None:
+        v = comm.reduce([out4["n_correct"], out4["n_total"], out4["sum_mse"], out4["sum_hd"]])
+        return dict(n_correct=int(round(v[0])), n_total=int(round(v[1])), sum_mse=float(v[2]), sum_hd=float(v[3]))
     import torch
     import torch.distributed as dist
     t = torch.tensor([out4["n_correct"], out4["n_total"], out4["sum_mse"], out4["sum_hd"]], dtype=torch.float64, device=device or "cpu")
@@ -34,8 +49,9 @@ def reduce_scores(out4, device=None):
     return dict(n_correct=int(round(v[0])), n_total=int(round(v[1])), sum_mse=float(v[2]), sum_hd=float(v[3]))
 
 
-def evaluate_sharded(tree, ev_off, ev_vars, ev_vals, golden, truths, rank, world, device):
-    """This rank's slice through fbn_evaluate on cuda:`device`, then the all-reduce. Returns (labels of the slice, scores)."""
+def evaluate_sharded(tree, ev_off, ev_vars, ev_vals, golden, truths, rank, world, device, comm=None):
+    """This rank's slice through fbn_evaluate on cuda:`device`, then the reduction of the four scores (fbn_reduce when `comm`
+    is an fbn_comm, else torch.distributed). Returns (labels of the slice, scores summed over the ranks)."""
     import torch
     from . import capi
     c0, c1 = case_slice(len(ev_off) - 1, rank, world)
@@ -43,7 +59,7 @@ def evaluate_sharded(tree, ev_off, ev_vars, ev_vals, golden, truths, rank, world
     plan = capi.Plan(tree, device=device)
     labels, _, sc, _ = plan.evaluate(off, ev, ew, golden[c0:c1], truths[c0:c1])
     plan.close()
-    return labels, reduce_scores(sc, torch.device("cuda", device))
+    return labels, reduce_scores(sc, torch.device("cuda", device), comm=comm)
 
 
 def main():
@@ -65,7 +81,10 @@ def main():
     tree = m.tree()
     off, ev, ew, truths = m.cases()
     golden = m.golden(a.pt)
-    labels, sc = evaluate_sharded(tree, off, ev, ew, golden, truths, rank, world, local)
+    comm = comm_from_process_group(local) if world > 1 else None
+    labels, sc = evaluate_sharded(tree, off, ev, ew, golden, truths, rank, world, local, comm=comm)
+    if comm is not None:
+        comm.close()
     if rank == 0:
         print("average MSE = %g" % (sc["sum_mse"] / sc["n_total"]))
         print("average HD = %g" % (sc["sum_hd"] / sc["n_total"]))

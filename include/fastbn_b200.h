@@ -26,6 +26,7 @@ extern "C" {
 #define FBN_ERR_NO_DEVICE 2 /* no CUDA device (the product path never falls back to the CPU) */
 #define FBN_ERR_CUDA 3      /* a CUDA runtime call failed */
 #define FBN_ERR_NOMEM 4
+#define FBN_ERR_COMM 5      /* NCCL could not be loaded or an NCCL call failed (fbn_comm_*, fbn_reduce) */
 
 /* Execution modes. FUSED: one persistent kernel, one CTA per tile of 32 cases, whole tree per launch (small / medium
  * trees). LEVEL: one launch per tree level over all resident tiles, many CTAs per tile, big tables split across CTAs with a
@@ -90,7 +91,7 @@ typedef struct fbn_plan_info {
     double alg_bytes_per_case;   /* SURVEY.md 8(d) algorithmic bytes per case (fixed-shape fp64 tables), evidence excluded */
     double kernel_bytes_per_case;/* bytes the fused kernel itself moves per case (scratch r/w + output) */
     int32_t flat_records;        /* 1: small tree run by jt_flat_kernel (one warp per tile, per-entry records), else 0 */
-    int32_t reserved;
+    int32_t kernel_rev;          /* revision of the kernels' memory behaviour: ncu traffic figures are valid for one revision only */
 } fbn_plan_info;
 
 typedef struct fbn_stats {
@@ -150,6 +151,30 @@ int fbn_evaluate(fbn_plan *plan, int64_t n_cases, const int64_t *ev_offsets, con
  */
 int fbn_score_device(fbn_plan *plan, int64_t n_cases, const double *posteriors, const int32_t *labels,
                      const double *golden, const int32_t *truths, double *out4_host, void *stream);
+
+/*
+ * Multi-GPU: test cases are independent, so every GPU runs its own contiguous slice with a replicated plan and NO data-path
+ * collective (reference loop src/JunctionTree.cpp:1517-1528 carries only the mse / hd accumulators between cases). The one
+ * exchange step is the sum of out4 = {n_correct, n_total, sum_mse, sum_hd} over the ranks: ONE ncclAllReduce of four doubles
+ * (counts are exact below 2^53). The reference has no counterpart (its USE_MPI flag is a dead stub, CMakeLists.txt:10-16).
+ *
+ *   one process per GPU : rank 0 calls fbn_comm_unique_id and hands the 128 bytes to the other ranks by any means (file,
+ *                         socket, torch.distributed store); every rank calls fbn_comm_create, later fbn_reduce.
+ *   one process, n GPUs : fbn_comm_create_all gives one communicator per device; fbn_reduce must then be called
+ *                         concurrently, one host thread per communicator (our C++ JunctionTree does that).
+ * NCCL is loaded at run time (libnccl.so.2; a copy the process already loaded is preferred); FBN_ERR_COMM if absent.
+ */
+#define FBN_COMM_ID_BYTES 128
+typedef struct fbn_comm fbn_comm;
+int fbn_comm_unique_id(void *out128);
+int fbn_comm_create(int32_t device, int32_t rank, int32_t world, const void *id128, fbn_comm **out);
+int fbn_comm_create_all(int32_t n_devices, const int32_t *devices, fbn_comm **out /* [n_devices] */);
+/* in-place sum over all ranks of four host doubles; collective: every rank must call it; returns when the result is there */
+int fbn_reduce(fbn_comm *comm, double inout4[4]);
+/* same on four DEVICE doubles, enqueued on `stream` (no synchronisation) */
+int fbn_reduce_device(fbn_comm *comm, double *dev4, void *stream);
+int fbn_comm_info(const fbn_comm *comm, int32_t *rank, int32_t *world, int32_t *nccl_version);
+void fbn_comm_destroy(fbn_comm *comm);
 
 #ifdef __cplusplus
 }

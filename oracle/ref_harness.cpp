@@ -204,6 +204,53 @@ double fbnref_run_batch(void *h, int64_t n_cases, const int64_t *ev_off, const i
     return omp_get_wtime() - t0;
 }
 
+// Batch form with the reference's intra-case OpenMP parallelism (`-t N`): the same per-case sequence with num_threads
+// passed to LoadDiscreteEvidence / MessagePassingUpdateJT (src/JunctionTree.cpp:1476,1487). Works for any number of cases
+// (the stock loop of PredictUseJTInfer divides by n/20).
+double fbnref_run_batch_threads(void *h, int64_t n_cases, const int64_t *ev_off, const int32_t *vars, const int32_t *vals,
+                                double *post /* may be null */, int32_t *labels /* may be null */, int num_threads) {
+    RefCtx *c = (RefCtx *)h;
+    Quiet q(g_quiet);
+    JunctionTree *jt = c->jt;
+    std::vector<DiscreteConfig> Es(n_cases);
+    for (int64_t i = 0; i < n_cases; ++i)
+        for (int64_t k = ev_off[i]; k < ev_off[i + 1]; ++k) Es[i].insert(std::pair<int, int>(vars[k], vals[k]));
+    double t0 = omp_get_wtime();
+    for (int64_t i = 0; i < n_cases; ++i) {
+        jt->LoadDiscreteEvidence(Es[i], num_threads, c->timer);
+        for (size_t k = 0; k < jt->tree->vector_clique_ptr_container.size(); ++k)
+            jt->tree->vector_clique_ptr_container[k]->p_table.Normalize();
+        jt->MessagePassingUpdateJT(num_threads, c->timer);
+        int lab = jt->InferenceUsingJT();
+        jt->GetProbabilitiesAllNodes(Es[i]);
+        if (post)
+            for (int v = 0; v < c->network->num_nodes; ++v)
+                for (int d = 0; d < c->var_dims[v]; ++d) post[i * c->sum_dims + c->var_off[v] + d] = jt->probs_one_sample[v][d];
+        jt->ResetJunctionTree();
+        if (labels) labels[i] = lab;
+    }
+    double secs = omp_get_wtime() - t0;
+    omp_set_num_threads(1);
+    return secs;
+}
+
+// The stock driver loop itself, timed like the reference's own `jt` timer (src/JunctionTree.cpp:66-74): golden table load
+// outside, then PredictUseJTInfer(num_threads, timer) incl. CalculateMSE / CalculateHellingerDistance per case and the
+// progress lines, then Accuracy. Needs >= 20 loaded cases (quirk 5). Returns the accuracy, *secs = the timed span.
+double fbnref_predict_timed(void *h, const char *pt_path, int num_threads, double *secs) {
+    RefCtx *c = (RefCtx *)h;
+    Quiet q(g_quiet);
+    c->jt->LoadGroundTruthProbabilityTable(pt_path);
+    Timer *timer = new Timer();
+    double t0 = omp_get_wtime();
+    std::vector<int> predictions = c->jt->PredictUseJTInfer(num_threads, timer);
+    double acc = c->jt->Accuracy(predictions);
+    *secs = omp_get_wtime() - t0;
+    delete timer;
+    omp_set_num_threads(1);
+    return acc;
+}
+
 // The reference's own public entry point (include/Inference.h:44), banners and timers included.
 double fbnref_evaluate_accuracy(void *h, const char *pt_path, int num_threads, int quiet) {
     RefCtx *c = (RefCtx *)h;

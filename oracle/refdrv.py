@@ -33,6 +33,10 @@ def lib():
         L.fbnref_run_custom.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.fbnref_run_batch.restype = C.c_double
         L.fbnref_run_batch.argtypes = [C.c_void_p, C.c_int64] + [C.c_void_p] * 5
+        L.fbnref_run_batch_threads.restype = C.c_double
+        L.fbnref_run_batch_threads.argtypes = [C.c_void_p, C.c_int64] + [C.c_void_p] * 5 + [C.c_int]
+        L.fbnref_predict_timed.restype = C.c_double
+        L.fbnref_predict_timed.argtypes = [C.c_void_p, C.c_char_p, C.c_int, C.c_void_p]
         L.fbnref_evaluate_accuracy.restype = C.c_double
         L.fbnref_evaluate_accuracy.argtypes = [C.c_void_p, C.c_char_p, C.c_int, C.c_int]
         L.fbnref_case_evidence.restype = C.c_int
@@ -104,6 +108,24 @@ class Reference:
         labels = np.zeros(n, np.int32)
         secs = self.L.fbnref_run_batch(self.h, n, _p(ev_off), _p(ev_vars), _p(ev_vals), _p(post), _p(labels))
         return post, labels, secs
+
+    def run_batch_threads(self, ev_off, ev_vars, ev_vals, threads, want_post=False):
+        """Per-case sequence with the reference's intra-case OpenMP parallelism (-t N). Returns (post|None, labels, seconds)."""
+        ev_off = np.ascontiguousarray(ev_off, np.int64)
+        ev_vars = np.ascontiguousarray(ev_vars, np.int32)
+        ev_vals = np.ascontiguousarray(ev_vals, np.int32)
+        n = len(ev_off) - 1
+        post = np.zeros((n, self.sum_dims), np.float64) if want_post else None
+        labels = np.zeros(n, np.int32)
+        secs = self.L.fbnref_run_batch_threads(self.h, n, _p(ev_off), _p(ev_vars), _p(ev_vals), _p(post), _p(labels), int(threads))
+        return post, labels, secs
+
+    def predict_timed(self, pt_path, threads=1):
+        """The stock PredictUseJTInfer(num_threads) loop over the loaded LIBSVM cases (>= 20), timed like the `jt` timer.
+        Returns (accuracy, seconds)."""
+        secs = np.zeros(1, np.float64)
+        acc = self.L.fbnref_predict_timed(self.h, pt_path.encode(), int(threads), _p(secs))
+        return float(acc), float(secs[0])
 
     def evaluate_accuracy(self, pt_path, threads=1, quiet=True):
         return self.L.fbnref_evaluate_accuracy(self.h, pt_path.encode(), threads, 1 if quiet else 0)
