@@ -17,7 +17,7 @@ ABI_SYMBOLS = ["fbn_last_error", "fbn_device_count", "fbn_device_warmup", "fbn_p
 
 
 MODE_AUTO, MODE_FUSED, MODE_LEVEL = 0, 1, 2
-TILE_CASES = 32      # test cases per tile (fastbn_b200/csrc/plan.h)
+TILE_CASES = 64      # test cases per tile: 32 lanes x kW = 2 cases per lane (fastbn_b200/csrc/plan.h; fbn_plan_info.tile_cases)
 COMM_ID_BYTES = 128  # FBN_COMM_ID_BYTES
 
 
@@ -42,7 +42,8 @@ class PlanInfo(C.Structure):
                 ("clique_entries", C.c_int64), ("separator_entries", C.c_int64), ("parent_entries", C.c_int64),
                 ("marginal_entries", C.c_int64), ("scratch_bytes", C.c_int64), ("plan_bytes", C.c_int64),
                 ("alg_bytes_per_case", C.c_double), ("kernel_bytes_per_case", C.c_double),
-                ("flat_records", C.c_int32), ("kernel_rev", C.c_int32)]
+                ("flat_records", C.c_int32), ("kernel_rev", C.c_int32), ("tile_cases", C.c_int32), ("reserved", C.c_int32),
+                ("view_entries", C.c_int64), ("gather_rows", C.c_int64)]
 
 
 class Stats(C.Structure):

@@ -38,7 +38,7 @@ int fbn_set_error(int code, const std::string &msg) { return fail(code, msg); } 
 
 // Revision of the kernels' memory behaviour. bench.py attaches an ncu traffic figure (profiles/traffic.json) to a run only
 // when it was captured at the same revision: bump on every change that alters what the kernels read or write.
-static const int kKernelRev = 1;
+static const int kKernelRev = 2;
 #define CK(call)                                                                                       \
     do {                                                                                               \
         cudaError_t e__ = (call);                                                                      \
@@ -137,16 +137,19 @@ static double tree_entries(const fbn_tree_desc *t) {  // sum of clique table siz
 // above this many clique entries per case AUTO uses level mode (tile >= ~0.5 GB: too few tiles fit for one CTA per tile)
 static const double kLevelAutoEntries = 2.0e6;
 static const int64_t kLevelMaxResident = 4096;
+// Level mode: tiles in flight by default (FBN_LEVEL_RESIDENT overrides). The CTAs of a phase launch are scheduled tile by tile
+// (blockIdx.x = CTA of the tile varies fastest), so a big view keeps the whole GPU on one or two tiles at a time and the
+// message rows it gathers over and over (each is re-read |view| / |message| times) stay in the 126 MB L2; more tiles in
+// flight only add parallelism to the small phases.
+static const int64_t kLevelResident = 32;
 
 static int pick_team(double entries) {
-    // fused mode: more warps per tile for bigger tables (measured on ALARM / HEPAR2- / PIGS-shape)
+    // fused mode: more warps per tile for bigger tables; 16 resident warps per SM at 128 registers (two cases per lane), so a
+    // team of T warps runs 16 / T tiles per SM
     if (entries <= 8192) return 1;
-    if (entries <= 32768) return 4;
-    if (entries <= 131072) return 8;
-    // PIGS shape (265 k entries): 2 CTAs x 16 warps per SM, 472 k cases/s against 452 k with 1 x 32 (round 1f; possible since the
-    // clique-norm shares moved from shared memory to scratch rows); bigger tiles: few fit, so all 32 warps work on one
-    if (entries <= 524288) return 16;
-    return 32;
+    if (entries <= 131072) return 4;
+    if (entries <= 524288) return 8;
+    return 16;
 }
 
 // one inference pass over n_cases cases whose inputs are on the device: fused kernel or the per-level launches
@@ -199,9 +202,10 @@ extern "C" int fbn_plan_create(const fbn_tree_desc *tree, const fbn_plan_options
     int team = opt && opt->team_warps > 0 ? opt->team_warps : 0;
     if (!team && !level) team = pick_team(entries);
     if (!team && level) {
-        // nominal warps per tile: enough CTAs over all resident tiles to fill the GPU several times over
-        int64_t est_tile = (int64_t)(entries * 1.25 + 4096) * fbn::kLanes * 8;
-        int64_t res = std::max<int64_t>(1, std::min<int64_t>(kLevelMaxResident, budget / est_tile));
+        // nominal warps per tile: enough CTAs over all resident tiles to fill the GPU several times over. A tile holds the
+        // messages only (cliques are recomputed), roughly 2 rows per separator entry; separators are not known here, so the
+        // estimate is refined after planning (resident is computed from the plan's real tile size below)
+        int64_t res = kLevelResident;
         if (opt && opt->max_resident > 0) res = std::min<int64_t>(res, opt->max_resident);
         int64_t nb = (8 * (int64_t)prop.multiProcessorCount + res - 1) / res;
         nb = std::max<int64_t>(2, std::min<int64_t>(nb, 512));
@@ -220,21 +224,23 @@ extern "C" int fbn_plan_create(const fbn_tree_desc *tree, const fbn_plan_options
     fbn::DevPlan &d = p->dp;
     int rc;
 #define UP(field) if ((rc = upload(p, h.field, &d.field)) != FBN_OK) { fbn_plan_destroy(p); return rc; }
-    UP(pot) UP(lam16) UP(idx32) UP(flatc) UP(flatp) UP(cops) UP(pops) UP(p2ops) UP(oplist) UP(fins) UP(phases) UP(vars)
+    UP(pot) UP(lam16) UP(idx32) UP(flatc) UP(ops) UP(oplist) UP(fins) UP(phases) UP(vars)
 #undef UP
     d.n_phases = (int32_t)h.phases.size();
     d.n_vars = h.n_vars; d.sum_dims = h.sum_dims; d.query_var = h.query_var;
     d.tile_rows = h.tile_rows; d.mg_row0 = h.mg_row0;
     d.max_normslots = h.max_normslots; d.max_pslots = h.max_pslots; d.max_mask_words = h.max_mask_words; d.team = h.team; d.cb = h.cb;
     d.flat = h.flat ? 1 : 0;
-    d.part_row0 = h.part_row0; d.normpart_row0 = h.normpart_row0; d.nb_max = h.nb_max; d.lam_words = h.sum_dims + h.n_vars;
+    d.part_row0 = h.part_row0; d.normpart_row0 = h.normpart_row0; d.nb_max = h.nb_max; d.lam_words = (h.sum_dims + h.n_vars) * fbn::kW;
 
     p->n_sms = prop.multiProcessorCount;
     cudaError_t ce;
-    int64_t tile_bytes = (int64_t)h.tile_rows * fbn::kLanes * 8;
+    int64_t tile_bytes = (int64_t)h.tile_rows * fbn::kRowDoubles * 8;
     int64_t resident;
     if (level) {
-        resident = std::max<int64_t>(1, std::min<int64_t>(kLevelMaxResident, budget / tile_bytes));
+        int64_t want = kLevelResident;
+        if (const char *e = getenv("FBN_LEVEL_RESIDENT")) want = std::max(1, atoi(e));
+        resident = std::max<int64_t>(1, std::min<int64_t>(std::min<int64_t>(want, kLevelMaxResident), budget / tile_bytes));
         p->launches_per_wave = 2;
         for (const fbn::Phase &ph : h.phases) p->launches_per_wave += 1 + (ph.fin_end > ph.fin_begin ? 1 : 0);
     } else {
@@ -253,7 +259,7 @@ extern "C" int fbn_plan_create(const fbn_tree_desc *tree, const fbn_plan_options
         if (resident * tile_bytes > budget) resident = std::max<int64_t>(1, budget / tile_bytes);
     }
     if (opt && opt->max_resident > 0) resident = std::min<int64_t>(resident, opt->max_resident);
-    if (opt && opt->cases_hint > 0) resident = std::min<int64_t>(resident, ((int64_t)opt->cases_hint + fbn::kLanes - 1) / fbn::kLanes);
+    if (opt && opt->cases_hint > 0) resident = std::min<int64_t>(resident, ((int64_t)opt->cases_hint + fbn::kTileCases - 1) / fbn::kTileCases);
     if (!level && resident >= p->n_sms) resident = resident / p->n_sms * p->n_sms;  // whole waves over the SMs
     p->grid = (int)resident;
     p->scratch_bytes = resident * tile_bytes;
@@ -328,6 +334,7 @@ extern "C" int fbn_plan_get_info(const fbn_plan *p, fbn_plan_info *o) {
     o->marginal_entries = h.marginal_entries; o->scratch_bytes = p->scratch_bytes; o->plan_bytes = p->plan_bytes;
     o->alg_bytes_per_case = h.alg_bytes_per_case; o->kernel_bytes_per_case = h.kernel_bytes_per_case;
     o->flat_records = p->dp.flat;
+    o->tile_cases = fbn::kTileCases; o->view_entries = h.view_entries; o->gather_rows = h.gather_rows;
     o->kernel_rev = kKernelRev;
     return FBN_OK;
 }
@@ -495,14 +502,14 @@ static int run_pipeline(fbn_plan *p, int64_t n_cases, const int64_t *ev_offsets,
     double chunk_mb = 96.0;  // measured on B200 (tools/e2e_sweep.py): 96 MB chunks give the shortest pipeline for 1M ALARM cases
     if (const char *e = getenv("FBN_CHUNK_MB")) chunk_mb = std::max(1.0, atof(e));
     int64_t chunk = (int64_t)(chunk_mb * 1048576.0 / (8.0 * sd));
-    if (!getenv("FBN_CHUNK_MB")) chunk = std::max<int64_t>(chunk, (int64_t)p->grid * fbn::kLanes / 2);  // at least half a wave of tiles
-    chunk = std::min<int64_t>(chunk, std::max<int64_t>(fbn::kLanes, (int64_t)(1024.0 * 1048576.0 / (8.0 * sd))));
+    if (!getenv("FBN_CHUNK_MB")) chunk = std::max<int64_t>(chunk, (int64_t)p->grid * fbn::kTileCases / 2);  // at least half a wave of tiles
+    chunk = std::min<int64_t>(chunk, std::max<int64_t>(fbn::kTileCases, (int64_t)(1024.0 * 1048576.0 / (8.0 * sd))));
     {   // whole waves of resident tiles per chunk when a chunk holds more than one (a ragged last wave runs nearly empty)
-        const int64_t wave = (int64_t)p->grid * fbn::kLanes;
+        const int64_t wave = (int64_t)p->grid * fbn::kTileCases;
         if (chunk > wave) chunk = chunk / wave * wave;
     }
-    chunk = (chunk + fbn::kLanes - 1) / fbn::kLanes * fbn::kLanes;
-    chunk = std::min<int64_t>(chunk, (n_cases + fbn::kLanes - 1) / fbn::kLanes * fbn::kLanes);
+    chunk = (chunk + fbn::kTileCases - 1) / fbn::kTileCases * fbn::kTileCases;
+    chunk = std::min<int64_t>(chunk, (n_cases + fbn::kTileCases - 1) / fbn::kTileCases * fbn::kTileCases);
     std::vector<int64_t> bounds{0};  // chunk boundaries (a ramp of smaller first chunks was measured: no gain)
     while (bounds.back() < n_cases) bounds.push_back(std::min(n_cases, bounds.back() + chunk));
     const int64_t n_chunks = (int64_t)bounds.size() - 1;

@@ -1,8 +1,9 @@
 // sm_100a kernels of the junction-tree hot path. One persistent kernel runs whole test cases:
 //   evidence -> Collect (deepest level first) -> Distribute -> per-variable marginals -> normalise + argmax.
-// Thread mapping: lane = test case inside a 32-case tile, warp = one column of one table. All table indices, evidence
-// masks (32-bit lambda words, one bit per case) and loop bounds are warp-uniform; all scratch accesses are coalesced
-// 256-byte rows and lane-private, so no shuffles or atomics are needed on the data path.
+// Thread mapping: a lane holds kW test cases of a 32*kW-case tile, a warp = one block of targets of one SumOp (plan.h). All
+// table indices, evidence masks (32-bit lambda words, one bit per case) and loop bounds are warp-uniform; all scratch
+// accesses are coalesced rows of 32 x (8*kW)-byte vectors and lane-private, so no shuffles or atomics are needed on the
+// data path. Clique tables are never written: every op recomputes the entries it sums (ops.cuh).
 #include <cstdint>
 #include <cuda_runtime.h>
 
@@ -11,128 +12,40 @@
 
 namespace fbn {
 
-#ifndef FBN_FUSED_STREAM
-#define FBN_FUSED_STREAM 1
-#endif
-constexpr bool kFusedStream = FBN_FUSED_STREAM != 0;
-// tuning experiments: ops as separate functions (own register allocation) instead of inlined into the phase loop
-#ifdef FBN_OPS_NOINLINE
-#define FBN_OP_INLINE __noinline__
-#else
-#define FBN_OP_INLINE __forceinline__
-#endif
-
-struct Smem {
-    uint32_t *lam;    // [sum_dims]  bit l set <=> state allowed for case l of the tile
-    uint32_t *obs;    // [n_vars]    bit l set <=> variable observed in case l
-    uint32_t *mask;   // [max_mask_words] per-phase evidence mask tables: one word per clique row / column
-    double *normacc;  // TEAM == 1: [max_normslots][32]; TEAM > 1: unused (norm shares live in scratch rows, normpart_row0)
-    double *part;     // [max_pslots][32]
-};
-
-// COLLECT op: all units (column block x row chunk) of one clique that this warp owns.
-template <int TEAM, int kColBlock>
-__device__ FBN_OP_INLINE void collect_op(const DevPlan &P, const CollectOp &__restrict__ op, double *S, const Smem &sm, int lane, int warp) {
-    double scale = 1.0;
-    const int32_t *__restrict__ invrows = P.idx32 + op.invrow_off;
-    for (int k = 0; k < op.nchild; ++k) scale *= *row_ptr(S, __ldg(invrows + k));
-    const int units = (op.cols + kColBlock - 1) / kColBlock * op.chunks;
+// One SumOp: all units (target block x row chunk) of the op that this warp owns.
+template <int TEAM, int CB>
+__device__ __forceinline__ void sum_op(const DevPlan &P, const SumOp &__restrict__ op, double *S, const uint32_t *lam, const uint32_t *mask,
+                                       int lane, int warp) {
+    const V scale = op_scale(P, op, S);
+    const int units = (op.cols + CB - 1) / CB * op.chunks;
     const bool tables = op.rowmask_off >= 0;
-    double nacc = 0.0;
+    V nacc = vset(0.0);
     for (int u = (warp - op.rot) & (TEAM - 1); u < units; u += TEAM) {
         int j0, nc, ck, r0, r1;
-        collect_unit<kColBlock>(P, op, u, j0, nc, ck, r0, r1);
-        uint32_t cm[kColBlock];
-        double acc[kColBlock];
+        sum_unit<CB>(P, op, u, j0, nc, ck, r0, r1);
+        M cm[CB];
+        V acc[CB];
 #pragma unroll
-        for (int c = 0; c < kColBlock; ++c) acc[c] = 0.0;
+        for (int c = 0; c < CB; ++c) acc[c] = vset(0.0);
         if (tables) {
 #pragma unroll
-            for (int c = 0; c < kColBlock; ++c) cm[c] = sm.mask[op.colmask_off + min(j0 + c, op.cols - 1)];
-            RowMaskTable rm{sm.mask + op.rowmask_off};
-            collect_block_any<kColBlock, kFusedStream>(P, op, rm, cm, S, lane, j0, nc, r0, r1, scale, acc);
+            for (int c = 0; c < CB; ++c) {
+                const uint32_t *mw = mask + (op.colmask_off + min(j0 + c, op.cols - 1)) * kW;
+#pragma unroll
+                for (int i = 0; i < kW; ++i) cm[c].w[i] = mw[i];
+            }
+            RowMaskTable rm{mask + op.rowmask_off * kW};
+            sum_block_any<CB>(P, op, rm, cm, S, lane, j0, r0, r1, scale, acc);
         } else {
 #pragma unroll
-            for (int c = 0; c < kColBlock; ++c) {
-                const uint16_t *__restrict__ cl16 = P.lam16 + op.collam_off + (int64_t)min(j0 + c, op.cols - 1) * op.ncolv;
-                uint32_t m = 0xffffffffu;
-                for (int i = 0; i < op.ncolv; ++i) m &= sm.lam[__ldg(cl16 + i)];
-                cm[c] = m;
-            }
-            RowMaskLam rm{sm.lam, P.lam16 + op.rowlam_off, op.nrest, 0u};
-            collect_block_any<kColBlock, kFusedStream>(P, op, rm, cm, S, lane, j0, nc, r0, r1, scale, acc);
+            for (int c = 0; c < CB; ++c) cm[c] = col_mask_from_lam(P, op, lam, min(j0 + c, op.cols - 1));
+            RowMaskLam rm{lam, P.lam16 + op.rowlam_off, op.nrest, M()};
+            sum_block_any<CB>(P, op, rm, cm, S, lane, j0, r0, r1, scale, acc);
         }
-#pragma unroll
-        for (int c = 0; c < kColBlock; ++c)
-            if (c < nc) {
-                if (op.chunks > 1) sm.part[(op.pslot0 + (j0 + c) * op.chunks + ck) * kLanes + lane] = acc[c];
-                else *row_ptr(S, op.mup_row + j0 + c) = acc[c];
-                nacc += acc[c];
-            }
+        vadd(nacc, store_unit<CB>(P, op, S, j0, nc, ck, acc));
     }
-    if (TEAM == 1) sm.normacc[op.normslot * kLanes + lane] = nacc;
-    else *row_ptr(S, P.normpart_row0 + op.normslot * TEAM + warp) = nacc;
-}
-
-// PULL op: out[q] = sum_r src[base_q + rest_r] * fac[basecol_q + restcol_r]
-template <int TEAM, int kColBlock>
-__device__ FBN_OP_INLINE void pull_op(const DevPlan &P, const PullOp &__restrict__ op, double *S, const Smem &sm, int lane, int warp) {
-    const int units = (op.nT + kColBlock - 1) / kColBlock * op.chunks;
-    for (int u = (warp - op.rot) & (TEAM - 1); u < units; u += TEAM) {
-        int q0, nq, ck, r0, r1;
-        pull_unit<kColBlock>(op, u, q0, nq, ck, r0, r1);
-        double acc[kColBlock], mup[kColBlock];
-        const bool divide = op.chunks == 1 && op.kind == 1;
-#pragma unroll
-        for (int c = 0; c < kColBlock; ++c) {
-            acc[c] = 0.0;
-            // the divisor is requested before the sum is formed: one memory latency less on the unit's critical path
-            mup[c] = divide ? *row_ptr(S, op.mup_row + min(q0 + c, op.nT - 1)) : 1.0;
-        }
-        pull_block<kColBlock, kFusedStream>(P, op, S, q0, r0, r1, acc);
-#pragma unroll
-        for (int c = 0; c < kColBlock; ++c)
-            if (c < nq) {
-                const int q = q0 + c;
-                if (op.chunks > 1) {
-                    sm.part[(op.pslot0 + q * op.chunks + ck) * kLanes + lane] = acc[c];
-                } else if (op.kind == 1) {
-                    const double m = mup[c];
-                    *row_ptr(S, op.dst_row + q) = (m == 0.0) ? 0.0 : acc[c] / m;  // TableDivision 0-guard, PotentialTable.cpp:718-734
-                } else {
-                    *row_ptr(S, op.dst_row + q) = acc[c];
-                }
-            }
-    }
-}
-
-template <int TEAM>
-__device__ __forceinline__ void fin_item(const DevPlan &P, const FinItem &F, double *S, const Smem &sm, int lane) {
-    double s = 0.0;
-    if (F.type == FIN_NORM) {
-        if (TEAM == 1) {
-            s = sm.normacc[F.slot0 * kLanes + lane];
-        } else {
-            const double *np = row_ptr(S, P.normpart_row0 + F.slot0 * TEAM);
-            constexpr int G = TEAM < 8 ? TEAM : 8;  // independent loads in flight; summed in warp order
-#pragma unroll 1
-            for (int w0 = 0; w0 < TEAM; w0 += G) {
-                double v[G];
-#pragma unroll
-                for (int w = 0; w < G; ++w) v[w] = np[(w0 + w) * kLanes];
-#pragma unroll
-                for (int w = 0; w < G; ++w) s += v[w];
-            }
-        }
-        *row_ptr(S, F.dst_row) = 1.0 / s;
-        return;
-    }
-    for (int i = 0; i < F.nslots; ++i) s += sm.part[(F.slot0 + i) * kLanes + lane];
-    if (F.type == FIN_D) {
-        const double m = *row_ptr(S, F.aux_row);
-        s = (m == 0.0) ? 0.0 : s / m;
-    }
-    *row_ptr(S, F.dst_row) = s;
+    // this warp's share of sum(clique): one row per (collect op of the phase, warp), summed by the phase's FIN_NORM item
+    if (op.kind == SUM_COLLECT) stv(row_ptr(S, P.normpart_row0 + op.normslot * P.nb_max + warp), nacc);
 }
 
 template <int TEAM, int CB>
@@ -142,91 +55,64 @@ __global__ void __launch_bounds__(TEAM * 32, (FBN_OCC / TEAM) > 0 ? (FBN_OCC / T
                                                             const int32_t *__restrict__ ev_vals, int32_t *__restrict__ labels,
                                                             double *__restrict__ post, int64_t n_tiles) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    Smem sm;
-    sm.lam = reinterpret_cast<uint32_t *>(smem_raw);
-    sm.obs = sm.lam + P.sum_dims;
-    size_t o = ((size_t)(P.sum_dims + P.n_vars) * 4 + 15) & ~(size_t)15;
-    sm.mask = reinterpret_cast<uint32_t *>(smem_raw + o);
-    o += ((size_t)P.max_mask_words * 4 + 15) & ~(size_t)15;
-    sm.normacc = reinterpret_cast<double *>(smem_raw + o);
-    sm.part = sm.normacc + (size_t)P.max_normslots * (TEAM == 1 ? kLanes : 0);
+    uint32_t *lam = reinterpret_cast<uint32_t *>(smem_raw);  // [lam_words]: allowed-state words, then observed words
+    uint32_t *mask = reinterpret_cast<uint32_t *>(smem_raw + (((size_t)P.lam_words * 4 + 15) & ~(size_t)15));  // per-phase mask tables
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    double *S = scratch + (int64_t)blockIdx.x * P.tile_rows * kLanes + lane;  // lane-private column of this CTA's tile
+    double *S = scratch + (int64_t)blockIdx.x * P.tile_rows * kRowDoubles + lane * kW;  // lane-private columns of this CTA's tile
+    auto sync = [] { if (TEAM > 1) __syncthreads(); else __syncwarp(); };
 
     for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        // ---- evidence -> lambda bit words (LoadDiscreteEvidence, src/JunctionTree.cpp:316-383, mask form :386-457)
-        if (TEAM > 1) __syncthreads(); else __syncwarp();  // previous tile's readers of lam/obs are done (lanes may diverge)
-        for (int i = threadIdx.x; i < P.sum_dims + P.n_vars; i += TEAM * 32) sm.lam[i] = i < P.sum_dims ? 0xffffffffu : 0u;
-        if (TEAM > 1) __syncthreads(); else __syncwarp();
-        const int64_t cs = tile * kLanes + lane;
-        const bool valid = cs < n_cases;
-        if (valid) {
-            const int64_t k1 = ev_off[cs + 1] - ev_base;
-            for (int64_t k = ev_off[cs] - ev_base + warp; k < k1; k += TEAM) {
-                const int v = ev_vars[k], val = ev_vals[k];
-                if (v < 0 || v >= P.n_vars) continue;  // src/JunctionTree.cpp:326-331
-                const VarInfo vi = P.vars[v];
-                atomicOr(&sm.obs[v], 1u << lane);
-                for (int d = 0; d < vi.dim; ++d)
-                    if (d != val) atomicAnd(&sm.lam[vi.off + d], ~(1u << lane));
-            }
-        }
-        if (TEAM > 1) __syncthreads(); else __syncwarp();
+        sync();  // previous tile's readers of lam are done (lanes may diverge)
+        for (int i = threadIdx.x; i < P.lam_words; i += TEAM * 32) lam[i] = i < P.sum_dims * kW ? 0xffffffffu : 0u;
+        sync();
+        load_evidence(P, lam, tile, n_cases, ev_off, ev_base, ev_vars, ev_vals, lane, warp, TEAM);
+        sync();
 
         for (int ph = 0; ph < P.n_phases; ++ph) {
             const Phase p = P.phases[ph];
-            if (p.kind == 0) {
-                // evidence mask tables of every clique of this phase: lanes work on different rows (warp-uniform data)
-                for (int oi = p.op_begin; oi < p.op_end; ++oi) {
-                    const CollectOp *__restrict__ op = P.cops + P.oplist[oi];
-                    if (op->rowmask_off < 0) continue;
-                    const int nrest = op->nrest, ncolv = op->ncolv, rows = op->rows, cols = op->cols;
-                    const uint16_t *__restrict__ rl16 = P.lam16 + op->rowlam_off;
-                    for (int r = threadIdx.x; r < rows; r += TEAM * 32) {
-                        uint32_t m = 0xffffffffu;
-                        for (int i = 0; i < nrest; ++i) m &= sm.lam[__ldg(rl16 + (int64_t)r * nrest + i)];
-                        sm.mask[op->rowmask_off + r] = m;
+            // evidence mask tables of every op of this phase: threads work on different rows (warp-uniform data)
+            for (int oi = p.op_begin; oi < p.op_end; ++oi) {
+                const SumOp *__restrict__ op = P.ops + P.oplist[oi];
+                if (op->rowmask_off < 0) continue;
+                const int nrest = op->nrest, ncolv = op->ncolv, rows = op->rows, cols = op->cols;
+                const uint16_t *__restrict__ rl16 = P.lam16 + op->rowlam_off;
+                for (int r = threadIdx.x; r < rows; r += TEAM * 32) {
+                    uint32_t m[kW];
+#pragma unroll
+                    for (int i = 0; i < kW; ++i) m[i] = 0xffffffffu;
+                    for (int k = 0; k < nrest; ++k) {
+                        const uint32_t *lw = lam + (int)__ldg(rl16 + (int64_t)r * nrest + k) * kW;
+#pragma unroll
+                        for (int i = 0; i < kW; ++i) m[i] &= lw[i];
                     }
-                    const uint16_t *__restrict__ cl16 = P.lam16 + op->collam_off;
-                    for (int j = threadIdx.x; j < cols; j += TEAM * 32) {
-                        uint32_t m = 0xffffffffu;
-                        for (int i = 0; i < ncolv; ++i) m &= sm.lam[__ldg(cl16 + (int64_t)j * ncolv + i)];
-                        sm.mask[op->colmask_off + j] = m;
+#pragma unroll
+                    for (int i = 0; i < kW; ++i) mask[(op->rowmask_off + r) * kW + i] = m[i];
+                }
+                const uint16_t *__restrict__ cl16 = P.lam16 + op->collam_off;
+                for (int j = threadIdx.x; j < cols; j += TEAM * 32) {
+                    uint32_t m[kW];
+#pragma unroll
+                    for (int i = 0; i < kW; ++i) m[i] = 0xffffffffu;
+                    for (int k = 0; k < ncolv; ++k) {
+                        const uint32_t *lw = lam + (int)__ldg(cl16 + (int64_t)j * ncolv + k) * kW;
+#pragma unroll
+                        for (int i = 0; i < kW; ++i) m[i] &= lw[i];
                     }
-                }
-                if (TEAM > 1) __syncthreads(); else __syncwarp();
-                for (int oi = p.op_begin; oi < p.op_end; ++oi) {
-                    collect_op<TEAM, CB>(P, P.cops[P.oplist[oi]], S, sm, lane, warp);
-                }
-            } else {
-                for (int oi = p.op_begin; oi < p.op_end; ++oi) {
-                    pull_op<TEAM, CB>(P, P.pops[P.oplist[oi]], S, sm, lane, warp);
+#pragma unroll
+                    for (int i = 0; i < kW; ++i) mask[(op->colmask_off + j) * kW + i] = m[i];
                 }
             }
+            sync();
+            for (int oi = p.op_begin; oi < p.op_end; ++oi) sum_op<TEAM, CB>(P, P.ops[P.oplist[oi]], S, lam, mask, lane, warp);
             if (p.fin_end > p.fin_begin) {
-                if (TEAM > 1) __syncthreads();
-                for (int f = p.fin_begin + warp; f < p.fin_end; f += TEAM) fin_item<TEAM>(P, P.fins[f], S, sm, lane);
+                sync();
+                for (int f = p.fin_begin + warp; f < p.fin_end; f += TEAM) fin_item(P, P.fins[f], S, TEAM);
             }
-            if (TEAM > 1) __syncthreads(); else __syncwarp();  // the next phase overwrites the mask tables / partial slots
+            sync();  // the next phase overwrites the mask tables / partial slots and reads this phase's rows
         }
 
-        // ---- posteriors + label (GetProbabilitiesOneNode :1392-1454, Inference::ArgMax Inference.cpp:92-102)
-        for (int v = warp; v < P.n_vars; v += TEAM) {
-            const VarInfo vi = P.vars[v];
-            const bool observed = (sm.obs[v] >> lane) & 1u;
-            const double *mg = row_ptr(S, P.mg_row0 + vi.off);
-            double sum = 0.0;
-            for (int d = 0; d < vi.dim; ++d) sum += mg[d * kLanes];
-            double best = 0.0;
-            int arg = -1;
-            for (int d = 0; d < vi.dim; ++d) {
-                const double pr = observed ? 0.0 : mg[d * kLanes] / sum;
-                if (valid && post) post[cs * P.sum_dims + vi.off + d] = pr;
-                if (pr > best) { best = pr; arg = d; }
-            }
-            if (v == P.query_var && valid && labels) labels[cs] = arg;
-        }
+        for (int v = warp; v < P.n_vars; v += TEAM) output_var(P, S, lam, v, tile, n_cases, lane, labels, post);
     }
 }
 
@@ -296,9 +182,8 @@ __global__ void score_reduce_kernel(int64_t n_cases, const double *__restrict__ 
 
 // ---- launch helpers (called from capi.cu) ------------------------------------------------------------------------
 size_t fused_smem_bytes(const DevPlan &P) {
-    size_t o = ((size_t)(P.sum_dims + P.n_vars) * 4 + 15) & ~(size_t)15;
-    o += ((size_t)P.max_mask_words * 4 + 15) & ~(size_t)15;
-    return o + ((size_t)(P.team == 1 ? P.max_normslots : 0) + (size_t)P.max_pslots) * kLanes * sizeof(double);
+    size_t o = ((size_t)P.lam_words * 4 + 15) & ~(size_t)15;
+    return o + (((size_t)P.max_mask_words * kW * 4 + 15) & ~(size_t)15);
 }
 
 template <int TEAM>
@@ -327,7 +212,7 @@ cudaError_t fused_prepare(const DevPlan &P, int smem_optin, int *blocks_per_sm) 
 
 cudaError_t fused_launch(const DevPlan &P, int grid, double *scratch, int64_t n_cases, const int64_t *ev_off, int64_t ev_base,
                          const int32_t *ev_vars, const int32_t *ev_vals, int32_t *labels, double *post, cudaStream_t st) {
-    const int64_t n_tiles = (n_cases + kLanes - 1) / kLanes;
+    const int64_t n_tiles = (n_cases + kTileCases - 1) / kTileCases;
     if (n_tiles == 0) return cudaSuccess;
     if (grid > n_tiles) grid = (int)n_tiles;
     size_t smem = fused_smem_bytes(P);

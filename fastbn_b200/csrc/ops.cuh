@@ -1,8 +1,9 @@
 // Device-side building blocks shared by the fused kernel (kernels.cu) and the level kernels (level_kernels.cu).
-// Thread mapping everywhere: lane = test case inside a 32-case tile; a warp owns a UNIT = a block of up to CB
-// adjacent columns (collect) / target entries (pull) of one table times a range of rows. Register blocking over the
-// columns gives CB independent 256-byte row loads per index load (memory-level parallelism) and amortises the
-// warp-uniform index loads; all scratch accesses are coalesced 256-byte rows.
+// Thread mapping everywhere: a lane holds kW test cases of a 32*kW-case tile (one 8*kW-byte vector per scratch row: 128-bit
+// loads / stores for kW = 2); a warp owns a UNIT = a block of up to CB adjacent targets of one SumOp (plan.h) times a
+// range of rows of its view. Register blocking over the targets gives CB independent row gathers per index load
+// (memory-level parallelism) and amortises the warp-uniform index loads; all scratch accesses are coalesced rows.
+// Clique entries are recomputed in registers, summed and dropped: the only scratch traffic is message rows.
 #pragma once
 #include <cstdint>
 #include <type_traits>
@@ -12,125 +13,177 @@
 
 namespace fbn {
 
-// rest entries per batch of the QB = 2 PULL loop (fused kernel, >= 2 warps per tile); 1 = plain loop
-#ifndef FBN_PULL_BATCH
-#define FBN_PULL_BATCH 8
+// unroll factor of the single-register-set row loop of the CB = 2 kernels
+#ifndef FBN_SUM_UNROLL_CB2
+#define FBN_SUM_UNROLL_CB2 2
 #endif
-// two register sets in the COLLECT row loop of the CB = 2 (fused, >= 2 warps per tile) kernels too
-#ifndef FBN_TWOSETS_CB2
-#define FBN_TWOSETS_CB2 0
-#endif
-// unroll factor of the single-register-set COLLECT row loop of the CB = 2 kernels
-#ifndef FBN_COLLECT_UNROLL_CB2
-#define FBN_COLLECT_UNROLL_CB2 2
-#endif
-constexpr int kCollectUnrollCB2 = FBN_COLLECT_UNROLL_CB2;
+constexpr int kSumUnrollCB2 = FBN_SUM_UNROLL_CB2;
 
-__device__ __forceinline__ double *row_ptr(double *S, int32_t row) { return S + (int64_t)row * kLanes; }
+// ---- per-lane vectors: the kW cases a lane owns -------------------------------------------------------------------
+struct V {
+    double x[kW];
+};
+struct M {   // evidence mask words: bit l of w[i] <=> case (lane l, slot i) of the tile
+    uint32_t w[kW];
+};
 
-// Cache policy of the two big streams (clique entries written by COLLECT, read once per child by PULL). FBN_STREAM_HINTS
-// marks them evict-first so that the small, heavily re-used rows (messages, ratios, index maps, pristine potentials)
-// keep the L2.
-#ifndef FBN_STREAM_HINTS
-#define FBN_STREAM_HINTS 1
-#endif
-template <bool STREAM>
-__device__ __forceinline__ void store_clique(double *p, double v) {
-    if (STREAM && FBN_STREAM_HINTS) __stcs(p, v);
-    else *p = v;
+// S points at this lane's first double of row 0 of the tile (tile base + lane * kW)
+__device__ __forceinline__ double *row_ptr(double *S, int32_t row) { return S + (int64_t)row * kRowDoubles; }
+__device__ __forceinline__ const double *row_ptr(const double *S, int32_t row) { return S + (int64_t)row * kRowDoubles; }
+
+__device__ __forceinline__ V ldv(const double *p) {
+    V v;
+    if constexpr (kW == 1) {
+        v.x[0] = *p;
+    } else {
+#pragma unroll
+        for (int i = 0; i < kW; i += 2) {
+            const double2 t = *reinterpret_cast<const double2 *>(p + i);   // LDG.E.128
+            v.x[i] = t.x;
+            v.x[i + 1] = t.y;
+        }
+    }
+    return v;
 }
-template <bool STREAM>
-__device__ __forceinline__ double load_clique(const double *p) {
-    if (STREAM && FBN_STREAM_HINTS) return __ldcs(p);
-    return *p;
+__device__ __forceinline__ void stv(double *p, const V &v) {
+    if constexpr (kW == 1) {
+        *p = v.x[0];
+    } else {
+#pragma unroll
+        for (int i = 0; i < kW; i += 2) *reinterpret_cast<double2 *>(p + i) = make_double2(v.x[i], v.x[i + 1]);   // STG.E.128
+    }
+}
+__device__ __forceinline__ V vset(double a) {
+    V v;
+#pragma unroll
+    for (int i = 0; i < kW; ++i) v.x[i] = a;
+    return v;
+}
+__device__ __forceinline__ void vmul(V &a, const V &b) {
+#pragma unroll
+    for (int i = 0; i < kW; ++i) a.x[i] *= b.x[i];
+}
+__device__ __forceinline__ void vadd(V &a, const V &b) {
+#pragma unroll
+    for (int i = 0; i < kW; ++i) a.x[i] += b.x[i];
 }
 
 // ---- row evidence masks -----------------------------------------------------------------------------------------
-// mask word of clique row r: bit l set <=> case l of the tile allows that row (AND of the lambda words of the row's digits)
+// mask of view row r: bit l of word i set <=> case (l, i) of the tile allows that row (AND of the lambda words of the row's digits)
 struct RowMaskTable {  // fused mode, tables built once per phase in shared memory
     static constexpr int kSpan = 1 << 30;  // rows per begin(): the whole range
     const uint32_t *tab;
     __device__ __forceinline__ void begin(int, int, int) {}
-    __device__ __forceinline__ uint32_t get(int r, int) const { return tab[r]; }
+    __device__ __forceinline__ M get(int r, int) const {
+        M m;
+#pragma unroll
+        for (int i = 0; i < kW; ++i) m.w[i] = tab[r * kW + i];
+        return m;
+    }
 };
-struct RowMaskLam {  // evaluated on the fly, lane-parallel: lane i builds the word of row rb+i, get() broadcasts it
+struct RowMaskLam {  // evaluated on the fly, lane-parallel: lane i builds the words of row rb+i, get() broadcasts them
     static constexpr int kSpan = 32;
-    const uint32_t *lam;       // lambda words of the tile (shared or global memory)
+    const uint32_t *lam;       // lambda words of the tile (shared or global memory), kW per (variable, state)
     const uint16_t *rowlam;    // op's rows x nrest lambda indices
     int nrest;
-    uint32_t mine;
+    M mine;
     __device__ __forceinline__ void begin(int rb, int r1, int lane) {
-        mine = 0xffffffffu;
+#pragma unroll
+        for (int i = 0; i < kW; ++i) mine.w[i] = 0xffffffffu;
         if (rb + lane < r1) {
             const uint16_t *__restrict__ rl = rowlam + (int64_t)(rb + lane) * nrest;
-            for (int i = 0; i < nrest; ++i) mine &= lam[__ldg(rl + i)];
+            for (int k = 0; k < nrest; ++k) {
+                const uint32_t *lw = lam + (int)__ldg(rl + k) * kW;
+#pragma unroll
+                for (int i = 0; i < kW; ++i) mine.w[i] &= lw[i];
+            }
         }
     }
-    __device__ __forceinline__ uint32_t get(int r, int rb) const { return __shfl_sync(0xffffffffu, mine, r - rb); }
+    __device__ __forceinline__ M get(int r, int rb) const {
+        M m;
+#pragma unroll
+        for (int i = 0; i < kW; ++i) m.w[i] = __shfl_sync(0xffffffffu, mine.w[i], r - rb);
+        return m;
+    }
 };
 
-// ---- COLLECT -----------------------------------------------------------------------------------------------------
-// Columns [j0, j0+nc) (nc <= CB), rows [r0, r1) of one clique:
-//   C[e] = pristine[e] * scale * mask(e) * prod_k message_k[rowpart_k(r) + colpart_k(j)];  acc[c] += C[r, j0+c]
-// NC = number of children (compile-time 0..3, -1 = generic). Loads of columns beyond nc are clamped to the last column
+// mask of target j of an op, from the lambda words
+__device__ __forceinline__ M col_mask_from_lam(const DevPlan &P, const SumOp &op, const uint32_t *lam, int j) {
+    M m;
+#pragma unroll
+    for (int i = 0; i < kW; ++i) m.w[i] = 0xffffffffu;
+    const uint16_t *__restrict__ cl16 = P.lam16 + op.collam_off + (int64_t)j * op.ncolv;
+    for (int k = 0; k < op.ncolv; ++k) {
+        const uint32_t *lw = lam + (int)__ldg(cl16 + k) * kW;
+#pragma unroll
+        for (int i = 0; i < kW; ++i) m.w[i] &= lw[i];
+    }
+    return m;
+}
+
+// ---- SUM ---------------------------------------------------------------------------------------------------------
+// Targets [j0, j0+nc) (nc <= CB), rows [r0, r1) of one view:
+//   e = pristine[r, j] * scale * mask(r, j) * prod_g message_g[rowpart_g(r) + colpart_g(j)];  acc[c] += e(r, j0+c)
+// NG = number of gathers per entry (compile-time 0..4, -1 = generic). Loads of targets beyond nc are clamped to the last one
 // (valid addresses, results discarded), so the inner loop has no divergent control flow.
-// Row loop of collect_block. UMASK (compile time): children whose message row is the same for all CB columns of the block
-// (one gather per row, folded into the row's scalar factor).
-// Software pipeline: the gathers of row r+1 are issued BEFORE row r is multiplied, masked and stored (two register sets,
-// used alternately), so the memory latency of a row overlaps the arithmetic and the stores of the previous one; the row parts
-// of the child maps are fetched two rows ahead, the coalesced pristine-potential load one group ahead. Rows that need more
-// than 9 gathers keep one register set (gathers issued together at the top of the row). The clique row pointer advances by
-// a 64-bit add, stores go to immediate offsets c * 256 B.
-template <int NC, int UMASK, int CB, bool STREAM, class RowMask>
-__device__ __forceinline__ void collect_rows(const DevPlan &P, const CollectOp &op, RowMask &rmask, const uint32_t (&cm)[CB], double *S,
-                                             int lane, int j0, int nc, int r0, int r1, double scale, const int32_t (&cp)[NC > 0 ? NC : 1][CB],
-                                             double (&acc)[CB]) {
-    constexpr int NCC = NC > 0 ? NC : 1;
-    constexpr int NU = (UMASK & 1) + ((UMASK >> 1) & 1) + ((UMASK >> 2) & 1);
-    constexpr int kGathers = NC > 0 ? (NC - NU) * CB + NU : 0;  // per row
-    constexpr bool kTwoSets = NC > 0 && ((CB >= 4 && kGathers <= 9) || (FBN_TWOSETS_CB2 != 0 && CB == 2 && kGathers <= 6));
-    const int nchild = NC >= 0 ? NC : op.nchild, cols = op.cols;
-    const double *__restrict__ pot = P.pot + op.pot_off;
+// UMASK (compile time): gathers whose row is the same for all CB targets of the block (one gather per row, folded into the
+// row's scalar factor).
+// Software pipeline: the gathers of row r+1 are issued BEFORE row r is multiplied, masked and summed (two register sets,
+// used alternately); the row parts of the index maps are fetched two rows ahead, the coalesced pristine-potential load one
+// group ahead. Rows that need many gathers keep one register set (gathers issued together at the top of the row).
+template <int NG, int UMASK, int CB, class RowMask>
+__device__ __forceinline__ void sum_rows(const DevPlan &P, const SumOp &op, RowMask &rmask, const M (&cm)[CB], const double *S,
+                                         int lane, int j0, int r0, int r1, const V &scale, const int32_t (&cp)[NG > 0 ? NG : 1][CB],
+                                         V (&acc)[CB]) {
+    constexpr int NGC = NG > 0 ? NG : 1;
+    constexpr int NU = (UMASK & 1) + ((UMASK >> 1) & 1) + ((UMASK >> 2) & 1) + ((UMASK >> 3) & 1);
+    constexpr int kGathers = NG > 0 ? (NG - NU) * CB + NU : 0;  // per row
+    constexpr bool kTwoSets = NG > 0 && CB >= 4 && kGathers * kW <= 12;
+    const int ng = NG >= 0 ? NG : op.ng, cols = op.cols;
+    const bool has_pot = op.pot_off >= 0;
+    const double *__restrict__ pot = P.pot + (has_pot ? op.pot_off : 0);
     const int32_t *__restrict__ rowpart = P.idx32 + op.rowpart_off;
     const int32_t *__restrict__ colpart = P.idx32 + op.colpart_off;
-    const int64_t rstride = (int64_t)cols * kLanes;
-    double *clp = row_ptr(S, op.cl_row) + ((int64_t)r0 * cols + j0) * kLanes;
     const uint32_t lanebit = 1u << lane;
-    uint32_t colon = 0;  // bit c: this lane's case allows column j0+c
+    uint32_t colon[kW];  // bit c of word i: case (lane, i) allows target j0+c
 #pragma unroll
-    for (int c = 0; c < CB; ++c)
-        if (cm[c] & lanebit) colon |= 1u << c;
-    // pristine potentials: ONE coalesced load serves RPL rows x CB columns (lane = row-in-group * CB + column), the row
+    for (int i = 0; i < kW; ++i) {
+        colon[i] = 0;
+#pragma unroll
+        for (int c = 0; c < CB; ++c)
+            if (cm[c].w[i] & lanebit) colon[i] |= 1u << c;
+    }
+    // pristine potentials: ONE coalesced load serves RPL rows x CB targets (lane = row-in-group * CB + target), the row
     // loop picks its values by shuffle; a warp-uniform 8-byte load per entry would cost a load instruction (and a
     // scoreboard stall) per entry
     constexpr int RPL = 32 / CB;
     const int lane_c = lane % CB, lane_r = lane / CB;
     const double *potl = pot + min(j0 + lane_c, cols - 1);
-    double potv = 0.0, potv_next = __ldg(potl + (int64_t)min(r0 + lane_r, r1 - 1) * cols);
+    double potv = 1.0, potv_next = has_pot ? __ldg(potl + (int64_t)min(r0 + lane_r, r1 - 1) * cols) : 1.0;
     int rb = r0;
 
-    auto load_parts = [&](int rr, int32_t (&rp)[NCC]) {
-        if (NC > 0) {
-            const int32_t *q = rowpart + (int64_t)min(rr, r1 - 1) * NC;
+    auto load_parts = [&](int rr, int32_t (&rp)[NGC]) {
+        if (NG > 0) {
+            const int32_t *q = rowpart + (int64_t)min(rr, r1 - 1) * NG;
 #pragma unroll
-            for (int k = 0; k < NC; ++k) rp[k] = __ldg(q + k);
+            for (int g = 0; g < NG; ++g) rp[g] = __ldg(q + g);
         }
     };
-    auto gather = [&](const int32_t (&rp)[NCC], double (&m)[NCC][CB]) {
-        if (NC > 0) {
+    auto gather = [&](const int32_t (&rp)[NGC], V (&m)[NGC][CB]) {
+        if (NG > 0) {
 #pragma unroll
-            for (int k = 0; k < NC; ++k) {
-                const double *mb = S + (int64_t)rp[k] * kLanes;
-                if ((UMASK >> k) & 1) {
-                    m[k][0] = mb[(int64_t)cp[k][0] * kLanes];
+            for (int g = 0; g < NG; ++g) {
+                const double *mb = S + (int64_t)rp[g] * kRowDoubles;
+                if ((UMASK >> g) & 1) {
+                    m[g][0] = ldv(mb + (int64_t)cp[g][0] * kRowDoubles);
                 } else {
 #pragma unroll
-                    for (int c = 0; c < CB; ++c) m[k][c] = mb[(int64_t)cp[k][c] * kLanes];
+                    for (int c = 0; c < CB; ++c) m[g][c] = ldv(mb + (int64_t)cp[g][c] * kRowDoubles);
                 }
             }
         }
     };
-    auto finish = [&](int r, const double (&m)[NCC][CB]) {
+    auto finish = [&](int r, const V (&m)[NGC][CB]) {
         if (RowMask::kSpan <= 32 && ((r - r0) & 31) == 0) {
             rb = r;
             rmask.begin(rb, r1, lane);
@@ -138,45 +191,43 @@ __device__ __forceinline__ void collect_rows(const DevPlan &P, const CollectOp &
         const int rg = (r - r0) & (RPL - 1);  // row inside its group of RPL
         if (rg == 0) {
             potv = potv_next;
-            potv_next = __ldg(potl + (int64_t)min(r + RPL + lane_r, r1 - 1) * cols);
+            if (has_pot) potv_next = __ldg(potl + (int64_t)min(r + RPL + lane_r, r1 - 1) * cols);
         }
-        const uint32_t on = (rmask.get(r, rb) & lanebit) ? colon : 0u;
-        double u = scale;
-        if (NC > 0) {
+        const M rm = rmask.get(r, rb);
+        V u = scale;
+        if (NG > 0) {
 #pragma unroll
-            for (int k = 0; k < NC; ++k)
-                if ((UMASK >> k) & 1) u *= m[k][0];
+            for (int g = 0; g < NG; ++g)
+                if ((UMASK >> g) & 1) vmul(u, m[g][0]);
         }
-        double v[CB];
+        double pc[CB];
 #pragma unroll
-        for (int c = 0; c < CB; ++c) v[c] = __shfl_sync(0xffffffffu, potv, rg * CB + c) * u;
-        if (NC > 0) {
+        for (int c = 0; c < CB; ++c) pc[c] = __shfl_sync(0xffffffffu, potv, rg * CB + c);
 #pragma unroll
-            for (int k = 0; k < NC; ++k)
-                if (!((UMASK >> k) & 1)) {
+        for (int i = 0; i < kW; ++i) {
+            const uint32_t on = (rm.w[i] & lanebit) ? colon[i] : 0u;
 #pragma unroll
-                    for (int c = 0; c < CB; ++c) v[c] *= m[k][c];
+            for (int c = 0; c < CB; ++c) {
+                double v = pc[c] * u.x[i];
+                if (NG > 0) {
+#pragma unroll
+                    for (int g = 0; g < NG; ++g)
+                        if (!((UMASK >> g) & 1)) v *= m[g][c].x[i];
+                } else if (NG < 0) {
+                    for (int g = 0; g < ng; ++g) {
+                        const int32_t row = __ldg(rowpart + (int64_t)r * ng + g) + __ldg(colpart + (int64_t)min(j0 + c, cols - 1) * ng + g);
+                        v *= row_ptr(S, row)[i];
+                    }
                 }
-        } else if (NC < 0) {
-            for (int k = 0; k < nchild; ++k) {
-                const int32_t rpk = __ldg(rowpart + (int64_t)r * nchild + k);
-#pragma unroll
-                for (int c = 0; c < CB; ++c) v[c] *= *row_ptr(S, rpk + __ldg(colpart + (int64_t)min(j0 + c, cols - 1) * nchild + k));
+                acc[c].x[i] += ((on >> c) & 1u) ? v : 0.0;
             }
         }
-#pragma unroll
-        for (int c = 0; c < CB; ++c) {
-            const double w = ((on >> c) & 1u) ? v[c] : 0.0;
-            if (c < nc) store_clique<STREAM>(clp + c * kLanes, w);
-            acc[c] += w;
-        }
-        clp += rstride;
     };
 
     if (RowMask::kSpan > 32) rmask.begin(r0, r1, lane);
     if constexpr (kTwoSets) {
-        int32_t rp0[NCC], rp1[NCC];
-        double m0[NCC][CB], m1[NCC][CB];
+        int32_t rp0[NGC], rp1[NGC];
+        V m0[NGC][CB], m1[NGC][CB];
         load_parts(r0, rp0);
         load_parts(r0 + 1, rp1);
         gather(rp0, m0);          // row r0
@@ -193,13 +244,13 @@ __device__ __forceinline__ void collect_rows(const DevPlan &P, const CollectOp &
             }
         }
     } else {
-        int32_t rp[NCC], rpn[NCC];
-        double m[NCC][CB];
+        int32_t rp[NGC], rpn[NGC];
+        V m[NGC][CB];
         load_parts(r0, rpn);
-#pragma unroll(CB >= 4 ? 1 : kCollectUnrollCB2)
+#pragma unroll(CB >= 4 ? 1 : kSumUnrollCB2)
         for (int r = r0; r < r1; ++r) {
 #pragma unroll
-            for (int k = 0; k < NCC; ++k) rp[k] = rpn[k];
+            for (int g = 0; g < NGC; ++g) rp[g] = rpn[g];
             gather(rp, m);
             load_parts(r + 1, rpn);
             finish(r, m);
@@ -207,91 +258,65 @@ __device__ __forceinline__ void collect_rows(const DevPlan &P, const CollectOp &
     }
 }
 
-template <int NC, int CB, bool STREAM, class RowMask>
-__device__ __forceinline__ void collect_block(const DevPlan &P, const CollectOp &op, RowMask &rmask, const uint32_t (&cm)[CB], double *S,
-                                              int lane, int j0, int nc, int r0, int r1, double scale, double (&acc)[CB]) {
-    const int nchild = NC >= 0 ? NC : op.nchild, cols = op.cols;
-    if constexpr (CB == 1 && RowMask::kSpan > 32) {
-        // one column, mask tables in shared memory: the small-tree path (ALARM-size, one warp per tile). Kept as the plain
-        // loop — with 2-4 rows per column the blocking / shuffle / prefetch machinery below costs more than it saves.
-        const int32_t *__restrict__ cpart = P.idx32 + op.colpart_off + (int64_t)j0 * nchild;
-        int32_t cp1[NC > 0 ? NC : 1];
-        if (NC > 0) {
-#pragma unroll
-            for (int k = 0; k < NC; ++k) cp1[k] = __ldg(cpart + k);
-        }
-        const int32_t *__restrict__ rp = P.idx32 + op.rowpart_off + (int64_t)r0 * nchild;
-        const double *__restrict__ pot1 = P.pot + op.pot_off + j0;
-        double *cl1 = row_ptr(S, op.cl_row + j0);
-        double a = 0.0;
-#pragma unroll 2
-        for (int r = r0; r < r1; ++r, rp += nchild) {
-            const uint32_t m = cm[0] & rmask.get(r, r0);
-            const int64_t e = (int64_t)r * cols;
-            double v = __ldg(pot1 + e) * scale;
-            if (NC > 0) {
-#pragma unroll
-                for (int k = 0; k < NC; ++k) v *= *row_ptr(S, __ldg(rp + k) + cp1[k]);
-            } else if (NC < 0) {
-                for (int k = 0; k < nchild; ++k) v *= *row_ptr(S, __ldg(rp + k) + __ldg(cpart + k));
-            }
-            v = ((m >> lane) & 1u) ? v : 0.0;
-            store_clique<STREAM>(cl1 + e * kLanes, v);
-            a += v;
-        }
-        acc[0] += a;
-        return;
-    }
+template <int NG, int CB, class RowMask>
+__device__ __forceinline__ void sum_block(const DevPlan &P, const SumOp &op, RowMask &rmask, const M (&cm)[CB], const double *S,
+                                          int lane, int j0, int r0, int r1, const V &scale, V (&acc)[CB]) {
+    const int cols = op.cols;
     int jc[CB];
 #pragma unroll
     for (int c = 0; c < CB; ++c) jc[c] = min(j0 + c, cols - 1);
-    int32_t cp[NC > 0 ? NC : 1][CB];
+    int32_t cp[NG > 0 ? NG : 1][CB];
     const int32_t *__restrict__ colpart = P.idx32 + op.colpart_off;
-    // umask bit k: all CB columns of the block read the SAME message row of child k (the block's column variables are
-    // outside separator k) -> one gather per row instead of CB, folded into the row's scalar factor
+    // umask bit g: all CB targets of the block read the SAME row of gather g (the block's target variables are outside
+    // that source table) -> one gather per row instead of CB, folded into the row's scalar factor
     int umask = 0;
-    if (NC > 0) {
+    if (NG > 0) {
 #pragma unroll
-        for (int k = 0; k < NC; ++k) {
+        for (int g = 0; g < NG; ++g) {
             bool u = true;
 #pragma unroll
             for (int c = 0; c < CB; ++c) {
-                cp[k][c] = __ldg(colpart + (int64_t)jc[c] * NC + k);
-                u = u && cp[k][c] == cp[k][0];
+                cp[g][c] = __ldg(colpart + (int64_t)jc[c] * NG + g);
+                u = u && cp[g][c] == cp[g][0];
             }
-            if (u) umask |= 1 << k;
+            if (u) umask |= 1 << g;
         }
     }
-    if constexpr (NC > 0 && NC <= 2 && CB >= 4) {
+    if constexpr (NG > 0 && NG <= 2 && CB >= 2) {
         switch (umask) {
-            case 0: collect_rows<NC, 0, CB, STREAM>(P, op, rmask, cm, S, lane, j0, nc, r0, r1, scale, cp, acc); break;
-            case 1: collect_rows<NC, 1, CB, STREAM>(P, op, rmask, cm, S, lane, j0, nc, r0, r1, scale, cp, acc); break;
-            case 2: collect_rows<NC, 2 % (1 << NC), CB, STREAM>(P, op, rmask, cm, S, lane, j0, nc, r0, r1, scale, cp, acc); break;
-            default: collect_rows<NC, (1 << NC) - 1, CB, STREAM>(P, op, rmask, cm, S, lane, j0, nc, r0, r1, scale, cp, acc); break;
+            case 0: sum_rows<NG, 0, CB>(P, op, rmask, cm, S, lane, j0, r0, r1, scale, cp, acc); break;
+            case 1: sum_rows<NG, 1, CB>(P, op, rmask, cm, S, lane, j0, r0, r1, scale, cp, acc); break;
+            case 2: sum_rows<NG, 2 % (1 << NG), CB>(P, op, rmask, cm, S, lane, j0, r0, r1, scale, cp, acc); break;
+            default: sum_rows<NG, (1 << NG) - 1, CB>(P, op, rmask, cm, S, lane, j0, r0, r1, scale, cp, acc); break;
         }
-    } else if constexpr (NC == 3 && CB >= 4) {
-        if (umask == 7) collect_rows<NC, 7, CB, STREAM>(P, op, rmask, cm, S, lane, j0, nc, r0, r1, scale, cp, acc);
-        else collect_rows<NC, 0, CB, STREAM>(P, op, rmask, cm, S, lane, j0, nc, r0, r1, scale, cp, acc);
+    } else if constexpr (NG >= 3 && CB >= 2) {
+        // three or four gathers: specialise the all-uniform block and the common "only the last gather (the clique's own down
+        // ratio, indexed by its trailing variables) differs per target" block
+        constexpr int kAll = (1 << NG) - 1, kButLast = kAll >> 1;
+        if (umask == kAll) sum_rows<NG, kAll, CB>(P, op, rmask, cm, S, lane, j0, r0, r1, scale, cp, acc);
+        else if ((umask & kButLast) == kButLast) sum_rows<NG, kButLast, CB>(P, op, rmask, cm, S, lane, j0, r0, r1, scale, cp, acc);
+        else sum_rows<NG, 0, CB>(P, op, rmask, cm, S, lane, j0, r0, r1, scale, cp, acc);
     } else {
-        collect_rows<NC, 0, CB, STREAM>(P, op, rmask, cm, S, lane, j0, nc, r0, r1, scale, cp, acc);
+        sum_rows<NG, 0, CB>(P, op, rmask, cm, S, lane, j0, r0, r1, scale, cp, acc);
     }
 }
 
-template <int CB, bool STREAM, class RowMask>
-__device__ __forceinline__ void collect_block_any(const DevPlan &P, const CollectOp &op, RowMask &rmask, const uint32_t (&cm)[CB],
-                                                  double *S, int lane, int j0, int nc, int r0, int r1, double scale, double (&acc)[CB]) {
-    switch (op.nchild) {
-        case 0: collect_block<0, CB, STREAM>(P, op, rmask, cm, S, lane, j0, nc, r0, r1, scale, acc); break;
-        case 1: collect_block<1, CB, STREAM>(P, op, rmask, cm, S, lane, j0, nc, r0, r1, scale, acc); break;
-        case 2: collect_block<2, CB, STREAM>(P, op, rmask, cm, S, lane, j0, nc, r0, r1, scale, acc); break;
-        case 3: collect_block<3, CB, STREAM>(P, op, rmask, cm, S, lane, j0, nc, r0, r1, scale, acc); break;
-        default: collect_block<-1, CB, STREAM>(P, op, rmask, cm, S, lane, j0, nc, r0, r1, scale, acc); break;
+template <int CB, class RowMask>
+__device__ __forceinline__ void sum_block_any(const DevPlan &P, const SumOp &op, RowMask &rmask, const M (&cm)[CB], const double *S,
+                                              int lane, int j0, int r0, int r1, const V &scale, V (&acc)[CB]) {
+    switch (op.ng) {
+        case 0: sum_block<0, CB>(P, op, rmask, cm, S, lane, j0, r0, r1, scale, acc); break;
+        case 1: sum_block<1, CB>(P, op, rmask, cm, S, lane, j0, r0, r1, scale, acc); break;
+        case 2: sum_block<2, CB>(P, op, rmask, cm, S, lane, j0, r0, r1, scale, acc); break;
+        case 3: sum_block<3, CB>(P, op, rmask, cm, S, lane, j0, r0, r1, scale, acc); break;
+        case 4: sum_block<4, CB>(P, op, rmask, cm, S, lane, j0, r0, r1, scale, acc); break;
+        default: sum_block<-1, CB>(P, op, rmask, cm, S, lane, j0, r0, r1, scale, acc); break;
     }
 }
 
-// unit u of a collect op -> column block + row range
+// unit u of an op -> target block + row range
 template <int CB>
-__device__ __forceinline__ void collect_unit(const DevPlan &P, const CollectOp &op, int u, int &j0, int &nc, int &ck, int &r0, int &r1) {
+__device__ __forceinline__ void sum_unit(const DevPlan &P, const SumOp &op, int u, int &j0, int &nc, int &ck, int &r0, int &r1) {
     int jb = u;
     ck = 0; r0 = 0; r1 = op.rows;
     if (op.chunks > 1) {
@@ -300,186 +325,116 @@ __device__ __forceinline__ void collect_unit(const DevPlan &P, const CollectOp &
         r0 = ck * op.rows_per_chunk;
         r1 = min(op.rows, r0 + op.rows_per_chunk);
     }
-    if (op.perm_off >= 0) jb = __ldg(P.idx32 + op.perm_off + jb);  // planner's visiting order of the column blocks
+    if (op.perm_off >= 0) jb = __ldg(P.idx32 + op.perm_off + jb);  // planner's visiting order of the target blocks
     j0 = jb * CB;
     nc = min(CB, op.cols - j0);
 }
 
-// ---- PULL --------------------------------------------------------------------------------------------------------
-// targets [q0, q0+nq) (nq <= QB), rest entries [r0, r1):  acc[q] += src[tbase[q].x + trest[r].x] * fac[tbase[q].y + trest[r].y]
-template <int QB, bool STREAM>
-__device__ __forceinline__ void pull_block(const DevPlan &P, const PullOp &op, double *S, int q0, int r0, int r1, double (&acc)[QB]) {
-    const int2 *__restrict__ tb = reinterpret_cast<const int2 *>(P.idx32 + op.tbase_off);
-    const int2 *__restrict__ tr = reinterpret_cast<const int2 *>(P.idx32 + op.trest_off);
-    if constexpr (QB == 1) {  // small-tree path: plain loop, four rest entries in flight
-        const int2 b = __ldg(tb + q0);
-        const double *src1 = row_ptr(S, op.src_row + b.x), *fac1 = row_ptr(S, op.fac_row + b.y);
-        double a = 0.0;
-#pragma unroll 4
-        for (int r = r0; r < r1; ++r) {
-            const int2 t = __ldg(tr + r);
-            a += load_clique<STREAM>(src1 + (int64_t)t.x * kLanes) * fac1[(int64_t)t.y * kLanes];
-        }
-        acc[0] += a;
-        return;
-    }
-    const double *src[QB], *fac[QB];
-    bool uni = true;  // all QB targets share the factor row (their variables are outside the source's column variables)
-#pragma unroll
-    for (int q = 0; q < QB; ++q) {
-        const int2 b = __ldg(tb + min(q0 + q, op.nT - 1));
-        src[q] = row_ptr(S, op.src_row + b.x);
-        fac[q] = row_ptr(S, op.fac_row + b.y);
-        uni = uni && fac[q] == fac[0];
-    }
-    if constexpr (QB == 2 && FBN_PULL_BATCH > 1) {
-        // fused kernel, several warps per tile: batches of RB rest entries. The RB index entries come first (L1-resident,
-        // warp-uniform), then ALL data loads of the batch (RB x QB source rows + RB or RB x QB factor rows) are issued before
-        // the first multiply-add; the sums run in rest order (same rounding as the plain loop). One DRAM latency per batch
-        // instead of one per dependent index -> address -> data chain (measured on B200: RB 4 / 6 / 8 / 12 / 16 -> PIGS-shape
-        // 423 / 428 / 440 / 434 / 435 k cases/s; fetching the next batch's indices ahead costs 8 registers and loses).
-        constexpr int RB = FBN_PULL_BATCH;
-        int r = r0;
-        auto batch = [&](auto uni_c, auto n_c) {  // N rest entries starting at r
-            constexpr bool UNI = decltype(uni_c)::value;
-            constexpr int N = decltype(n_c)::value, NF = UNI ? 1 : QB;
-            int2 t[N];
-#pragma unroll
-            for (int i = 0; i < N; ++i) t[i] = __ldg(tr + r + i);
-            double s[N][QB], f[N][NF];
-#pragma unroll
-            for (int i = 0; i < N; ++i) {
-#pragma unroll
-                for (int q = 0; q < QB; ++q) s[i][q] = load_clique<STREAM>(src[q] + (int64_t)t[i].x * kLanes);
-#pragma unroll
-                for (int q = 0; q < NF; ++q) f[i][q] = fac[q][(int64_t)t[i].y * kLanes];
-            }
-#pragma unroll
-            for (int i = 0; i < N; ++i) {
-#pragma unroll
-                for (int q = 0; q < QB; ++q) acc[q] += s[i][q] * f[i][UNI ? 0 : q];
-            }
-            r += N;
-        };
-        auto batches = [&](auto uni_c) {
-            while (r + RB <= r1) batch(uni_c, std::integral_constant<int, RB>{});
-            // the last < RB rest entries in batches of 4, 2, 1 (table sizes are rarely multiples of RB)
-            if constexpr (RB > 4) {
-                while (r + 4 <= r1) batch(uni_c, std::integral_constant<int, 4>{});
-            }
-            if (r + 2 <= r1) batch(uni_c, std::integral_constant<int, 2>{});
-            if (r + 2 <= r1) batch(uni_c, std::integral_constant<int, 2>{});
-            if (r < r1) batch(uni_c, std::integral_constant<int, 1>{});
-        };
-        if (uni) batches(std::true_type{});
-        else batches(std::false_type{});
-        return;
-    }
-    int2 t_next = __ldg(tr + min(r0, r1 - 1));  // index prefetch, as in collect_block
-    if (uni) {
-#pragma unroll(QB >= 4 ? 2 : 4)
-        for (int r = r0; r < r1; ++r) {
-            const int2 t = t_next;
-            t_next = __ldg(tr + min(r + 1, r1 - 1));
-            const double f = fac[0][(int64_t)t.y * kLanes];
-#pragma unroll
-            for (int q = 0; q < QB; ++q) acc[q] += load_clique<STREAM>(src[q] + (int64_t)t.x * kLanes) * f;
-        }
-        return;
-    }
-#pragma unroll(QB >= 4 ? 2 : 4)
-    for (int r = r0; r < r1; ++r) {
-        const int2 t = t_next;
-        t_next = __ldg(tr + min(r + 1, r1 - 1));
-#pragma unroll
-        for (int q = 0; q < QB; ++q) acc[q] += load_clique<STREAM>(src[q] + (int64_t)t.x * kLanes) * fac[q][(int64_t)t.y * kLanes];
-    }
+// product of the 1/norm rows that scale every entry of an op (PotentialTableBase::Normalize as scalars applied by the consumers)
+__device__ __forceinline__ V op_scale(const DevPlan &P, const SumOp &op, const double *S) {
+    V scale = vset(1.0);
+    const int32_t *__restrict__ invrows = P.idx32 + op.invrow_off;
+    for (int k = 0; k < op.ninv; ++k) vmul(scale, ldv(row_ptr(S, __ldg(invrows + k))));
+    return scale;
 }
 
-// ---- PULL2 (level mode) ----------------------------------------------------------------------------------------------
-// Unit u = (G12 configuration a, block b of QB configurations of G1) of a Pull2Op (plan.h): one pass over the G2
-// configurations gives QB complete entries of separator A and one partial row per G2 configuration for separator B.
-template <int QB>
-__device__ __forceinline__ void pull2_unit(const DevPlan &P, const Pull2Op &op, double *S, int u) {
-    const int4 *__restrict__ ta = reinterpret_cast<const int4 *>(P.idx32 + op.a_off);
-    const int4 *__restrict__ t1 = reinterpret_cast<const int4 *>(P.idx32 + op.g1_off);
-    const int4 *__restrict__ t2 = reinterpret_cast<const int4 *>(P.idx32 + op.g2_off);
-    const int a = u / op.nblk1, b = u - a * op.nblk1;
-    const int4 A = __ldg(ta + a);
-    const int g0 = b * QB, nq = min(QB, op.n1 - g0);
-    const double *src[QB], *fac[QB];
-    int32_t qa[QB];
-    double acc[QB];
-#pragma unroll
-    for (int c = 0; c < QB; ++c) {
-        const int4 G = __ldg(t1 + min(g0 + c, op.n1 - 1));
-        src[c] = row_ptr(S, op.src_row + A.x + G.x);
-        fac[c] = row_ptr(S, op.fac_row + A.y + G.y);
-        qa[c] = A.z + G.z;
-        acc[c] = 0.0;
-    }
-    double *part = row_ptr(S, P.part_row0 + op.pslot0) + ((int64_t)A.w * op.nblk1 + b) * kLanes;
-    const int64_t pstride = (int64_t)op.nblk1 * kLanes;
-    // software pipeline, two register sets: the 2*QB loads of configuration r+1 are issued before configuration r is
-    // multiplied, accumulated and its partial row stored; the index entries are fetched two configurations ahead
-    auto loads = [&](const int4 &R, double (&sv)[QB], double (&fv)[QB]) {
-#pragma unroll
-        for (int c = 0; c < QB; ++c) {
-            sv[c] = load_clique<true>(src[c] + (int64_t)R.x * kLanes);
-            fv[c] = fac[c][(int64_t)R.y * kLanes];
-        }
-    };
-    auto finish = [&](const int4 &R, const double (&sv)[QB], const double (&fv)[QB]) {
-        double prod[QB];
-#pragma unroll
-        for (int c = 0; c < QB; ++c) {
-            prod[c] = sv[c] * fv[c];
-            acc[c] += prod[c];
-            if (c >= nq) prod[c] = 0.0;  // clamped duplicates of a ragged last block do not belong to the partial
-        }
-        // fixed pairwise order (deterministic)
-#pragma unroll
-        for (int w = 1; w < QB; w *= 2)
-#pragma unroll
-            for (int c = 0; c + w < QB; c += 2 * w) prod[c] += prod[c + w];
-        part[(int64_t)R.z * pstride] = prod[0];
-    };
-    double s0[QB], f0[QB], s1[QB], f1[QB];
-    int4 Ra = __ldg(t2), Rb = __ldg(t2 + min(1, op.n2 - 1));
-    loads(Ra, s0, f0);
-    for (int r = 0; r < op.n2; r += 2) {
-        // here: (s0, f0) = configuration r (in flight), Ra its index entry, Rb the entry of r+1
-        loads(Rb, s1, f1);
-        const int4 Rc = __ldg(t2 + min(r + 2, op.n2 - 1));
-        finish(Ra, s0, f0);
-        if (r + 1 < op.n2) {
-            loads(Rc, s0, f0);
-            const int4 Rd = __ldg(t2 + min(r + 3, op.n2 - 1));
-            finish(Rb, s1, f1);
-            Rb = Rd;
-        }
-        Ra = Rc;
-    }
-#pragma unroll
-    for (int c = 0; c < QB; ++c)
-        if (c < nq) {
-            const double m = *row_ptr(S, op.mupA_row + qa[c]);
-            *row_ptr(S, op.dstA_row + qa[c]) = (m == 0.0) ? 0.0 : acc[c] / m;  // TableDivision 0-guard, PotentialTable.cpp:718-734
-        }
-}
-
+// what happens to the finished sums of a unit: partial slot, or the op's own finaliser. Returns the sum of the unit's targets
+// (a collect op's share of the clique norm).
 template <int CB>
-__device__ __forceinline__ void pull_unit(const PullOp &op, int u, int &q0, int &nq, int &ck, int &r0, int &r1) {
-    int qb = u;
-    ck = 0; r0 = 0; r1 = op.nR;
-    if (op.chunks > 1) {
-        qb = u / op.chunks;
-        ck = u - qb * op.chunks;
-        r0 = ck * op.rows_per_chunk;
-        r1 = min(op.nR, r0 + op.rows_per_chunk);
+__device__ __forceinline__ V store_unit(const DevPlan &P, const SumOp &op, double *S, int j0, int nc, int ck, const V (&acc)[CB]) {
+    V nacc = vset(0.0);
+#pragma unroll
+    for (int c = 0; c < CB; ++c)
+        if (c < nc) {
+            const int j = j0 + c;
+            if (op.chunks > 1) {
+                stv(row_ptr(S, P.part_row0 + op.pslot0 + j * op.chunks + ck), acc[c]);
+            } else if (op.kind == SUM_DISTRIBUTE) {
+                const V up = ldv(row_ptr(S, op.aux_row + j));
+                V d;
+#pragma unroll
+                for (int i = 0; i < kW; ++i) d.x[i] = (up.x[i] == 0.0) ? 0.0 : acc[c].x[i];  // TableDivision 0 guard, PotentialTable.cpp:718-734
+                stv(row_ptr(S, op.dst_row + j), d);
+            } else {
+                stv(row_ptr(S, op.dst_row + j), acc[c]);
+            }
+            vadd(nacc, acc[c]);
+        }
+    return nacc;
+}
+
+// finaliser of a phase: sums of partial slots / norm shares. `shares` = norm shares per collect op actually written.
+__device__ __forceinline__ void fin_item(const DevPlan &P, const FinItem &F, double *S, int shares) {
+    V s = vset(0.0);
+    if (F.type == FIN_NORM) {
+        const double *np = row_ptr(S, P.normpart_row0 + F.slot0 * P.nb_max);
+        for (int b0 = 0; b0 < shares; b0 += 4) {   // four independent loads in flight; summed in share order
+            V v[4];
+#pragma unroll
+            for (int b = 0; b < 4; ++b) v[b] = ldv(np + (int64_t)min(b0 + b, shares - 1) * kRowDoubles);
+#pragma unroll
+            for (int b = 0; b < 4; ++b)
+                if (b0 + b < shares) vadd(s, v[b]);
+        }
+#pragma unroll
+        for (int i = 0; i < kW; ++i) s.x[i] = 1.0 / s.x[i];
+        stv(row_ptr(S, F.dst_row), s);
+        return;
     }
-    q0 = qb * CB;
-    nq = min(CB, op.nT - q0);
+    const double *pp = row_ptr(S, P.part_row0 + F.slot0);
+    for (int i = 0; i < F.nslots; ++i) vadd(s, ldv(pp + (int64_t)i * kRowDoubles));
+    if (F.type == FIN_D) {
+        const V up = ldv(row_ptr(S, F.aux_row));
+#pragma unroll
+        for (int i = 0; i < kW; ++i)
+            if (up.x[i] == 0.0) s.x[i] = 0.0;
+    }
+    stv(row_ptr(S, F.dst_row), s);
+}
+
+// ---- evidence -> lambda words (LoadDiscreteEvidence, src/JunctionTree.cpp:316-383, mask form :386-457) ------------------
+// lam[(off_v + d) * kW + i] bit l: state d of variable v allowed for case (l, i); lam[(sum_dims + v) * kW + i] bit l: v observed.
+// Called by `nw` warps that share the tile (warp `warp` takes every nw-th evidence pair); lam must be initialised.
+__device__ __forceinline__ void load_evidence(const DevPlan &P, uint32_t *lam, int64_t tile, int64_t n_cases, const int64_t *ev_off,
+                                              int64_t ev_base, const int32_t *ev_vars, const int32_t *ev_vals, int lane, int warp, int nw) {
+#pragma unroll
+    for (int i = 0; i < kW; ++i) {
+        const int64_t cs = tile * kTileCases + lane * kW + i;
+        if (cs >= n_cases) continue;
+        const int64_t k1 = ev_off[cs + 1] - ev_base;
+        for (int64_t k = ev_off[cs] - ev_base + warp; k < k1; k += nw) {
+            const int v = ev_vars[k], val = ev_vals[k];
+            if (v < 0 || v >= P.n_vars) continue;  // src/JunctionTree.cpp:326-331
+            const VarInfo vi = P.vars[v];
+            atomicOr(&lam[(P.sum_dims + v) * kW + i], 1u << lane);
+            for (int d = 0; d < vi.dim; ++d)
+                if (d != val) atomicAnd(&lam[(vi.off + d) * kW + i], ~(1u << lane));
+        }
+    }
+}
+
+// ---- posteriors + label of one variable (GetProbabilitiesOneNode src/JunctionTree.cpp:1392-1454, Inference::ArgMax
+//      src/Inference.cpp:92-102): normalise the unnormalised marginal rows, zeros for an observed variable
+__device__ __forceinline__ void output_var(const DevPlan &P, const double *S, const uint32_t *lam, int v, int64_t tile, int64_t n_cases,
+                                           int lane, int32_t *labels, double *post) {
+    const VarInfo vi = P.vars[v];
+    const double *mg = row_ptr(S, P.mg_row0 + vi.off);
+#pragma unroll
+    for (int i = 0; i < kW; ++i) {
+        const int64_t cs = tile * kTileCases + lane * kW + i;
+        const bool valid = cs < n_cases;
+        const bool observed = (lam[(P.sum_dims + v) * kW + i] >> lane) & 1u;
+        double sum = 0.0;
+        for (int d = 0; d < vi.dim; ++d) sum += mg[(int64_t)d * kRowDoubles + i];
+        double best = 0.0;
+        int arg = -1;
+        for (int d = 0; d < vi.dim; ++d) {
+            const double pr = observed ? 0.0 : mg[(int64_t)d * kRowDoubles + i] / sum;
+            if (valid && post) post[cs * P.sum_dims + vi.off + d] = pr;
+            if (pr > best) { best = pr; arg = d; }
+        }
+        if (v == P.query_var && valid && labels) labels[cs] = arg;
+    }
 }
 
 }  // namespace fbn

@@ -28,9 +28,9 @@ extern "C" {
 #define FBN_ERR_NOMEM 4
 #define FBN_ERR_COMM 5      /* NCCL could not be loaded or an NCCL call failed (fbn_comm_*, fbn_reduce) */
 
-/* Execution modes. FUSED: one persistent kernel, one CTA per tile of 32 cases, whole tree per launch (small / medium
- * trees). LEVEL: one launch per tree level over all resident tiles, many CTAs per tile, big tables split across CTAs with a
- * two-stage reduction (PIGS-/MUNIN-shape). AUTO picks by table sizes. */
+/* Execution modes. FUSED: one persistent kernel, one CTA per tile (fbn_plan_info.tile_cases test cases), whole tree per
+ * launch (small / medium trees). LEVEL: one launch per tree level over all resident tiles, many CTAs per tile, big tables
+ * split across CTAs with a two-stage reduction (MUNIN-shape). AUTO picks by table sizes. */
 #define FBN_MODE_AUTO 0
 #define FBN_MODE_FUSED 1
 #define FBN_MODE_LEVEL 2
@@ -66,7 +66,7 @@ typedef struct fbn_plan fbn_plan; /* opaque: device-resident flattened tree + sc
 
 typedef struct fbn_plan_options {
     int32_t device;        /* CUDA device ordinal; -1 = current device */
-    int32_t team_warps;    /* fused mode: warps (power of two <= 32) of the one CTA that owns a 32-case tile;
+    int32_t team_warps;    /* fused mode: warps (power of two <= 32) of the one CTA that owns a tile;
                               level mode: nominal warps per tile over all CTAs of a phase launch; 0 = choose */
     int32_t max_resident;  /* cap on resident tiles (scratch = max_resident x tile bytes); 0 = choose */
     int32_t mode;          /* FBN_MODE_AUTO / FBN_MODE_FUSED / FBN_MODE_LEVEL */
@@ -92,6 +92,10 @@ typedef struct fbn_plan_info {
     double kernel_bytes_per_case;/* bytes the fused kernel itself moves per case (scratch r/w + output) */
     int32_t flat_records;        /* 1: small tree run by jt_flat_kernel (one warp per tile, per-entry records), else 0 */
     int32_t kernel_rev;          /* revision of the kernels' memory behaviour: ncu traffic figures are valid for one revision only */
+    int32_t tile_cases;          /* test cases per tile (32 lanes x cases per lane) */
+    int32_t reserved;
+    int64_t view_entries;        /* clique entries recomputed per case, summed over all ops (collect + distribute + marginals) */
+    int64_t gather_rows;         /* message rows gathered per case, before register blocking */
 } fbn_plan_info;
 
 typedef struct fbn_stats {
