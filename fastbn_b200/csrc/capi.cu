@@ -21,7 +21,7 @@ size_t flat_smem_bytes(const DevPlan &P);
 cudaError_t flat_prepare(const DevPlan &P, int smem_optin, int *blocks_per_sm);
 cudaError_t flat_launch(const DevPlan &P, int grid, double *scratch, int64_t n_cases, const int64_t *ev_off, int64_t ev_base,
                         const int32_t *ev_vars, const int32_t *ev_vals, int32_t *labels, double *post, cudaStream_t st);
-cudaError_t level_launch(const DevPlan &P, const std::vector<Phase> &phases, int resident, double *scratch, uint32_t *lamG,
+cudaError_t level_launch(const DevPlan &P, const std::vector<Phase> &phases, int resident, double *scratch, uint8_t *patG,
                          int64_t n_cases, const int64_t *ev_off, int64_t ev_base, const int32_t *ev_vars, const int32_t *ev_vals,
                          int32_t *labels, double *post, cudaStream_t st, int64_t *n_launch);
 cudaError_t score_cases_launch(int64_t n_cases, int n_vars, int sum_dims, const VarInfo *vars, const double *post, const double *golden,
@@ -38,7 +38,7 @@ int fbn_set_error(int code, const std::string &msg) { return fail(code, msg); } 
 
 // Revision of the kernels' memory behaviour. bench.py attaches an ncu traffic figure (profiles/traffic.json) to a run only
 // when it was captured at the same revision: bump on every change that alters what the kernels read or write.
-static const int kKernelRev = 2;
+static const int kKernelRev = 3;
 #define CK(call)                                                                                       \
     do {                                                                                               \
         cudaError_t e__ = (call);                                                                      \
@@ -76,7 +76,7 @@ struct fbn_plan {
     int n_sms = 0, blocks_per_sm = 0, grid = 0;
     std::vector<void *> dev_allocs;
     double *scratch = nullptr;
-    uint32_t *lamG = nullptr;   // level mode: evidence bit words of the resident tiles
+    uint8_t *patG = nullptr;    // level mode: evidence pattern bytes of the resident tiles
     bool level = false;
     int launches_per_wave = 1;
     int64_t scratch_bytes = 0, plan_bytes = 0;
@@ -147,9 +147,8 @@ static int pick_team(double entries) {
     // fused mode: more warps per tile for bigger tables; 16 resident warps per SM at 128 registers (two cases per lane), so a
     // team of T warps runs 16 / T tiles per SM
     if (entries <= 8192) return 1;
-    if (entries <= 131072) return 4;
-    if (entries <= 524288) return 8;
-    return 16;
+    if (entries <= 131072) return 8;   // HEPAR2 shape: 8 warps 2.62 M cases/s, 4 warps 2.47 M
+    return 16;                         // PIGS shape: 16 warps 573 k cases/s, 8 warps 537 k
 }
 
 // one inference pass over n_cases cases whose inputs are on the device: fused kernel or the per-level launches
@@ -157,7 +156,7 @@ static cudaError_t launch_inference(fbn_plan *p, int64_t n_cases, const int64_t 
                                     const int32_t *ev_vals, int32_t *labels, double *post, cudaStream_t st, int64_t *n_launch) {
     if (n_cases <= 0) { *n_launch = 0; return cudaSuccess; }
     if (p->level)
-        return fbn::level_launch(p->dp, p->hp.phases, p->grid, p->scratch, p->lamG, n_cases, ev_off, ev_base, ev_vars, ev_vals,
+        return fbn::level_launch(p->dp, p->hp.phases, p->grid, p->scratch, p->patG, n_cases, ev_off, ev_base, ev_vars, ev_vals,
                                  labels, post, st, n_launch);
     *n_launch = 1;
     if (p->dp.flat)
@@ -224,14 +223,15 @@ extern "C" int fbn_plan_create(const fbn_tree_desc *tree, const fbn_plan_options
     fbn::DevPlan &d = p->dp;
     int rc;
 #define UP(field) if ((rc = upload(p, h.field, &d.field)) != FBN_OK) { fbn_plan_destroy(p); return rc; }
-    UP(pot) UP(lam16) UP(idx32) UP(flatc) UP(ops) UP(oplist) UP(fins) UP(phases) UP(vars)
+    UP(pot) UP(idx32) UP(flatc) UP(lamvars) UP(ops) UP(oplist) UP(fins) UP(phases) UP(vars)
 #undef UP
     d.n_phases = (int32_t)h.phases.size();
     d.n_vars = h.n_vars; d.sum_dims = h.sum_dims; d.query_var = h.query_var;
     d.tile_rows = h.tile_rows; d.mg_row0 = h.mg_row0;
-    d.max_normslots = h.max_normslots; d.max_pslots = h.max_pslots; d.max_mask_words = h.max_mask_words; d.team = h.team; d.cb = h.cb;
+    d.max_normslots = h.max_normslots; d.max_pslots = h.max_pslots; d.team = h.team; d.cb = h.cb;
+    d.n_lamvars = (int32_t)h.lamvars.size(); d.lam_row0 = h.lam_row0;
     d.flat = h.flat ? 1 : 0;
-    d.part_row0 = h.part_row0; d.normpart_row0 = h.normpart_row0; d.nb_max = h.nb_max; d.lam_words = (h.sum_dims + h.n_vars) * fbn::kW;
+    d.part_row0 = h.part_row0; d.normpart_row0 = h.normpart_row0; d.nb_max = h.nb_max; d.pat_bytes = h.n_vars * fbn::kTileCases;
 
     p->n_sms = prop.multiProcessorCount;
     cudaError_t ce;
@@ -279,8 +279,8 @@ extern "C" int fbn_plan_create(const fbn_tree_desc *tree, const fbn_plan_options
     } while (0)
     CKP(cudaMemset(p->scratch, 0, (size_t)p->scratch_bytes));
     if (level) {
-        CKP(cudaMalloc((void **)&p->lamG, (size_t)resident * d.lam_words * 4));
-        p->plan_bytes += resident * (int64_t)d.lam_words * 4;
+        CKP(cudaMalloc((void **)&p->patG, (size_t)resident * d.pat_bytes));
+        p->plan_bytes += resident * (int64_t)d.pat_bytes;
     }
     CKP(cudaStreamCreateWithFlags(&p->s_in, cudaStreamNonBlocking));
     CKP(cudaStreamCreateWithFlags(&p->s_k, cudaStreamNonBlocking));
@@ -310,7 +310,7 @@ extern "C" void fbn_plan_destroy(fbn_plan *p) {
     cudaDeviceSynchronize();
     for (void *d : p->dev_allocs) cudaFree(d);
     cudaFree(p->scratch);
-    cudaFree(p->lamG);
+    cudaFree(p->patG);
     cudaFree(p->score_case);
     cudaFree(p->score_out4);
     for (auto &b : p->buf) free_chunk(b);

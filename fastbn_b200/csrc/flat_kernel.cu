@@ -2,9 +2,12 @@
 // Same SumOps, scratch layout and phase order as jt_fused_kernel<1,1> (kernels.cu), but the per-table index arithmetic is
 // taken out of the inner loop: the planner writes one RECORD per view entry (pristine potential + the absolute scratch rows
 // of the message entries it multiplies with), target-major — plan.h, SumOp::flat_off. The loop is then: load a batch of
-// records (warp-uniform 16-byte loads), issue all their gathers (one 128-bit load per lane and gather for kW = 2), do the
-// arithmetic; the end of a target's sum is a warp-uniform counter. Nothing but message rows is written: the entries are
-// recomputed by every op that needs them, so a case costs its messages in HBM traffic, not its cliques.
+// records (warp-uniform 16-byte loads), issue all their loads (each case's potential under its own evidence pattern, one
+// 128-bit load per lane and gather for kW = 2), do the arithmetic; the end of a target's sum is a warp-uniform counter.
+// Nothing but message rows is written: the entries are recomputed by every op that needs them, so a case costs its messages
+// in HBM traffic, not its cliques; evidence costs no per-entry test (pattern-folded potentials, plan.h).
+// Measured and rejected on B200 (round 2): a software pipeline over the batches (two register sets, the loads of batch k+1
+// in flight while batch k is summed): 131-149 M ALARM cases/s at 16-32 warps per SM against 158 M without (spills).
 #include <cstdint>
 #include <type_traits>
 
@@ -18,26 +21,31 @@ namespace fbn {
 namespace {
 
 #ifndef FBN_FLAT_BATCH
-#define FBN_FLAT_BATCH 4
+#define FBN_FLAT_BATCH 2   // measured on B200 (ALARM, 64 registers x 32 warps per SM): batch 2 158 M cases/s, batch 4 (spills) 125 M
 #endif
-constexpr int kBatch = FBN_FLAT_BATCH;  // records per batch: their loads are all issued before the first use
-
-// one SumOp of a flat plan, NG = gathers per entry (0..6)
+// records per batch: their loads are all issued before the first use. Ops with many gathers per entry take smaller batches
+// (the gathered vectors of a batch live in registers: batch x gathers x 2*kW registers).
 template <int NG>
-__device__ __forceinline__ void flat_sum(const DevPlan &P, const SumOp &__restrict__ op, double *S, const uint32_t *mask, int lane) {
+struct FlatBatch {
+    static constexpr int value = NG <= 2 ? FBN_FLAT_BATCH : (NG <= 4 ? (FBN_FLAT_BATCH + 1) / 2 : 1);
+};
+
+// one SumOp of a flat plan, NG = gathers per entry (0..4)
+template <int NG>
+__device__ __forceinline__ void flat_sum(const DevPlan &P, const SumOp &__restrict__ op, double *S, const uint8_t *pat, int lane) {
+    constexpr int kBatch = FlatBatch<NG>::value;
     const V scale = op_scale(P, op, S);
-    constexpr int kStride = NG > 2 ? 2 : 1;
+    const Fx fx = op_fx(P, op, pat, lane);
+    constexpr int kStride = NG > 3 ? 2 : 1;
     const int4 *__restrict__ rec = reinterpret_cast<const int4 *>(P.flatc + op.flat_off);
-    const uint32_t *rmt = mask + op.rowmask_off * kW, *cmt = mask + op.colmask_off * kW;
-    const uint32_t lanebit = 1u << lane;
+    const double *__restrict__ potl[kW];   // this lane's pattern slots of the potentials
+#pragma unroll
+    for (int i = 0; i < kW; ++i) potl[i] = P.pot + fx.x[i];
     const int rows = op.rows, cols = op.cols, n = rows * cols;
     const bool guard = op.kind == SUM_DISTRIBUTE;
     double *dst = row_ptr(S, op.dst_row);
     const double *aux = row_ptr(S, guard ? op.aux_row : op.dst_row);
     int r = 0, j = 0;
-    bool con[kW];
-#pragma unroll
-    for (int i = 0; i < kW; ++i) con[i] = (cmt[i] & lanebit) != 0;
     V up = vset(1.0);  // the child's up message entry of the current target, requested when the target begins (0 guard)
     if (guard) up = ldv(aux);
     V acc = vset(0.0), nacc = vset(0.0);
@@ -48,44 +56,42 @@ __device__ __forceinline__ void flat_sum(const DevPlan &P, const SumOp &__restri
         for (int b = 0; b < kBatch; ++b) {
             const int e = kFull ? e0 + b : min(e0 + b, n - 1);
             A[b] = __ldg(rec + (int64_t)e * kStride);
-            if (NG > 2) B[b] = __ldg(rec + (int64_t)e * kStride + 1);
+            if (NG > 3) B[b] = __ldg(rec + (int64_t)e * kStride + 1);
         }
+        double pv[kBatch][kW];
         V m[kBatch][NG > 0 ? NG : 1];
 #pragma unroll
         for (int b = 0; b < kBatch; ++b) {
-            if (NG > 0) m[b][0] = ldv(row_ptr(S, A[b].z));
-            if (NG > 1) m[b][1] = ldv(row_ptr(S, A[b].w));
-            if (NG > 2) m[b][2] = ldv(row_ptr(S, B[b].x));
-            if (NG > 3) m[b][3] = ldv(row_ptr(S, B[b].y));
-            if (NG > 4) m[b][4] = ldv(row_ptr(S, B[b].z));
-            if (NG > 5) m[b][5] = ldv(row_ptr(S, B[b].w));
+#pragma unroll
+            for (int i = 0; i < kW; ++i) pv[b][i] = __ldg(potl[i] + A[b].x);
+            if (NG > 0) m[b][0] = ldv(row_ptr(S, A[b].y));
+            if (NG > 1) m[b][1] = ldv(row_ptr(S, A[b].z));
+            if (NG > 2) m[b][2] = ldv(row_ptr(S, A[b].w));
+            if (NG > 3) m[b][3] = ldv(row_ptr(S, B[b].x));
         }
 #pragma unroll
         for (int b = 0; b < kBatch; ++b) {
             if (kFull || e0 + b < n) {
-                const double pv = __hiloint2double(A[b].y, A[b].x);
 #pragma unroll
                 for (int i = 0; i < kW; ++i) {
-                    double v = pv * scale.x[i];
+                    double v = pv[b][i];
 #pragma unroll
                     for (int g = 0; g < NG; ++g) v *= m[b][g].x[i];
-                    acc.x[i] += (con[i] && (rmt[r * kW + i] & lanebit)) ? v : 0.0;
+                    acc.x[i] += v;
                 }
                 if (++r == rows) {  // end of target j
-                    V d = acc;
+                    const V a = finish_target(P, op, pat, lane, j, acc, scale);
+                    V d = a;
                     if (guard) {
 #pragma unroll
-                        for (int i = 0; i < kW; ++i) d.x[i] = (up.x[i] == 0.0) ? 0.0 : acc.x[i];  // TableDivision 0 guard, PotentialTable.cpp:718-734
+                        for (int i = 0; i < kW; ++i) d.x[i] = (up.x[i] == 0.0) ? 0.0 : a.x[i];  // TableDivision 0 guard, PotentialTable.cpp:718-734
                     }
                     stv(dst + (int64_t)j * kRowDoubles, d);
-                    vadd(nacc, acc);
+                    vadd(nacc, a);
                     acc = vset(0.0);
                     r = 0;
                     ++j;
-                    const int jn = min(j, cols - 1);
-#pragma unroll
-                    for (int i = 0; i < kW; ++i) con[i] = j < cols && (cmt[jn * kW + i] & lanebit) != 0;
-                    if (guard) up = ldv(aux + (int64_t)jn * kRowDoubles);
+                    if (guard) up = ldv(aux + (int64_t)min(j, cols - 1) * kRowDoubles);
                 }
             }
         }
@@ -100,10 +106,46 @@ __device__ __forceinline__ void flat_sum(const DevPlan &P, const SumOp &__restri
     }
 }
 
+// ops with more than four gathers per entry (cliques with more than three children: rare): plain loop, its own register
+// allocation, so that the common instantiations above keep theirs
+__device__ __noinline__ void flat_sum_generic(const DevPlan &P, const SumOp &__restrict__ op, double *S, const uint8_t *pat, int lane) {
+    const V scale = op_scale(P, op, S);
+    const Fx fx = op_fx(P, op, pat, lane);
+    const int ng = op.ng, stride = ng > 3 ? 8 : 4;
+    const int32_t *__restrict__ rec = P.flatc + op.flat_off;
+    const bool guard = op.kind == SUM_DISTRIBUTE;
+    V nacc = vset(0.0);
+    for (int j = 0; j < op.cols; ++j) {
+        V acc = vset(0.0);
+        for (int r = 0; r < op.rows; ++r) {
+            const int32_t *q = rec + ((int64_t)j * op.rows + r) * stride;
+            V v;
+#pragma unroll
+            for (int i = 0; i < kW; ++i) v.x[i] = __ldg(P.pot + __ldg(q) + fx.x[i]);
+            for (int g = 0; g < ng; ++g) vmul(v, ldv(row_ptr(S, __ldg(q + 1 + g))));
+            vadd(acc, v);
+        }
+        V a = finish_target(P, op, pat, lane, j, acc, scale);
+        vadd(nacc, a);
+        if (guard) {
+            const V up = ldv(row_ptr(S, op.aux_row + j));
+#pragma unroll
+            for (int i = 0; i < kW; ++i)
+                if (up.x[i] == 0.0) a.x[i] = 0.0;  // TableDivision 0 guard, PotentialTable.cpp:718-734
+        }
+        stv(row_ptr(S, op.dst_row + j), a);
+    }
+    if (op.kind == SUM_COLLECT) {
+#pragma unroll
+        for (int i = 0; i < kW; ++i) nacc.x[i] = 1.0 / nacc.x[i];
+        stv(row_ptr(S, op.inv_row), nacc);
+    }
+}
+
 }  // namespace
 
 #ifndef FBN_FLAT_OCC
-#define FBN_FLAT_OCC 16   // resident warps per SM the register allocation is bounded for
+#define FBN_FLAT_OCC 32   // resident warps per SM the register allocation is bounded for (measured on B200, batch 2: 32 -> 158 M, 24 -> 151 M ALARM cases/s)
 #endif
 #ifndef FBN_FLAT_WPC
 #define FBN_FLAT_WPC 1    // warps per CTA; every warp runs its own tiles (an SM holds at most 32 CTAs, so > 32 warps need WPC > 1)
@@ -115,78 +157,40 @@ __global__ void __launch_bounds__(32 * kWpc, FBN_FLAT_OCC / kWpc) jt_flat_kernel
                                                          int32_t *__restrict__ labels, double *__restrict__ post, int64_t n_tiles) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const size_t lam_bytes = ((size_t)P.lam_words * 4 + 15) & ~(size_t)15;
-    const size_t warp_bytes = lam_bytes + (((size_t)P.max_mask_words * kW * 4 + 15) & ~(size_t)15);
-    uint32_t *lam = reinterpret_cast<uint32_t *>(smem_raw + warp * warp_bytes);
-    uint32_t *mask = reinterpret_cast<uint32_t *>(smem_raw + warp * warp_bytes + lam_bytes);
+    const size_t warp_bytes = ((size_t)P.pat_bytes + 15) & ~(size_t)15;
+    uint8_t *pat = smem_raw + warp * warp_bytes;   // [n_vars][kTileCases] evidence pattern bytes of this warp's tile
     const int64_t slot = (int64_t)blockIdx.x * kWpc + warp;  // this warp's resident tile
     double *S = scratch + slot * P.tile_rows * kRowDoubles + lane * kW;  // lane-private columns of this warp's tile
 
     for (int64_t tile = slot; tile < n_tiles; tile += (int64_t)gridDim.x * kWpc) {
         __syncwarp();
-        for (int i = lane; i < P.lam_words; i += 32) lam[i] = i < P.sum_dims * kW ? 0xffffffffu : 0u;
+        for (int i = lane; i < P.pat_bytes / 4; i += 32) reinterpret_cast<uint32_t *>(pat)[i] = 0u;
         __syncwarp();
-        load_evidence(P, lam, tile, n_cases, ev_off, ev_base, ev_vars, ev_vals, lane, 0, 1);
+        load_patterns(P, pat, tile, n_cases, ev_off, ev_base, ev_vars, ev_vals, lane);
         __syncwarp();
+        write_lambda_rows(P, S, pat, lane, 0, 1);
 
         for (int ph = 0; ph < P.n_phases; ++ph) {
             const Phase p = P.phases[ph];
-            // evidence mask tables of the ops of this phase: kW words per view row / target, lanes build different entries
-            for (int oi = p.op_begin; oi < p.op_end; ++oi) {
-                const SumOp *__restrict__ op = P.ops + P.oplist[oi];
-                const int nrest = op->nrest, ncolv = op->ncolv, rows = op->rows, cols = op->cols;
-                const uint16_t *__restrict__ rl16 = P.lam16 + op->rowlam_off;
-                for (int r = lane; r < rows; r += 32) {
-                    uint32_t m[kW];
-#pragma unroll
-                    for (int i = 0; i < kW; ++i) m[i] = 0xffffffffu;
-                    for (int k = 0; k < nrest; ++k) {
-                        const uint32_t *lw = lam + (int)__ldg(rl16 + (int64_t)r * nrest + k) * kW;
-#pragma unroll
-                        for (int i = 0; i < kW; ++i) m[i] &= lw[i];
-                    }
-#pragma unroll
-                    for (int i = 0; i < kW; ++i) mask[(op->rowmask_off + r) * kW + i] = m[i];
-                }
-                const uint16_t *__restrict__ cl16 = P.lam16 + op->collam_off;
-                for (int j = lane; j < cols; j += 32) {
-                    uint32_t m[kW];
-#pragma unroll
-                    for (int i = 0; i < kW; ++i) m[i] = 0xffffffffu;
-                    for (int k = 0; k < ncolv; ++k) {
-                        const uint32_t *lw = lam + (int)__ldg(cl16 + (int64_t)j * ncolv + k) * kW;
-#pragma unroll
-                        for (int i = 0; i < kW; ++i) m[i] &= lw[i];
-                    }
-#pragma unroll
-                    for (int i = 0; i < kW; ++i) mask[(op->colmask_off + j) * kW + i] = m[i];
-                }
-            }
-            __syncwarp();
             for (int oi = p.op_begin; oi < p.op_end; ++oi) {
                 const SumOp &op = P.ops[P.oplist[oi]];
                 switch (op.ng) {
-                    case 0: flat_sum<0>(P, op, S, mask, lane); break;
-                    case 1: flat_sum<1>(P, op, S, mask, lane); break;
-                    case 2: flat_sum<2>(P, op, S, mask, lane); break;
-                    case 3: flat_sum<3>(P, op, S, mask, lane); break;
-                    case 4: flat_sum<4>(P, op, S, mask, lane); break;
-                    case 5: flat_sum<5>(P, op, S, mask, lane); break;
-                    default: flat_sum<6>(P, op, S, mask, lane); break;
+                    case 0: flat_sum<0>(P, op, S, pat, lane); break;
+                    case 1: flat_sum<1>(P, op, S, pat, lane); break;
+                    case 2: flat_sum<2>(P, op, S, pat, lane); break;
+                    case 3: flat_sum<3>(P, op, S, pat, lane); break;
+                    case 4: flat_sum<4>(P, op, S, pat, lane); break;
+                    default: flat_sum_generic(P, op, S, pat, lane); break;
                 }
             }
-            __syncwarp();  // the next phase overwrites the mask tables
         }
 
-        for (int v = 0; v < P.n_vars; ++v) output_var(P, S, lam, v, tile, n_cases, lane, labels, post);
+        for (int v = 0; v < P.n_vars; ++v) output_var(P, S, pat, v, tile, n_cases, lane, labels, post);
     }
 }
 
 // ---- launch helpers (called from capi.cu) ------------------------------------------------------------------------
-size_t flat_smem_bytes(const DevPlan &P) {
-    size_t o = ((size_t)P.lam_words * 4 + 15) & ~(size_t)15;
-    return o + (((size_t)P.max_mask_words * kW * 4 + 15) & ~(size_t)15);
-}
+size_t flat_smem_bytes(const DevPlan &P) { return ((size_t)P.pat_bytes + 15) & ~(size_t)15; }
 
 // *tiles_per_sm = resident warps (tiles) per SM.
 // The attribute is per function and per context, not per plan: it is raised to the device's opt-in maximum so that plans

@@ -1,9 +1,9 @@
 // sm_100a kernels of the junction-tree hot path. One persistent kernel runs whole test cases:
 //   evidence -> Collect (deepest level first) -> Distribute -> per-variable marginals -> normalise + argmax.
 // Thread mapping: a lane holds kW test cases of a 32*kW-case tile, a warp = one block of targets of one SumOp (plan.h). All
-// table indices, evidence masks (32-bit lambda words, one bit per case) and loop bounds are warp-uniform; all scratch
-// accesses are coalesced rows of 32 x (8*kW)-byte vectors and lane-private, so no shuffles or atomics are needed on the
-// data path. Clique tables are never written: every op recomputes the entries it sums (ops.cuh).
+// table indices and loop bounds are warp-uniform; all scratch accesses are coalesced rows of 32 x (8*kW)-byte vectors and
+// lane-private, so no shuffles or atomics are needed on the data path. Clique tables are never written: every op recomputes
+// the entries it sums, and evidence costs no per-entry test (pattern-folded potentials, ops.cuh).
 #include <cstdint>
 #include <cuda_runtime.h>
 
@@ -14,35 +14,19 @@ namespace fbn {
 
 // One SumOp: all units (target block x row chunk) of the op that this warp owns.
 template <int TEAM, int CB>
-__device__ __forceinline__ void sum_op(const DevPlan &P, const SumOp &__restrict__ op, double *S, const uint32_t *lam, const uint32_t *mask,
-                                       int lane, int warp) {
+__device__ __forceinline__ void sum_op(const DevPlan &P, const SumOp &__restrict__ op, double *S, const uint8_t *pat, int lane, int warp) {
     const V scale = op_scale(P, op, S);
+    const Fx fx = op_fx(P, op, pat, lane);
     const int units = (op.cols + CB - 1) / CB * op.chunks;
-    const bool tables = op.rowmask_off >= 0;
     V nacc = vset(0.0);
     for (int u = (warp - op.rot) & (TEAM - 1); u < units; u += TEAM) {
         int j0, nc, ck, r0, r1;
         sum_unit<CB>(P, op, u, j0, nc, ck, r0, r1);
-        M cm[CB];
         V acc[CB];
 #pragma unroll
         for (int c = 0; c < CB; ++c) acc[c] = vset(0.0);
-        if (tables) {
-#pragma unroll
-            for (int c = 0; c < CB; ++c) {
-                const uint32_t *mw = mask + (op.colmask_off + min(j0 + c, op.cols - 1)) * kW;
-#pragma unroll
-                for (int i = 0; i < kW; ++i) cm[c].w[i] = mw[i];
-            }
-            RowMaskTable rm{mask + op.rowmask_off * kW};
-            sum_block_any<CB>(P, op, rm, cm, S, lane, j0, r0, r1, scale, acc);
-        } else {
-#pragma unroll
-            for (int c = 0; c < CB; ++c) cm[c] = col_mask_from_lam(P, op, lam, min(j0 + c, op.cols - 1));
-            RowMaskLam rm{lam, P.lam16 + op.rowlam_off, op.nrest, M()};
-            sum_block_any<CB>(P, op, rm, cm, S, lane, j0, r0, r1, scale, acc);
-        }
-        vadd(nacc, store_unit<CB>(P, op, S, j0, nc, ck, acc));
+        sum_block_any<CB>(P, op, fx, S, lane, j0, r0, r1, acc);
+        vadd(nacc, store_unit<CB>(P, op, S, pat, lane, j0, nc, ck, scale, acc));
     }
     // this warp's share of sum(clique): one row per (collect op of the phase, warp), summed by the phase's FIN_NORM item
     if (op.kind == SUM_COLLECT) stv(row_ptr(S, P.normpart_row0 + op.normslot * P.nb_max + warp), nacc);
@@ -55,64 +39,32 @@ __global__ void __launch_bounds__(TEAM * 32, (FBN_OCC / TEAM) > 0 ? (FBN_OCC / T
                                                             const int32_t *__restrict__ ev_vals, int32_t *__restrict__ labels,
                                                             double *__restrict__ post, int64_t n_tiles) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    uint32_t *lam = reinterpret_cast<uint32_t *>(smem_raw);  // [lam_words]: allowed-state words, then observed words
-    uint32_t *mask = reinterpret_cast<uint32_t *>(smem_raw + (((size_t)P.lam_words * 4 + 15) & ~(size_t)15));  // per-phase mask tables
+    uint8_t *pat = smem_raw;  // [n_vars][kTileCases] evidence pattern bytes of the tile
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     double *S = scratch + (int64_t)blockIdx.x * P.tile_rows * kRowDoubles + lane * kW;  // lane-private columns of this CTA's tile
     auto sync = [] { if (TEAM > 1) __syncthreads(); else __syncwarp(); };
 
     for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        sync();  // previous tile's readers of lam are done (lanes may diverge)
-        for (int i = threadIdx.x; i < P.lam_words; i += TEAM * 32) lam[i] = i < P.sum_dims * kW ? 0xffffffffu : 0u;
+        sync();  // previous tile's readers of the patterns are done (lanes may diverge)
+        for (int i = threadIdx.x; i < P.pat_bytes / 4; i += TEAM * 32) reinterpret_cast<uint32_t *>(pat)[i] = 0u;
         sync();
-        load_evidence(P, lam, tile, n_cases, ev_off, ev_base, ev_vars, ev_vals, lane, warp, TEAM);
+        if (warp == 0) load_patterns(P, pat, tile, n_cases, ev_off, ev_base, ev_vars, ev_vals, lane);
+        sync();
+        write_lambda_rows(P, S, pat, lane, warp, TEAM);
         sync();
 
         for (int ph = 0; ph < P.n_phases; ++ph) {
             const Phase p = P.phases[ph];
-            // evidence mask tables of every op of this phase: threads work on different rows (warp-uniform data)
-            for (int oi = p.op_begin; oi < p.op_end; ++oi) {
-                const SumOp *__restrict__ op = P.ops + P.oplist[oi];
-                if (op->rowmask_off < 0) continue;
-                const int nrest = op->nrest, ncolv = op->ncolv, rows = op->rows, cols = op->cols;
-                const uint16_t *__restrict__ rl16 = P.lam16 + op->rowlam_off;
-                for (int r = threadIdx.x; r < rows; r += TEAM * 32) {
-                    uint32_t m[kW];
-#pragma unroll
-                    for (int i = 0; i < kW; ++i) m[i] = 0xffffffffu;
-                    for (int k = 0; k < nrest; ++k) {
-                        const uint32_t *lw = lam + (int)__ldg(rl16 + (int64_t)r * nrest + k) * kW;
-#pragma unroll
-                        for (int i = 0; i < kW; ++i) m[i] &= lw[i];
-                    }
-#pragma unroll
-                    for (int i = 0; i < kW; ++i) mask[(op->rowmask_off + r) * kW + i] = m[i];
-                }
-                const uint16_t *__restrict__ cl16 = P.lam16 + op->collam_off;
-                for (int j = threadIdx.x; j < cols; j += TEAM * 32) {
-                    uint32_t m[kW];
-#pragma unroll
-                    for (int i = 0; i < kW; ++i) m[i] = 0xffffffffu;
-                    for (int k = 0; k < ncolv; ++k) {
-                        const uint32_t *lw = lam + (int)__ldg(cl16 + (int64_t)j * ncolv + k) * kW;
-#pragma unroll
-                        for (int i = 0; i < kW; ++i) m[i] &= lw[i];
-                    }
-#pragma unroll
-                    for (int i = 0; i < kW; ++i) mask[(op->colmask_off + j) * kW + i] = m[i];
-                }
-            }
-            sync();
-            for (int oi = p.op_begin; oi < p.op_end; ++oi) sum_op<TEAM, CB>(P, P.ops[P.oplist[oi]], S, lam, mask, lane, warp);
+            for (int oi = p.op_begin; oi < p.op_end; ++oi) sum_op<TEAM, CB>(P, P.ops[P.oplist[oi]], S, pat, lane, warp);
             if (p.fin_end > p.fin_begin) {
                 sync();
                 for (int f = p.fin_begin + warp; f < p.fin_end; f += TEAM) fin_item(P, P.fins[f], S, TEAM);
             }
-            sync();  // the next phase overwrites the mask tables / partial slots and reads this phase's rows
+            sync();  // the next phase overwrites the partial slots and reads this phase's rows
         }
 
-        for (int v = warp; v < P.n_vars; v += TEAM) output_var(P, S, lam, v, tile, n_cases, lane, labels, post);
+        for (int v = warp; v < P.n_vars; v += TEAM) output_var(P, S, pat, v, tile, n_cases, lane, labels, post);
     }
 }
 
@@ -181,16 +133,11 @@ __global__ void score_reduce_kernel(int64_t n_cases, const double *__restrict__ 
 }
 
 // ---- launch helpers (called from capi.cu) ------------------------------------------------------------------------
-size_t fused_smem_bytes(const DevPlan &P) {
-    size_t o = ((size_t)P.lam_words * 4 + 15) & ~(size_t)15;
-    return o + (((size_t)P.max_mask_words * kW * 4 + 15) & ~(size_t)15);
-}
+size_t fused_smem_bytes(const DevPlan &P) { return ((size_t)P.pat_bytes + 15) & ~(size_t)15; }
 
-template <int TEAM>
+template <int TEAM, int CB>
 static cudaError_t prep(const DevPlan &P, int smem_optin, int *blocks_per_sm) {
     size_t smem = fused_smem_bytes(P);
-    constexpr int CB = TEAM == 1 ? 1 : 2;
-    if (P.cb != CB) return cudaErrorInvalidValue;
     // per function and per context, not per plan: raised to the device's opt-in maximum so that two live plans of the same
     // instantiation never lower it for each other (a launch still asks only for what its plan needs)
     cudaError_t e = cudaFuncSetAttribute(jt_fused_kernel<TEAM, CB>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin);
@@ -198,15 +145,27 @@ static cudaError_t prep(const DevPlan &P, int smem_optin, int *blocks_per_sm) {
     return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, jt_fused_kernel<TEAM, CB>, TEAM * 32, smem);
 }
 
-cudaError_t fused_prepare(const DevPlan &P, int smem_optin, int *blocks_per_sm) {
-    switch (P.team) {
-        case 1: return prep<1>(P, smem_optin, blocks_per_sm);
-        case 2: return prep<2>(P, smem_optin, blocks_per_sm);
-        case 4: return prep<4>(P, smem_optin, blocks_per_sm);
-        case 8: return prep<8>(P, smem_optin, blocks_per_sm);
-        case 16: return prep<16>(P, smem_optin, blocks_per_sm);
-        case 32: return prep<32>(P, smem_optin, blocks_per_sm);
+// dispatch on (team, targets per unit): team 1 runs cb 1, larger teams cb 2 or 4
+#define FBN_FUSED_DISPATCH(F)                                   \
+    switch (P.team * 8 + P.cb) {                                \
+        case 1 * 8 + 1: F(1, 1); break;                         \
+        case 2 * 8 + 2: F(2, 2); break;                         \
+        case 2 * 8 + 4: F(2, 4); break;                         \
+        case 4 * 8 + 2: F(4, 2); break;                         \
+        case 4 * 8 + 4: F(4, 4); break;                         \
+        case 8 * 8 + 2: F(8, 2); break;                         \
+        case 8 * 8 + 4: F(8, 4); break;                         \
+        case 16 * 8 + 2: F(16, 2); break;                       \
+        case 16 * 8 + 4: F(16, 4); break;                       \
+        case 32 * 8 + 2: F(32, 2); break;                       \
+        case 32 * 8 + 4: F(32, 4); break;                       \
+        default: return cudaErrorInvalidValue;                  \
     }
+
+cudaError_t fused_prepare(const DevPlan &P, int smem_optin, int *blocks_per_sm) {
+#define FBN_PREP(T, C) return prep<T, C>(P, smem_optin, blocks_per_sm)
+    FBN_FUSED_DISPATCH(FBN_PREP)
+#undef FBN_PREP
     return cudaErrorInvalidValue;
 }
 
@@ -216,16 +175,8 @@ cudaError_t fused_launch(const DevPlan &P, int grid, double *scratch, int64_t n_
     if (n_tiles == 0) return cudaSuccess;
     if (grid > n_tiles) grid = (int)n_tiles;
     size_t smem = fused_smem_bytes(P);
-#define FBN_LAUNCH(T) jt_fused_kernel<T, (T == 1 ? 1 : 2)><<<grid, T * 32, smem, st>>>(P, scratch, n_cases, ev_off, ev_base, ev_vars, ev_vals, labels, post, n_tiles)
-    switch (P.team) {
-        case 1: FBN_LAUNCH(1); break;
-        case 2: FBN_LAUNCH(2); break;
-        case 4: FBN_LAUNCH(4); break;
-        case 8: FBN_LAUNCH(8); break;
-        case 16: FBN_LAUNCH(16); break;
-        case 32: FBN_LAUNCH(32); break;
-        default: return cudaErrorInvalidValue;
-    }
+#define FBN_LAUNCH(T, C) jt_fused_kernel<T, C><<<grid, T * 32, smem, st>>>(P, scratch, n_cases, ev_off, ev_base, ev_vars, ev_vals, labels, post, n_tiles)
+    FBN_FUSED_DISPATCH(FBN_LAUNCH)
 #undef FBN_LAUNCH
     return cudaGetLastError();
 }

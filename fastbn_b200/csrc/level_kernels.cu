@@ -24,30 +24,34 @@ namespace fbn {
 
 namespace {
 
-// evidence -> per-tile lambda words in global memory. One CTA per tile.
-__global__ void __launch_bounds__(128) lvl_evidence_kernel(const DevPlan P, uint32_t *__restrict__ lamG, int64_t tile0,
+// evidence -> per-tile pattern bytes in global memory (+ lambda rows of the variables some op gathers). One CTA per tile.
+__global__ void __launch_bounds__(128) lvl_evidence_kernel(const DevPlan P, double *__restrict__ scratch, uint8_t *__restrict__ patG, int64_t tile0,
                                                            int64_t n_cases, const int64_t *__restrict__ ev_off, int64_t ev_base,
                                                            const int32_t *__restrict__ ev_vars, const int32_t *__restrict__ ev_vals) {
-    uint32_t *lam = lamG + (int64_t)blockIdx.x * P.lam_words;
-    for (int i = threadIdx.x; i < P.lam_words; i += blockDim.x) lam[i] = i < P.sum_dims * kW ? 0xffffffffu : 0u;
+    uint8_t *pat = patG + (int64_t)blockIdx.x * P.pat_bytes;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < P.pat_bytes / 4; i += blockDim.x) reinterpret_cast<uint32_t *>(pat)[i] = 0u;
     __syncthreads();
-    load_evidence(P, lam, tile0 + blockIdx.x, n_cases, ev_off, ev_base, ev_vars, ev_vals, threadIdx.x & 31, threadIdx.x >> 5, blockDim.x >> 5);
+    if (warp == 0) load_patterns(P, pat, tile0 + blockIdx.x, n_cases, ev_off, ev_base, ev_vars, ev_vals, lane);
+    __syncthreads();
+    double *S = scratch + (int64_t)blockIdx.x * P.tile_rows * kRowDoubles + lane * kW;
+    write_lambda_rows(P, S, pat, lane, warp, blockDim.x >> 5);
 }
 
-// One phase (tree level) of SumOps: grid (CTAs per tile, tiles). Row masks are evaluated lane-parallel from the tile's
-// lambda words (RowMaskLam, ops.cuh).
+// One phase (tree level) of SumOps: grid (CTAs per tile, tiles).
 template <int CB>
 __global__ void __launch_bounds__(kLevelWarps * 32, FBN_LVL_OCC) lvl_sum_kernel(const DevPlan P, double *__restrict__ scratch,
-                                                                                const uint32_t *__restrict__ lamG, int phase_idx) {
+                                                                                const uint8_t *__restrict__ patG, int phase_idx) {
     __shared__ double red[kLevelWarps][kRowDoubles];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int gw = blockIdx.x * kLevelWarps + warp, GW = gridDim.x * kLevelWarps;
     double *S = scratch + (int64_t)blockIdx.y * P.tile_rows * kRowDoubles + lane * kW;
-    const uint32_t *lam = lamG + (int64_t)blockIdx.y * P.lam_words;
+    const uint8_t *pat = patG + (int64_t)blockIdx.y * P.pat_bytes;
     const Phase ph = P.phases[phase_idx];
     for (int oi = ph.op_begin; oi < ph.op_end; ++oi) {
         const SumOp &__restrict__ op = P.ops[P.oplist[oi]];
         const V scale = op_scale(P, op, S);
+        const Fx fx = op_fx(P, op, pat, lane);
         const int units = (op.cols + CB - 1) / CB * op.chunks;
         int start = (gw - op.rot % GW) % GW;
         if (start < 0) start += GW;
@@ -55,16 +59,11 @@ __global__ void __launch_bounds__(kLevelWarps * 32, FBN_LVL_OCC) lvl_sum_kernel(
         for (int u = start; u < units; u += GW) {
             int j0, nc, ck, r0, r1;
             sum_unit<CB>(P, op, u, j0, nc, ck, r0, r1);
-            M cm[CB];
             V acc[CB];
 #pragma unroll
-            for (int c = 0; c < CB; ++c) {
-                acc[c] = vset(0.0);
-                cm[c] = col_mask_from_lam(P, op, lam, min(j0 + c, op.cols - 1));
-            }
-            RowMaskLam rm{lam, P.lam16 + op.rowlam_off, op.nrest, M()};
-            sum_block_any<CB>(P, op, rm, cm, S, lane, j0, r0, r1, scale, acc);
-            vadd(nacc, store_unit<CB>(P, op, S, j0, nc, ck, acc));
+            for (int c = 0; c < CB; ++c) acc[c] = vset(0.0);
+            sum_block_any<CB>(P, op, fx, S, lane, j0, r0, r1, acc);
+            vadd(nacc, store_unit<CB>(P, op, S, pat, lane, j0, nc, ck, scale, acc));
         }
         if (op.kind == SUM_COLLECT) {  // this CTA's share of sum(clique): one share row per (collect op, CTA)
 #pragma unroll
@@ -95,19 +94,19 @@ __global__ void __launch_bounds__(kLevelWarps * 32) lvl_fin_kernel(const DevPlan
 
 // posteriors + label
 __global__ void __launch_bounds__(kLevelWarps * 32) lvl_output_kernel(const DevPlan P, double *__restrict__ scratch,
-                                                                      const uint32_t *__restrict__ lamG, int64_t tile0, int64_t n_cases,
+                                                                      const uint8_t *__restrict__ patG, int64_t tile0, int64_t n_cases,
                                                                       int32_t *__restrict__ labels, double *__restrict__ post) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int v = blockIdx.x * kLevelWarps + warp;
     if (v >= P.n_vars) return;
     const double *S = scratch + (int64_t)blockIdx.y * P.tile_rows * kRowDoubles + lane * kW;
-    output_var(P, S, lamG + (int64_t)blockIdx.y * P.lam_words, v, tile0 + blockIdx.y, n_cases, lane, labels, post);
+    output_var(P, S, patG + (int64_t)blockIdx.y * P.pat_bytes, v, tile0 + blockIdx.y, n_cases, lane, labels, post);
 }
 
 }  // namespace
 
 // Enqueues all launches for n_cases cases (several waves of `resident` tiles). Returns the number of launches via *n_launch.
-cudaError_t level_launch(const DevPlan &P, const std::vector<Phase> &phases, int resident, double *scratch, uint32_t *lamG,
+cudaError_t level_launch(const DevPlan &P, const std::vector<Phase> &phases, int resident, double *scratch, uint8_t *patG,
                          int64_t n_cases, const int64_t *ev_off, int64_t ev_base, const int32_t *ev_vars, const int32_t *ev_vals,
                          int32_t *labels, double *post, cudaStream_t st, int64_t *n_launch) {
     if (P.cb != 4 && P.cb != 8) return cudaErrorInvalidValue;
@@ -115,7 +114,7 @@ cudaError_t level_launch(const DevPlan &P, const std::vector<Phase> &phases, int
     int64_t launches = 0;
     for (int64_t tile0 = 0; tile0 < n_tiles; tile0 += resident) {
         const unsigned wt = (unsigned)std::min<int64_t>(resident, n_tiles - tile0);
-        lvl_evidence_kernel<<<wt, 128, 0, st>>>(P, lamG, tile0, n_cases, ev_off, ev_base, ev_vars, ev_vals);
+        lvl_evidence_kernel<<<wt, 128, 0, st>>>(P, scratch, patG, tile0, n_cases, ev_off, ev_base, ev_vars, ev_vals);
         ++launches;
         for (size_t pi = 0; pi < phases.size(); ++pi) {
             const Phase &ph = phases[pi];
@@ -123,8 +122,8 @@ cudaError_t level_launch(const DevPlan &P, const std::vector<Phase> &phases, int
             int nb = (ph.n_units + 2 * kLevelWarps - 1) / (2 * kLevelWarps);
             nb = std::max(1, std::min(nb, P.nb_max));
             dim3 grid((unsigned)nb, wt);
-            if (P.cb == 8) lvl_sum_kernel<8><<<grid, kLevelWarps * 32, 0, st>>>(P, scratch, lamG, (int)pi);
-            else lvl_sum_kernel<4><<<grid, kLevelWarps * 32, 0, st>>>(P, scratch, lamG, (int)pi);
+            if (P.cb == 8) lvl_sum_kernel<8><<<grid, kLevelWarps * 32, 0, st>>>(P, scratch, patG, (int)pi);
+            else lvl_sum_kernel<4><<<grid, kLevelWarps * 32, 0, st>>>(P, scratch, patG, (int)pi);
             ++launches;
             const int nfin = ph.fin_end - ph.fin_begin;
             if (nfin > 0) {
@@ -134,7 +133,7 @@ cudaError_t level_launch(const DevPlan &P, const std::vector<Phase> &phases, int
             }
         }
         dim3 og((unsigned)((P.n_vars + kLevelWarps - 1) / kLevelWarps), wt);
-        lvl_output_kernel<<<og, kLevelWarps * 32, 0, st>>>(P, scratch, lamG, tile0, n_cases, labels, post);
+        lvl_output_kernel<<<og, kLevelWarps * 32, 0, st>>>(P, scratch, patG, tile0, n_cases, labels, post);
         ++launches;
         cudaError_t e = cudaGetLastError();
         if (e != cudaSuccess) return e;

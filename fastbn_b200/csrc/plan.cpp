@@ -115,10 +115,10 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
     if (level && (team < 1 || team > 65536)) return "level mode: gang warps must be in [1,65536]";
     P = HostPlan();
     P.level = level;
-    P.cb = level ? 4 : (team == 1 ? 1 : 2);
+    P.cb = level ? 4 : (team == 1 ? 1 : 4);  // measured on B200 (fused, HEPAR2- / PIGS-shape): 4 targets per unit +31 % / +26 % over 2
     if (const char *e = getenv("FBN_CB")) {
         int v = atoi(e);
-        if (level ? (v == 4 || v == 8) : (v == 1 || v == 2)) P.cb = v;
+        if (level ? (v == 4 || v == 8) : (team == 1 ? v == 1 : (v == 2 || v == 4))) P.cb = v;
     }
     const int64_t kColBlock = P.cb;
     P.n_vars = nv; P.n_cliques = nc; P.n_seps = ns; P.query_var = t.query_var; P.team = team;
@@ -190,68 +190,146 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
     std::vector<int64_t> sep_off(ns + 1, 0);
     for (int s = 0; s < ns; ++s) sep_off[s + 1] = sep_off[s] + sep[s].size;
     P.sep_entries = sep_off[ns];
-    int64_t rows_total = 2 * (P.sep_entries + 1) + nc + sd;
+    int64_t rows_total = 2 * (P.sep_entries + 1) + nc + 2 * sd;
     if (rows_total > ((int64_t)1 << 30)) return "tree too large: more than 2^30 scratch rows per tile";
     P.mup_row0 = 0;
     P.dn_row0 = P.mup_row0 + (int32_t)P.sep_entries + 1;
     P.inv_row0 = P.dn_row0 + (int32_t)P.sep_entries + 1;
     P.mg_row0 = P.inv_row0 + nc;
+    P.lam_row0 = P.mg_row0 + (int32_t)sd;
     P.tile_rows = (int32_t)rows_total;
     auto up_row = [&](int s) { return P.mup_row0 + (int32_t)sep_off[s]; };
     auto dn_row = [&](int s) { return P.dn_row0 + (int32_t)sep_off[s]; };
     const int32_t dummy_row = P.mup_row0 + (int32_t)P.sep_entries;  // the root's "up message" (one entry, never read)
 
     P.pot.assign(t.clique_potentials, t.clique_potentials + pot_off[nc]);
-    std::vector<double> ref_marg_entries_v(1, 0.0);
+    const int64_t one_idx = (int64_t)P.pot.size();  // a 1.0 for the views without potentials (flat records point at it)
+    P.pot.push_back(1.0);
+    // unary "tables" of the evidence indicators (lambda rows), gathered like messages by views whose pattern table would get too big
+    std::vector<Table> lamtab(nv);
+    for (int v = 0; v < nv; ++v) {
+        lamtab[v].vars = {v};
+        if (!finish_table(lamtab[v], t.var_dims, nv, err)) return err;
+    }
+    std::vector<char> lam_needed(nv, 0);
+    static const int64_t kMaxFx = getenv("FBN_MAX_FX") ? std::max(1, atoi(getenv("FBN_MAX_FX"))) : 64;
 
     // ---- views -------------------------------------------------------------------------------------------------------
     // A view of table X (clique c >= 0, or a separator: c < 0) with the variables at positions `tpos` as targets.
     // `native` = the targets are X's trailing variables in storage order: the original potentials serve as they are.
-    struct ViewTables { std::vector<const Table *> gtab; };  // for the visiting-order heuristic
-    std::vector<ViewTables> view_tabs;
-    auto make_view = [&](const Table &X, int c, const std::vector<int> &tpos, const std::vector<GatherSrc> &gs,
-                         const std::vector<int32_t> &invrows) {
+    auto make_view = [&](const Table &X, int c, const std::vector<int> &tpos, std::vector<GatherSrc> gs,
+                         const std::vector<int32_t> &invrows, int kind) {
         SumOp op = SumOp();
-        std::vector<int> rpos;
-        for (int i = 0; i < (int)X.vars.size(); ++i)
-            if (std::find(tpos.begin(), tpos.end(), i) == tpos.end()) rpos.push_back(i);
+        op.kind = kind;
+        auto is_target = [&](int i) { return std::find(tpos.begin(), tpos.end(), i) != tpos.end(); };
+        // uncovered variables: in none of the gathered tables. Target variables of distribute / marginal views need nothing
+        // (0 guard on the child's up message; an observed variable is reported as zeros).
+        std::vector<int> fold_pos, cmask_pos;
+        int64_t nfx = 1;
+        if (c >= 0) {
+            std::vector<int> unc;
+            for (int i = 0; i < (int)X.vars.size(); ++i) {
+                bool covered = false;
+                for (const GatherSrc &g : gs) covered = covered || g.tab->find(X.vars[i]) >= 0;
+                if (covered) continue;
+                if (!is_target(i)) unc.push_back(i);
+                else if (kind == SUM_COLLECT) cmask_pos.push_back(i);  // checked once per finished sum, not per entry
+            }
+            std::stable_sort(unc.begin(), unc.end(), [&](int a, int b) { return X.dims[a] < X.dims[b]; });
+            for (int i : unc) {
+                if (nfx * (X.dims[i] + 2) <= kMaxFx) {
+                    fold_pos.push_back(i);
+                    nfx *= X.dims[i] + 2;
+                    ++P.folded_vars;
+                } else {
+                    gs.push_back({&lamtab[X.vars[i]], P.lam_row0 + P.vars[X.vars[i]].off});
+                    lam_needed[X.vars[i]] = 1;
+                    ++P.lambda_gathers;
+                }
+            }
+        }
+        std::vector<int> rpos, frpos;  // row variables of the view; folded row variables (summed out)
+        for (int i = 0; i < (int)X.vars.size(); ++i) {
+            if (is_target(i)) continue;
+            if (std::find(fold_pos.begin(), fold_pos.end(), i) != fold_pos.end()) frpos.push_back(i);
+            else rpos.push_back(i);
+        }
         const std::vector<int32_t> roff = enumerate_offsets(X, rpos), coff = enumerate_offsets(X, tpos);
         op.rows = (int32_t)roff.size();
         op.cols = (int32_t)coff.size();
-        op.nrest = (int32_t)rpos.size();
-        op.ncolv = (int32_t)tpos.size();
-        bool native = true;
+        op.nfold = (int32_t)fold_pos.size();
+        op.nfx = (int32_t)nfx;
+        op.fold_off = (int64_t)P.idx32.size();
+        {
+            int64_t st = 1;
+            for (int i : fold_pos) { P.idx32.push_back(X.vars[i]); P.idx32.push_back((int32_t)st); st *= X.dims[i] + 2; }
+        }
+        op.cmask_off = (int64_t)P.idx32.size();
+        op.ncmask = (int32_t)cmask_pos.size();
+        for (int i : cmask_pos) {
+            int64_t cst = 1;  // stride of the variable's digit in the target index (targets are enumerated row-major over tpos)
+            for (size_t k = tpos.size(); k-- > 0 && tpos[k] != i;) cst *= X.dims[tpos[k]];
+            P.idx32.push_back(X.vars[i]); P.idx32.push_back((int32_t)cst); P.idx32.push_back(X.dims[i]);
+        }
+        bool native = fold_pos.empty();
         for (size_t i = 0; i < tpos.size(); ++i) native = native && tpos[i] == (int)(X.vars.size() - tpos.size() + i);
         if (c < 0) {
             op.pot_off = -1;  // separators carry no potentials (all ones in the reference)
         } else if (native) {
             op.pot_off = pot_off[c];
         } else {
+            // potX[(r*cols + j)*nfx + fx]: the folded row variables summed out under evidence pattern fx; a folded target
+            // variable zeroes the targets its pattern rules out
             op.pot_off = (int64_t)P.pot.size();
-            P.pot.resize(P.pot.size() + (size_t)X.size);
+            P.pot.resize(P.pot.size() + (size_t)op.rows * op.cols * nfx);
             double *dst = P.pot.data() + op.pot_off;
             const double *src = t.clique_potentials + pot_off[c];
-            for (int64_t r = 0; r < op.rows; ++r)
-                for (int64_t j = 0; j < op.cols; ++j) dst[r * op.cols + j] = src[roff[(size_t)r] + coff[(size_t)j]];
-        }
-        // lambda-bit indices (evidence mask): var offset + digit
-        op.rowlam_off = (int64_t)P.lam16.size();
-        if (c >= 0) {
-            std::vector<int> dg = enumerate_digits(X, rpos);
-            for (int64_t r = 0; r < op.rows; ++r)
-                for (int i = 0; i < op.nrest; ++i)
-                    P.lam16.push_back((uint16_t)(P.vars[X.vars[rpos[i]]].off + dg[(size_t)r * op.nrest + i]));
-        } else {
-            op.nrest = 0;  // separator views: the messages are masked already
-        }
-        op.collam_off = (int64_t)P.lam16.size();
-        if (c >= 0) {
-            std::vector<int> dg = enumerate_digits(X, tpos);
-            for (int64_t j = 0; j < op.cols; ++j)
-                for (int i = 0; i < op.ncolv; ++i)
-                    P.lam16.push_back((uint16_t)(P.vars[X.vars[tpos[i]]].off + dg[(size_t)j * op.ncolv + i]));
-        } else {
-            op.ncolv = 0;
+            const std::vector<int32_t> froff = enumerate_offsets(X, frpos);
+            const std::vector<int> frdig = enumerate_digits(X, frpos), cdig = enumerate_digits(X, tpos);
+            const int nfr = (int)frpos.size(), nfold = (int)fold_pos.size();
+            // fold slot of every folded variable: index k in fold_pos; for row ones also the index among frpos, for target ones among tpos
+            std::vector<int> fr_slot(nfr), fc_slot, fc_tidx;
+            for (int a = 0; a < nfr; ++a) fr_slot[a] = (int)(std::find(fold_pos.begin(), fold_pos.end(), frpos[a]) - fold_pos.begin());
+            for (int k = 0; k < nfold; ++k) {
+                auto it = std::find(tpos.begin(), tpos.end(), fold_pos[k]);
+                if (it != tpos.end()) { fc_slot.push_back(k); fc_tidx.push_back((int)(it - tpos.begin())); }
+            }
+            std::vector<int> pat(nfold);
+            std::vector<char> combo_ok(froff.size());
+            for (int64_t fx = 0; fx < nfx; ++fx) {
+                int64_t x = fx;
+                bool dead = false;  // a variable observed in no valid state: everything is zero
+                for (int k = 0; k < nfold; ++k) {
+                    const int d = X.dims[fold_pos[k]];
+                    pat[k] = (int)(x % (d + 2));
+                    x /= d + 2;
+                    dead = dead || pat[k] == d + 1;
+                }
+                for (size_t q = 0; q < froff.size(); ++q) {
+                    bool ok = !dead;
+                    for (int a = 0; a < nfr && ok; ++a) {
+                        const int pk = pat[fr_slot[a]];
+                        ok = pk == 0 || pk - 1 == frdig[q * nfr + a];
+                    }
+                    combo_ok[q] = ok;
+                }
+                for (int64_t j = 0; j < op.cols; ++j) {
+                    bool colok = !dead;
+                    for (size_t a = 0; a < fc_slot.size() && colok; ++a) {
+                        const int pk = pat[fc_slot[a]];
+                        colok = pk == 0 || pk - 1 == cdig[(size_t)j * tpos.size() + fc_tidx[a]];
+                    }
+                    for (int64_t r = 0; r < op.rows; ++r) {
+                        double sum = 0.0;
+                        if (colok) {
+                            const int64_t e0 = (int64_t)roff[(size_t)r] + coff[(size_t)j];
+                            for (size_t q = 0; q < froff.size(); ++q)
+                                if (combo_ok[q]) sum += src[e0 + froff[q]];
+                        }
+                        dst[(r * op.cols + j) * nfx + fx] = sum;
+                    }
+                }
+            }
         }
         // index maps of the gathered tables, split into row part + column part (TableExtensionMain, PotentialTable.cpp:603-613)
         op.ng = (int32_t)gs.size();
@@ -283,7 +361,7 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
         // CTA then read the same rows -> L1 hits), variables shared by several sources slowest.
         op.perm_off = -1;
         const int64_t nblk = (op.cols + kColBlock - 1) / kColBlock;
-        if (op.ng > 0 && nblk > 1 && X.size >= 32768 && !getenv("FBN_NO_PERM")) {
+        if (op.ng > 0 && nblk > 1 && (int64_t)op.rows * op.cols >= 32768 && !getenv("FBN_NO_PERM")) {
             const int ncv = (int)tpos.size();
             std::vector<int> order(ncv);  // target variables, slowest first
             std::iota(order.begin(), order.end(), 0);
@@ -344,8 +422,7 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
         for (int s : kids[c]) gs.push_back({&sep[s], up_row(s)});
         std::vector<int32_t> inv;
         for (int s : kids[c]) inv.push_back(P.inv_row0 + t.sep_child[s]);
-        SumOp op = make_view(clq[c], c, c == t.root ? std::vector<int>() : trailing(clq[c], sep[up_sep[c]].vars.size()), gs, inv);
-        op.kind = SUM_COLLECT;
+        SumOp op = make_view(clq[c], c, c == t.root ? std::vector<int>() : trailing(clq[c], sep[up_sep[c]].vars.size()), gs, inv, SUM_COLLECT);
         op.dst_row = c == t.root ? dummy_row : up_row(up_sep[c]);
         op.inv_row = P.inv_row0 + c;
         collect_op[c] = (int)P.ops.size();
@@ -362,8 +439,7 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
         for (int s2 : kids[p])
             if (s2 != s) gs.push_back({&sep[s2], up_row(s2)});
         if (p != t.root) gs.push_back({&sep[up_sep[p]], dn_row(up_sep[p])});
-        SumOp op = make_view(clq[p], p, tpos, gs, inv_rows_of(p));
-        op.kind = SUM_DISTRIBUTE;
+        SumOp op = make_view(clq[p], p, tpos, gs, inv_rows_of(p), SUM_DISTRIBUTE);
         op.dst_row = dn_row(s);
         op.aux_row = up_row(s);
         dist_op[c] = (int)P.ops.size();
@@ -394,17 +470,16 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
         SumOp op;
         if (best >= nc) {
             const int s = best - nc;
-            op = make_view(sep[s], -1, {sep[s].find(v)}, {{&sep[s], up_row(s)}, {&sep[s], dn_row(s)}}, {});
+            op = make_view(sep[s], -1, {sep[s].find(v)}, {{&sep[s], up_row(s)}, {&sep[s], dn_row(s)}}, {}, SUM_MARGINAL);
             marg_avail[v] = depth[t.sep_child[s]];
         } else {
             const int c = best;
             std::vector<GatherSrc> gs;
             for (int s : kids[c]) gs.push_back({&sep[s], up_row(s)});
             if (c != t.root) gs.push_back({&sep[up_sep[c]], dn_row(up_sep[c])});
-            op = make_view(clq[c], c, {clq[c].find(v)}, gs, inv_rows_of(c));
+            op = make_view(clq[c], c, {clq[c].find(v)}, gs, inv_rows_of(c), SUM_MARGINAL);
             marg_avail[v] = depth[c];
         }
-        op.kind = SUM_MARGINAL;
         op.dst_row = P.mg_row0 + P.vars[v].off;
         marg_op[v] = (int)P.ops.size();
         P.ops.push_back(op);
@@ -414,10 +489,7 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
     // ---- phases, warp work units, split-column partial slots ----
     // A block of cb adjacent targets is one unit of warp work unless its row range is long and the phase has too few column
     // blocks to keep `team` warps busy; then the rows are cut into chunks whose partial sums meet in scratch rows.
-    // Evidence-mask tables (kW 32-bit words per row and per column of every op of the phase) are built in shared memory at
-    // the start of a phase when they fit (fused mode); otherwise the masks are evaluated on the fly from the lambda words.
     const int64_t kMaxPslots = level ? std::max<int64_t>(192, std::min<int64_t>(1 << 16, P.clique_entries / 8)) : (team == 1 ? 0 : 512);
-    const int kMaxMaskWords = (level || getenv("FBN_NO_TABLES")) ? 0 : 6144;
     auto emit_phase = [&](int kind, const std::vector<int> &ops) {
         Phase ph = Phase();
         ph.kind = kind;
@@ -455,7 +527,7 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
             };
             std::stable_sort(ordered.begin(), ordered.end(), [&](int a, int b) { return unit_cost(a) > unit_cost(b); });
         }
-        int pslots = 0, normslots = 0, mask_words = 0;
+        int pslots = 0, normslots = 0;
         int64_t units = 0;
         for (int o : ordered) {
             SumOp &op = P.ops[o];
@@ -467,12 +539,6 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
             if (chunks > 1) pslots += (int)(chunks * cols);
             op.normslot = op.kind == SUM_COLLECT ? normslots++ : -1;
             op.chunks = (int32_t)chunks; op.rows_per_chunk = (int32_t)per; op.pslot0 = pslot0; op.rot = (int32_t)(level ? units : units % team);
-            if (mask_words + rows + cols <= kMaxMaskWords) {
-                op.rowmask_off = mask_words; op.colmask_off = mask_words + (int32_t)rows;
-                mask_words += (int32_t)(rows + cols);
-            } else {
-                op.rowmask_off = op.colmask_off = -1;
-            }
             units += chunks * ((cols + kColBlock - 1) / kColBlock);
             P.oplist.push_back(o);
             if (chunks > 1)
@@ -498,11 +564,9 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
         ph.op_end = (int32_t)P.oplist.size();
         ph.fin_end = (int32_t)P.fins.size();
         ph.n_normslots = normslots;
-        ph.mask_words = mask_words;
         ph.n_units = (int32_t)std::min<int64_t>(units, INT32_MAX);
         P.max_normslots = std::max(P.max_normslots, normslots);
         P.max_pslots = std::max(P.max_pslots, pslots);
-        P.max_mask_words = std::max(P.max_mask_words, mask_words);
         P.phases.push_back(ph);
     };
     for (int d = maxdepth; d >= 0; --d) {  // Collect: deepest cliques first (src/JunctionTree.cpp:1240-1306)
@@ -534,8 +598,8 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
     // ---- flat records (small trees run by one warp per tile, jt_flat_kernel): one record per view entry with ABSOLUTE
     //      scratch rows, so the kernel's inner loop is a record load, the data loads and the arithmetic
     if (!level && team == 1 && !getenv("FBN_NO_FLAT")) {
-        bool ok = true;
-        for (const auto &op : P.ops) ok = ok && op.ng <= 6 && op.rowmask_off >= 0 && op.chunks == 1;
+        bool ok = P.pot.size() < ((size_t)1 << 31);
+        for (const auto &op : P.ops) ok = ok && op.ng <= 7 && op.chunks == 1;
         if (ok) {
             for (auto &op : P.ops) {
                 while (P.flatc.size() & 3) P.flatc.push_back(0);
@@ -543,19 +607,20 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
                 const int ng = op.ng;
                 for (int64_t j = 0; j < op.cols; ++j)
                     for (int64_t r = 0; r < op.rows; ++r) {
-                        int32_t m[6] = {0, 0, 0, 0, 0, 0};
+                        int32_t m[7] = {0, 0, 0, 0, 0, 0, 0};
                         for (int g = 0; g < ng; ++g)
                             m[g] = P.idx32[(size_t)(op.rowpart_off + r * ng + g)] + P.idx32[(size_t)(op.colpart_off + j * ng + g)];
-                        const double pv = op.pot_off < 0 ? 1.0 : P.pot[(size_t)(op.pot_off + r * op.cols + j)];
-                        int32_t bits[2];
-                        memcpy(bits, &pv, 8);
-                        P.flatc.push_back(bits[0]); P.flatc.push_back(bits[1]); P.flatc.push_back(m[0]); P.flatc.push_back(m[1]);
-                        if (ng > 2) { P.flatc.push_back(m[2]); P.flatc.push_back(m[3]); P.flatc.push_back(m[4]); P.flatc.push_back(m[5]); }
+                        const int64_t pi = op.pot_off < 0 ? one_idx : op.pot_off + (r * op.cols + j) * op.nfx;
+                        P.flatc.push_back((int32_t)pi); P.flatc.push_back(m[0]); P.flatc.push_back(m[1]); P.flatc.push_back(m[2]);
+                        if (ng > 3) { P.flatc.push_back(m[3]); P.flatc.push_back(m[4]); P.flatc.push_back(m[5]); P.flatc.push_back(m[6]); }
                     }
             }
             P.flat = true;
         }
     }
+
+    for (int v = 0; v < nv; ++v)
+        if (lam_needed[v]) P.lamvars.push_back(v);
 
     // ---- byte accounting ----
     // B = 8(Tc+Ts) + sum_edges(24|child| + 24|parent| + 32|sep|) + sum_vars 8|marginal clique| + 8 sum_dims
@@ -565,6 +630,7 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
     // what the kernels must move per case when every scratch row misses the caches once: each message / ratio / norm /
     // marginal row written once and read once + posterior/label output (gathers beyond the first hit L1/L2)
     P.kernel_bytes_per_case = 16.0 * (double)(2 * P.sep_entries + nc + sd) + 8.0 * (double)sd + 4.0;
+    (void)one_idx;
     return "";
 }
 

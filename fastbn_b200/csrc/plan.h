@@ -25,6 +25,7 @@
 //   [dn_row0 ..)   one row per separator entry, down ratio   (reference: Separator::p_table after Distribute / old)
 //   [inv_row0 ..)  one row per clique: 1 / (sum of the clique after Collect)  (reference: Normalize(), PotentialTableBase.cpp:433-445)
 //   [mg_row0 ..)   one row per (variable, state): unnormalised marginal
+//   [lam_row0 ..)  one row per (variable, state): evidence indicator 1.0 / 0.0 (written only for the variables some op gathers)
 //   [part_row0 ..) / [normpart_row0 ..)  partial sums of split ops (several warps per tile)
 #pragma once
 #include <cstdint>
@@ -51,24 +52,35 @@ constexpr int kMaxColBlock = 8;
 enum SumKind : int32_t { SUM_COLLECT = 0, SUM_DISTRIBUTE = 1, SUM_MARGINAL = 2 };
 
 // One sum over a rows x cols view of a table (see the header comment).
+//
+// Evidence never costs a per-entry mask test. A variable of the view that none of the gathered messages contains
+// ("uncovered": the messages of covered variables are already zero where the evidence rules a state out) is either
+//   FOLDED into the potentials: the planner sums the variable out of the view for every EVIDENCE PATTERN (0 = not observed,
+//     1 + d = observed in state d, dim + 1 = observed in no valid state) and stores nfx = prod (dim + 2) values per entry; a
+//     case looks its pattern index fx up once per op (fold list below, per-tile pattern bytes) and reads potX[entry*nfx + fx];
+//   (row variables only; an uncovered TARGET variable of a collect view is checked once per finished sum, cmask list below)
+//   or GATHERED as a unary message: the tile's lambda rows (lam_row0 + var offset + state: 1.0 allowed / 0.0 ruled out) are one
+//     more gather of the entry (used when the pattern table would get too big).
 struct SumOp {
-    int64_t pot_off;      // into pot[]: pristine potentials in VIEW order (rows*cols doubles, row-major), -1 = all ones
-    int64_t rowlam_off;   // into lam16[]: rows*nrest lambda-bit indices of the row (non-target) variables
-    int64_t collam_off;   // into lam16[]: cols*ncolv lambda-bit indices of the target variables
+    int64_t pot_off;      // into pot[]: potX in VIEW order ((r*cols + j)*nfx + fx doubles), -1 = all ones
+    int64_t fold_off;     // into idx32[]: nfold pairs {variable, pattern stride}
+    int64_t cmask_off;    // into idx32[]: ncmask triples {variable, stride of its digit in the target index, dim}: uncovered TARGET
+                          //   variables of a collect view; a finished sum is zeroed when the case observed another state
     int64_t rowpart_off;  // into idx32[]: rows*ng  (absolute scratch row of gather g's source, row part)
     int64_t colpart_off;  // into idx32[]: cols*ng  (column part)
-    int64_t invrow_off;   // into idx32[]: ninv absolute scratch rows whose product scales every entry (1/norm of cliques)
+    int64_t invrow_off;   // into idx32[]: ninv absolute scratch rows whose product scales the sums (1/norm of cliques)
     int64_t flat_off;     // flat plans (small trees, one warp per tile): into flatc[] (int4 records), -1 = none. One record
-                          //   per entry, COLUMN-major (all rows of target 0, then target 1, ...): first int4 = {pristine
-                          //   potential (2 x 32 bit), absolute scratch row of gather 0, of gather 1}; ops with more than two
-                          //   gathers append ceil((ng-2)/4) int4 of further rows
+                          //   per entry, TARGET-major (all rows of target 0, then target 1, ...): first int4 = {index of the
+                          //   entry's first potX value, absolute scratch row of gather 0, of gather 1, of gather 2}; ops with
+                          //   more than three gathers append one int4 of further rows
     int64_t perm_off;     // into idx32[]: visiting order of the column blocks, -1 = storage order
     int32_t kind;         // SumKind
     int32_t dst_row;      // scratch row of target 0: up message (root: dummy row) / down ratio / unnormalised marginal
     int32_t aux_row;      // SUM_DISTRIBUTE: row of entry 0 of the child's up message (0 guard of TableDivision)
     int32_t inv_row;      // SUM_COLLECT: scratch row receiving 1/sum(clique)
     int32_t rows, cols;
-    int32_t nrest, ncolv;
+    int32_t nfold, nfx;   // folded variables, evidence patterns per entry (1 = plain potentials)
+    int32_t ncmask;
     int32_t ng;           // gathers per entry
     int32_t ninv;
     int32_t normslot;     // SUM_COLLECT: index among the collect ops of its phase
@@ -76,9 +88,7 @@ struct SumOp {
     int32_t chunks, rows_per_chunk;
     int32_t pslot0;       // chunks > 1: partial slot of (col, chunk) = pslot0 + col*chunks + chunk
     int32_t rot;          // units of earlier ops in the phase (fused mode: mod team): keeps the round-robin over warps going
-    int32_t rowmask_off;  // shared-memory word offsets of this op's per-tile evidence mask tables (rows / cols entries of kW
-    int32_t colmask_off;  //   words), -1: tables do not fit, evaluate the masks on the fly
-    int32_t pad0, pad1;
+    int32_t pad0;
 };
 
 enum FinType : int32_t { FIN_SUM = 0, FIN_NORM = 1, FIN_D = 2 };
@@ -96,7 +106,7 @@ struct Phase {
     int32_t op_begin, op_end;  // into oplist[] (indices into ops[])
     int32_t fin_begin, fin_end;
     int32_t n_normslots;
-    int32_t mask_words;        // shared-memory mask-table entries (of kW words) this phase builds
+    int32_t pad;
     int32_t n_units;           // warp work units of the phase (level mode: sizes the grid)
 };
 
@@ -108,8 +118,10 @@ struct VarInfo {
 // Kernel parameter block (device pointers)
 struct DevPlan {
     const double *pot;
-    const uint16_t *lam16;
     const int32_t *idx32;
+    const int32_t *lamvars;  // variables whose lambda rows some op gathers
+    int32_t n_lamvars;
+    int32_t lam_row0;        // scratch row of (variable 0, state 0)'s lambda row
     const int32_t *flatc;   // flat plans: entry records (int4 aligned)
     const SumOp *ops;
     const int32_t *oplist;
@@ -120,22 +132,22 @@ struct DevPlan {
     int32_t n_vars, sum_dims, query_var;
     int32_t tile_rows;   // rows per tile
     int32_t mg_row0;
-    int32_t max_normslots, max_pslots, max_mask_words;
+    int32_t max_normslots, max_pslots;
     int32_t team;        // warps per tile (level mode: nominal gang warps the split was planned for)
     int32_t cb;          // targets per unit the plan was made for
     int32_t part_row0;      // first of max_pslots rows (partial sums of split ops)
     int32_t normpart_row0;  // first of max_normslots * nb_max rows: row (normslot * nb_max + share)
     int32_t nb_max;         // norm shares per collect op (fused: team warps; level: CTAs per tile a phase may be launched with)
-    int32_t lam_words;      // (sum_dims + n_vars) * kW
+    int32_t pat_bytes;      // n_vars * kTileCases: evidence pattern byte of (variable, case of the tile)
     int32_t flat;           // 1: every op has flat records (jt_flat_kernel)
 };
 
 // --- host-side plan ----------------------------------------------------------------------------------------------
 struct HostPlan {
     std::vector<double> pot;
-    std::vector<uint16_t> lam16;
     std::vector<int32_t> idx32;
     std::vector<int32_t> flatc;
+    std::vector<int32_t> lamvars;
     bool flat = false;
     std::vector<SumOp> ops;
     std::vector<int32_t> oplist;
@@ -144,8 +156,8 @@ struct HostPlan {
     std::vector<VarInfo> vars;
     int32_t n_vars = 0, n_cliques = 0, n_seps = 0, sum_dims = 0, query_var = 0;
     int32_t n_levels = 0;
-    int32_t tile_rows = 0, mup_row0 = 0, dn_row0 = 0, inv_row0 = 0, mg_row0 = 0;
-    int32_t max_normslots = 0, max_pslots = 0, max_mask_words = 0;
+    int32_t tile_rows = 0, mup_row0 = 0, dn_row0 = 0, inv_row0 = 0, mg_row0 = 0, lam_row0 = 0;
+    int32_t max_normslots = 0, max_pslots = 0;
     int32_t team = 1, cb = 1;
     bool level = false;          // level mode (one launch per phase, many CTAs per tile)
     int32_t part_row0 = 0, normpart_row0 = 0, nb_max = 1;
@@ -153,6 +165,7 @@ struct HostPlan {
     int64_t clique_entries = 0, sep_entries = 0, parent_entries = 0, marginal_entries = 0;
     int64_t view_entries = 0;    // sum over all ops of rows*cols (entries recomputed per case)
     int64_t gather_rows = 0;     // sum over all ops of rows*cols*ng (message rows gathered per case, before register blocking)
+    int64_t folded_vars = 0, lambda_gathers = 0;  // uncovered (view, variable) pairs folded into pattern tables / gathered as lambda rows
     // per-variable marginal source, for tests: table index (clique c, or n_cliques + s)
     std::vector<int32_t> marg_source;
     double alg_bytes_per_case = 0, kernel_bytes_per_case = 0;

@@ -19,7 +19,7 @@ static std::string g_err;
 extern "C" const char *emu_last_error() { return g_err.c_str(); }
 
 extern "C" int emu_run(const fbn_tree_desc *tree, int team, int64_t n_cases, const int64_t *ev_off, const int32_t *ev_vars,
-                       const int32_t *ev_vals, int32_t *labels, double *post, int64_t *info /* 12 */) {
+                       const int32_t *ev_vals, int32_t *labels, double *post, int64_t *info /* 16 */) {
     HostPlan P;
     const bool level = team < 0;  // negative: level mode planned for -team gang warps (fastbn_b200/csrc/level_kernels.cu)
     if (level) team = -team;
@@ -29,23 +29,25 @@ extern "C" int emu_run(const fbn_tree_desc *tree, int team, int64_t n_cases, con
         info[0] = (int64_t)P.phases.size(); info[1] = P.n_units; info[2] = (int64_t)P.fins.size();
         info[3] = P.max_pslots; info[4] = P.max_normslots; info[5] = P.tile_rows; info[6] = P.n_levels; info[7] = P.parent_entries;
         info[8] = P.view_entries; info[9] = P.gather_rows; info[10] = P.flat ? 1 : 0; info[11] = (int64_t)P.pot.size();
+        info[12] = P.folded_vars; info[13] = P.lambda_gathers;
     }
     const int kColBlock = P.cb;
     const int shares = level ? P.nb_max : team;   // norm shares per collect op
     const bool use_flat = P.flat;  // team 1 fused plans of small trees carry flat records: interpret those
     std::vector<double> S((size_t)P.tile_rows);
-    std::vector<char> lam((size_t)P.sum_dims), obs((size_t)P.n_vars);
+    std::vector<int> pat((size_t)P.n_vars);   // evidence pattern of every variable: 0 not observed, 1 + state, dim + 1 = no valid state
     for (int64_t cs = 0; cs < n_cases; ++cs) {
         std::fill(S.begin(), S.end(), -12345.0);  // poison: reading a row before writing it shows up in the results
-        std::fill(lam.begin(), lam.end(), 1);
-        std::fill(obs.begin(), obs.end(), 0);
+        std::fill(pat.begin(), pat.end(), 0);
         for (int64_t k = ev_off[cs]; k < ev_off[cs + 1]; ++k) {
             int v = ev_vars[k], val = ev_vals[k];
             if (v < 0 || v >= P.n_vars) continue;
-            obs[v] = 1;
-            for (int d = 0; d < P.vars[v].dim; ++d)
-                if (d != val) lam[P.vars[v].off + d] = 0;
+            const int dim = P.vars[v].dim;
+            const int np = (val < 0 || val >= dim) ? dim + 1 : 1 + val;
+            pat[v] = (pat[v] == 0 || pat[v] == np) ? np : dim + 1;  // two different states observed: nothing is consistent
         }
+        for (int v : P.lamvars)  // lambda rows of the variables some op gathers
+            for (int d = 0; d < P.vars[v].dim; ++d) S[P.lam_row0 + P.vars[v].off + d] = (pat[v] == 0 || pat[v] == 1 + d) ? 1.0 : 0.0;
         for (const Phase &ph : P.phases) {
             std::vector<double> normshare((size_t)std::max(1, ph.n_normslots) * shares, 0.0);
             std::vector<double> part((size_t)std::max(1, P.max_pslots), -777.0);
@@ -54,7 +56,9 @@ extern "C" int emu_run(const fbn_tree_desc *tree, int team, int64_t n_cases, con
                 const int units = (op.cols + kColBlock - 1) / kColBlock * op.chunks;
                 double scale = 1.0;
                 for (int k = 0; k < op.ninv; ++k) scale *= S[P.idx32[op.invrow_off + k]];
-                const int rstride = 1 + (op.ng > 2 ? 1 : 0);  // int4 per flat record
+                int64_t fx = 0;  // this case's evidence pattern of the op's folded variables
+                for (int k = 0; k < op.nfold; ++k) fx += (int64_t)pat[P.idx32[op.fold_off + 2 * k]] * P.idx32[op.fold_off + 2 * k + 1];
+                const int rstride = 1 + (op.ng > 3 ? 1 : 0);  // int4 per flat record
                 for (int u = 0; u < units; ++u)
                     for (int cc = 0; cc < kColBlock; ++cc) {  // the targets of the unit's block
                         int jb = u / op.chunks;
@@ -65,26 +69,25 @@ extern "C" int emu_run(const fbn_tree_desc *tree, int team, int64_t n_cases, con
                         const int share = (op.rot + u) % shares;
                         int r0 = 0, r1 = op.rows;
                         if (op.chunks > 1) { r0 = ck * op.rows_per_chunk; r1 = std::min(op.rows, r0 + op.rows_per_chunk); }
-                        bool cm = true;
-                        for (int i = 0; i < op.ncolv; ++i) cm = cm && lam[P.lam16[op.collam_off + (int64_t)j * op.ncolv + i]];
                         double acc = 0.0;
                         for (int r = r0; r < r1; ++r) {
-                            bool m = cm;
-                            for (int i = 0; i < op.nrest; ++i) m = m && lam[P.lam16[op.rowlam_off + (int64_t)r * op.nrest + i]];
                             double v;
-                            if (use_flat) {  // the flat records of jt_flat_kernel (column-major, absolute gather rows)
+                            if (use_flat) {  // the flat records of jt_flat_kernel (target-major, absolute gather rows)
                                 const int64_t x = op.flat_off + ((int64_t)j * op.rows + r) * 4 * rstride;
-                                double pv;
-                                memcpy(&pv, &P.flatc[x], 8);
-                                v = pv * scale;
-                                for (int g = 0; g < op.ng; ++g) v *= S[P.flatc[x + 2 + g]];  // {pot, g0, g1} {g2, g3, g4, g5}
+                                v = P.pot[P.flatc[x] + fx];
+                                for (int g = 0; g < op.ng; ++g) v *= S[P.flatc[x + 1 + g]];  // {pot index, g0, g1, g2} {g3, g4, g5, g6}
                             } else {
-                                v = (op.pot_off < 0 ? 1.0 : P.pot[op.pot_off + (int64_t)r * op.cols + j]) * scale;
+                                v = op.pot_off < 0 ? 1.0 : P.pot[op.pot_off + ((int64_t)r * op.cols + j) * op.nfx + fx];
                                 for (int g = 0; g < op.ng; ++g)
                                     v *= S[P.idx32[op.rowpart_off + (int64_t)r * op.ng + g] + P.idx32[op.colpart_off + (int64_t)j * op.ng + g]];
                             }
-                            if (!m) v = 0.0;
                             acc += v;
+                        }
+                        acc *= scale;
+                        for (int k = 0; k < op.ncmask; ++k) {  // uncovered target variables of a collect view
+                            const int32_t *cmk = &P.idx32[op.cmask_off + 3 * k];
+                            const int pv = pat[cmk[0]], d = (j / cmk[1]) % cmk[2];
+                            if (pv != 0 && pv != 1 + d) acc = 0.0;
                         }
                         if (op.chunks > 1) {
                             part[op.pslot0 + j * op.chunks + ck] = acc;
@@ -116,7 +119,7 @@ extern "C" int emu_run(const fbn_tree_desc *tree, int team, int64_t n_cases, con
             double best = 0.0;
             int arg = -1;
             for (int d = 0; d < vi.dim; ++d) {
-                double pr = obs[v] ? 0.0 : S[P.mg_row0 + vi.off + d] / sum;
+                double pr = pat[v] ? 0.0 : S[P.mg_row0 + vi.off + d] / sum;
                 if (post) post[cs * P.sum_dims + vi.off + d] = pr;
                 if (pr > best) { best = pr; arg = d; }
             }

@@ -36,7 +36,7 @@ def run(t, team, ev_off, ev_vars, ev_vals):
     sd = int(np.sum(t["var_dims"]))
     post = np.zeros((n, sd))
     lab = np.zeros(n, np.int32)
-    info = np.zeros(12, np.int64)
+    info = np.zeros(16, np.int64)
     eo = np.ascontiguousarray(ev_off, np.int64)
     ev = np.ascontiguousarray(ev_vars, np.int32)
     ew = np.ascontiguousarray(ev_vals, np.int32)
