@@ -14,23 +14,13 @@ namespace fbn {
 
 // One SumOp: all units (target block x row chunk) of the op that this warp owns.
 template <int TEAM, int CB>
-__device__ __forceinline__ void sum_op(const DevPlan &P, const SumOp &__restrict__ op, double *S, const uint8_t *pat, int lane, int warp) {
-    const V scale = op_scale(P, op, S);
-    const Fx fx = op_fx(P, op, pat, lane);
-    const int units = (op.cols + CB - 1) / CB * op.chunks;
-    V nacc = vset(0.0);
-    for (int u = (warp - op.rot) & (TEAM - 1); u < units; u += TEAM) {
-        int j0, nc, ck, r0, r1;
-        sum_unit<CB>(P, op, u, j0, nc, ck, r0, r1);
-        V acc[CB];
-#pragma unroll
-        for (int c = 0; c < CB; ++c) acc[c] = vset(0.0);
-        sum_block_any<CB>(P, op, fx, S, lane, j0, r0, r1, acc);
-        vadd(nacc, store_unit<CB>(P, op, S, pat, lane, j0, nc, ck, scale, acc));
-    }
+__device__ __forceinline__ void sum_op(const DevPlan &P, const SumOp &__restrict__ op, double *S, const uint8_t *pat, int lane, int warp,
+                                       PotStage &st) {
+    const V nacc = sum_units<CB, false>(P, op, S, pat, lane, (warp - op.rot) & (TEAM - 1), TEAM, st);
     // this warp's share of sum(clique): one row per (collect op of the phase, warp), summed by the phase's FIN_NORM item
     if (op.kind == SUM_COLLECT) stv(row_ptr(S, P.normpart_row0 + op.normslot * P.nb_max + warp), nacc);
 }
+
 
 template <int TEAM, int CB>
 __global__ void __launch_bounds__(TEAM * 32, (FBN_OCC / TEAM) > 0 ? (FBN_OCC / TEAM) : 1) jt_fused_kernel(const DevPlan P, double *__restrict__ scratch, int64_t n_cases,
@@ -38,10 +28,10 @@ __global__ void __launch_bounds__(TEAM * 32, (FBN_OCC / TEAM) > 0 ? (FBN_OCC / T
                                                             const int32_t *__restrict__ ev_vars,
                                                             const int32_t *__restrict__ ev_vals, int32_t *__restrict__ labels,
                                                             double *__restrict__ post, int64_t n_tiles) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
+    extern __shared__ __align__(128) unsigned char smem_raw[];
     uint8_t *pat = smem_raw;  // [n_vars][kTileCases] evidence pattern bytes of the tile
-
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    PotStage st = PotStage();  // potentials come in by coalesced loads here (shared-memory staging is a level-mode path, ops.cuh)
     double *S = scratch + (int64_t)blockIdx.x * P.tile_rows * kRowDoubles + lane * kW;  // lane-private columns of this CTA's tile
     auto sync = [] { if (TEAM > 1) __syncthreads(); else __syncwarp(); };
 
@@ -56,7 +46,7 @@ __global__ void __launch_bounds__(TEAM * 32, (FBN_OCC / TEAM) > 0 ? (FBN_OCC / T
 
         for (int ph = 0; ph < P.n_phases; ++ph) {
             const Phase p = P.phases[ph];
-            for (int oi = p.op_begin; oi < p.op_end; ++oi) sum_op<TEAM, CB>(P, P.ops[P.oplist[oi]], S, pat, lane, warp);
+            for (int oi = p.op_begin; oi < p.op_end; ++oi) sum_op<TEAM, CB>(P, P.ops[P.oplist[oi]], S, pat, lane, warp, st);
             if (p.fin_end > p.fin_begin) {
                 sync();
                 for (int f = p.fin_begin + warp; f < p.fin_end; f += TEAM) fin_item(P, P.fins[f], S, TEAM);

@@ -38,33 +38,28 @@ __global__ void __launch_bounds__(128) lvl_evidence_kernel(const DevPlan P, doub
     write_lambda_rows(P, S, pat, lane, warp, blockDim.x >> 5);
 }
 
-// One phase (tree level) of SumOps: grid (CTAs per tile, tiles).
+// One phase (tree level) of SumOps: grid (CTAs per tile, tiles). Dynamic shared memory: two potential buffers per warp, two
+// mbarriers per warp, the norm reduction rows.
+constexpr uint32_t kLvlPotBuf = 4096;
+constexpr size_t kLvlSmem = (size_t)kLevelWarps * (2 * kLvlPotBuf + 16) + (size_t)kLevelWarps * kRowDoubles * sizeof(double);
 template <int CB>
 __global__ void __launch_bounds__(kLevelWarps * 32, FBN_LVL_OCC) lvl_sum_kernel(const DevPlan P, double *__restrict__ scratch,
                                                                                 const uint8_t *__restrict__ patG, int phase_idx) {
-    __shared__ double red[kLevelWarps][kRowDoubles];
+    extern __shared__ __align__(128) unsigned char lsm[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(lsm + (size_t)kLevelWarps * 2 * kLvlPotBuf);
+    double(*red)[kRowDoubles] = reinterpret_cast<double(*)[kRowDoubles]>(lsm + (size_t)kLevelWarps * (2 * kLvlPotBuf + 16));
+    PotStage st;
+    pot_stage_init(st, lsm + (size_t)warp * 2 * kLvlPotBuf, bars + 2 * warp, kLvlPotBuf, lane);
     const int gw = blockIdx.x * kLevelWarps + warp, GW = gridDim.x * kLevelWarps;
     double *S = scratch + (int64_t)blockIdx.y * P.tile_rows * kRowDoubles + lane * kW;
     const uint8_t *pat = patG + (int64_t)blockIdx.y * P.pat_bytes;
     const Phase ph = P.phases[phase_idx];
     for (int oi = ph.op_begin; oi < ph.op_end; ++oi) {
         const SumOp &__restrict__ op = P.ops[P.oplist[oi]];
-        const V scale = op_scale(P, op, S);
-        const Fx fx = op_fx(P, op, pat, lane);
-        const int units = (op.cols + CB - 1) / CB * op.chunks;
         int start = (gw - op.rot % GW) % GW;
         if (start < 0) start += GW;
-        V nacc = vset(0.0);
-        for (int u = start; u < units; u += GW) {
-            int j0, nc, ck, r0, r1;
-            sum_unit<CB>(P, op, u, j0, nc, ck, r0, r1);
-            V acc[CB];
-#pragma unroll
-            for (int c = 0; c < CB; ++c) acc[c] = vset(0.0);
-            sum_block_any<CB>(P, op, fx, S, lane, j0, r0, r1, acc);
-            vadd(nacc, store_unit<CB>(P, op, S, pat, lane, j0, nc, ck, scale, acc));
-        }
+        const V nacc = sum_units<CB, true>(P, op, S, pat, lane, start, GW, st);
         if (op.kind == SUM_COLLECT) {  // this CTA's share of sum(clique): one share row per (collect op, CTA)
 #pragma unroll
             for (int i = 0; i < kW; ++i) red[warp][lane * kW + i] = nacc.x[i];
@@ -110,6 +105,12 @@ cudaError_t level_launch(const DevPlan &P, const std::vector<Phase> &phases, int
                          int64_t n_cases, const int64_t *ev_off, int64_t ev_base, const int32_t *ev_vars, const int32_t *ev_vals,
                          int32_t *labels, double *post, cudaStream_t st, int64_t *n_launch) {
     if (P.cb != 4 && P.cb != 8) return cudaErrorInvalidValue;
+    static bool attr_done = false;  // more than 48 KB of dynamic shared memory needs the opt-in, once per context is enough
+    if (!attr_done) {
+        cudaError_t ea = cudaFuncSetAttribute(lvl_sum_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kLvlSmem);
+        if (ea == cudaSuccess) ea = cudaFuncSetAttribute(lvl_sum_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kLvlSmem);
+        if (ea != cudaSuccess) return ea;
+    }
     const int64_t n_tiles = (n_cases + kTileCases - 1) / kTileCases;
     int64_t launches = 0;
     for (int64_t tile0 = 0; tile0 < n_tiles; tile0 += resident) {
@@ -122,8 +123,8 @@ cudaError_t level_launch(const DevPlan &P, const std::vector<Phase> &phases, int
             int nb = (ph.n_units + 2 * kLevelWarps - 1) / (2 * kLevelWarps);
             nb = std::max(1, std::min(nb, P.nb_max));
             dim3 grid((unsigned)nb, wt);
-            if (P.cb == 8) lvl_sum_kernel<8><<<grid, kLevelWarps * 32, 0, st>>>(P, scratch, patG, (int)pi);
-            else lvl_sum_kernel<4><<<grid, kLevelWarps * 32, 0, st>>>(P, scratch, patG, (int)pi);
+            if (P.cb == 8) lvl_sum_kernel<8><<<grid, kLevelWarps * 32, kLvlSmem, st>>>(P, scratch, patG, (int)pi);
+            else lvl_sum_kernel<4><<<grid, kLevelWarps * 32, kLvlSmem, st>>>(P, scratch, patG, (int)pi);
             ++launches;
             const int nfin = ph.fin_end - ph.fin_begin;
             if (nfin > 0) {

@@ -123,6 +123,68 @@ __device__ __forceinline__ Fx op_fx(const DevPlan &P, const SumOp &op, const uin
     return f;
 }
 
+// ---- potentials through shared memory: cp.async.bulk (TMA) + mbarrier ---------------------------------------------
+// The potentials of one unit of warp work are one contiguous stream (unit-major potX, plan.h). Every warp owns two
+// shared-memory buffers and two mbarriers: lane 0 starts the bulk copy of the NEXT block of rows (or of the next unit's
+// first block) while the warp sums the current one; the row loop then reads its potentials from shared memory (same
+// address in all lanes: one broadcast LDS.128 per two targets) instead of waiting on a global load and passing values
+// around by shuffles. Copies are issued and waited for in the same order, buffer = count & 1, mbarrier parity = (count >> 1) & 1.
+struct PotStage {
+    unsigned char *base;   // this warp's two buffers (generic address), buf_bytes each
+    uint32_t base_s;       // the same as a shared-memory address
+    uint32_t bar_s;        // shared-memory address of this warp's two mbarriers (8 bytes each)
+    uint32_t buf_bytes;
+    uint32_t issued, waited;
+};
+__device__ __forceinline__ void pot_stage_init(PotStage &st, unsigned char *bufs, uint64_t *bars, uint32_t buf_bytes, int lane) {
+    st.base = bufs;
+    st.base_s = (uint32_t)__cvta_generic_to_shared(bufs);
+    st.bar_s = (uint32_t)__cvta_generic_to_shared(bars);
+    st.buf_bytes = buf_bytes;
+    st.issued = st.waited = 0;
+    if (lane == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(st.bar_s));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(st.bar_s + 8));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+}
+// start the copy of `bytes` (multiple of 16, <= buf_bytes) from global `src` (16-byte aligned) into the next buffer
+__device__ __forceinline__ void pot_issue(PotStage &st, const double *src, uint32_t bytes, int lane) {
+    __syncwarp();  // every lane has finished reading the buffer this copy overwrites
+    if (lane == 0) {
+        const uint32_t slot = st.issued & 1u, bar = st.bar_s + 8 * slot;
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // the warp's reads of the buffer (generic proxy) before the copy engine's write
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(st.base_s + slot * st.buf_bytes),
+                     "l"(src), "r"(bytes), "r"(bar)
+                     : "memory");
+    }
+    ++st.issued;
+}
+// wait for the oldest copy in flight; returns its buffer
+__device__ __forceinline__ const double *pot_wait(PotStage &st) {
+    const uint32_t slot = st.waited & 1u, parity = (st.waited >> 1) & 1u, bar = st.bar_s + 8 * slot;
+    uint32_t done = 0;
+    while (!done) {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.b32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done)
+                     : "r"(bar), "r"(parity)
+                     : "memory");
+    }
+    ++st.waited;
+    return reinterpret_cast<const double *>(st.base + slot * st.buf_bytes);
+}
+// can this op's potentials go through the staged path? (plain potentials; folded views read per-case pattern slots)
+__device__ __forceinline__ bool pot_staged(const SumOp &op) { return op.pot_off >= 0 && op.nfx == 1; }
+// first block of rows of unit (j0, r0, r1): source address and bytes
+template <int CB>
+__device__ __forceinline__ void pot_unit_block(const DevPlan &P, const SumOp &op, const PotStage &st, int j0, int r0, int r1, const double *&src,
+                                               uint32_t &bytes) {
+    src = P.pot + op.pot_off + ((int64_t)(j0 / CB) * op.rows + r0) * CB;
+    bytes = (uint32_t)min(r1 - r0, (int)(st.buf_bytes / (CB * 8))) * (CB * 8);
+}
+
 // ---- SUM ---------------------------------------------------------------------------------------------------------
 // Targets [j0, j0+nc) (nc <= CB), rows [r0, r1) of one view:
 //   e = potX[r, j][fx] * prod_g message_g[rowpart_g(r) + colpart_g(j)];  acc[c] += e(r, j0+c)
@@ -135,22 +197,36 @@ __device__ __forceinline__ Fx op_fx(const DevPlan &P, const SumOp &op, const uin
 // Software pipeline: the loads of row r+1 are issued BEFORE row r is multiplied and summed (two register sets, used
 // alternately); the row parts of the index maps are fetched two rows ahead. Rows that need many gathers keep one register
 // set (loads issued together at the top of the row).
-template <int NG, int UMASK, int CB, bool FOLD>
+template <int NG, int UMASK, int CB, int POT, bool TMA>   // POT: 0 = all ones, 1 = plain (TMA: staged through shared memory, else coalesced load + shuffle), 2 = folded
 __device__ __forceinline__ void sum_rows(const DevPlan &P, const SumOp &op, const Fx &fx, const double *S, int lane, int j0, int r0, int r1,
-                                         const int32_t (&cp)[NG > 0 ? NG : 1][CB], V (&acc)[CB]) {
+                                         const int32_t (&cp)[NG > 0 ? NG : 1][CB], V (&acc)[CB], PotStage &st, const double *next_src,
+                                         uint32_t next_bytes) {
+    constexpr bool FOLD = POT == 2;
+    constexpr bool STAGE = POT == 1 && CB >= 2 && TMA;
     constexpr int NGC = NG > 0 ? NG : 1;
     constexpr int NU = (UMASK & 1) + ((UMASK >> 1) & 1) + ((UMASK >> 2) & 1) + ((UMASK >> 3) & 1);
-    constexpr int kLoads = (NG > 0 ? (NG - NU) * CB + NU : 0) * kW + (FOLD ? CB * kW / 2 : 0);  // 16-byte units per row
+    constexpr int kLoads = (NG > 0 ? (NG - NU) * CB + NU : 0) * kW + (POT == 2 ? CB * kW / 2 : 0);  // 16-byte units per row
     constexpr bool kTwoSets = NG > 0 && CB >= 4 && kLoads <= 12;
     const int ng = NG >= 0 ? NG : op.ng, cols = op.cols;
-    const bool has_pot = op.pot_off >= 0;
+    constexpr bool has_pot = POT != 0;
     const double *__restrict__ pot = P.pot + (has_pot ? op.pot_off : 0);
     const int32_t *__restrict__ rowpart = P.idx32 + op.rowpart_off;
     const int32_t *__restrict__ colpart = P.idx32 + op.colpart_off;
+    // POT 1, cb 1: ONE coalesced load serves 32 rows, the row loop picks its value by shuffle
     constexpr int RPL = 32 / CB;
-    const int lane_c = lane % CB, lane_r = lane / CB;
-    const double *potl = pot + min(j0 + lane_c, cols - 1);
-    double potv = 1.0, potv_next = (has_pot && !FOLD) ? __ldg(potl + (int64_t)min(r0 + lane_r, r1 - 1) * cols) : 1.0;
+    const double *potl = pot + (int64_t)(j0 / CB) * op.rows * CB * (POT == 2 ? op.nfx : 1);   // the unit's block of potX (unit-major)
+    double potv = 1.0, potv_next = (POT == 1 && !STAGE) ? __ldg(potl + min((int64_t)r0 * CB + lane, (int64_t)r1 * CB - 1)) : 1.0;
+    // POT 1, cb >= 2: blocks of `sb` rows come in through shared memory (PotStage above); the copy of rows [r0, r0 + sb) was
+    // started by the caller
+    const int sb = STAGE ? (int)(st.buf_bytes / (CB * 8)) : 0;
+    int sb_begin = r0, sb_end = STAGE ? min(r1, r0 + sb) : r1;
+    const double *pb = nullptr;
+    auto next_block = [&]() {  // rows [sb_begin, sb_end) are about to be summed: start the copy after them, wait for theirs
+        if (sb_end < r1) pot_issue(st, potl + (int64_t)sb_end * CB, (uint32_t)min(r1 - sb_end, sb) * (CB * 8), lane);
+        else if (next_src) pot_issue(st, next_src, next_bytes, lane);
+        pb = pot_wait(st);
+    };
+    if (STAGE) next_block();
     int jc[CB];
 #pragma unroll
     for (int c = 0; c < CB; ++c) jc[c] = min(j0 + c, cols - 1);
@@ -158,7 +234,7 @@ __device__ __forceinline__ void sum_rows(const DevPlan &P, const SumOp &op, cons
 
     struct Set {
         V m[NGC][CB];
-        double pv[FOLD ? CB : 1][kW];
+        double pv[POT == 2 ? CB : 1][kW];
     };
     auto load_parts = [&](int rr, int32_t (&rp)[NGC]) {
         if (NG > 0) {
@@ -169,11 +245,11 @@ __device__ __forceinline__ void sum_rows(const DevPlan &P, const SumOp &op, cons
     };
     auto gather = [&](int rr, const int32_t (&rp)[NGC], Set &s) {
         if (FOLD) {
-            const int64_t rbase = (int64_t)min(rr, r1 - 1) * cols;
+            const double *q = potl + (int64_t)min(rr, r1 - 1) * CB * nfx;
 #pragma unroll
             for (int c = 0; c < CB; ++c)
 #pragma unroll
-                for (int i = 0; i < kW; ++i) s.pv[FOLD ? c : 0][i] = __ldg(pot + (rbase + jc[c]) * nfx + fx.x[i]);
+                for (int i = 0; i < kW; ++i) s.pv[FOLD ? c : 0][i] = __ldg(q + c * nfx + fx.x[i]);
         }
         if (NG > 0) {
 #pragma unroll
@@ -190,14 +266,30 @@ __device__ __forceinline__ void sum_rows(const DevPlan &P, const SumOp &op, cons
     };
     auto finish = [&](int r, const Set &s) {
         double pc[CB];
-        if (!FOLD) {
+        if (STAGE) {
+            if (r == sb_end) {
+                sb_begin = sb_end;
+                sb_end = min(r1, sb_begin + sb);
+                next_block();
+            }
+            const double *q = pb + (r - sb_begin) * CB;
+#pragma unroll
+            for (int c = 0; c < CB; c += 2) {
+                const double2 t = *reinterpret_cast<const double2 *>(q + c);  // LDS.128, same address in all lanes
+                pc[c] = t.x;
+                pc[c + (CB > 1 ? 1 : 0)] = t.y;
+            }
+        } else if (POT == 1) {
             const int rg = (r - r0) & (RPL - 1);  // row inside its group of RPL
             if (rg == 0) {
                 potv = potv_next;
-                if (has_pot) potv_next = __ldg(potl + (int64_t)min(r + RPL + lane_r, r1 - 1) * cols);
+                potv_next = __ldg(potl + min((int64_t)(r + RPL) * CB + lane, (int64_t)r1 * CB - 1));
             }
 #pragma unroll
             for (int c = 0; c < CB; ++c) pc[c] = __shfl_sync(0xffffffffu, potv, rg * CB + c);
+        } else if (POT == 0) {
+#pragma unroll
+            for (int c = 0; c < CB; ++c) pc[c] = 1.0;
         }
         V u = vset(1.0);
         if (NG > 0) {
@@ -258,9 +350,9 @@ __device__ __forceinline__ void sum_rows(const DevPlan &P, const SumOp &op, cons
     }
 }
 
-template <int NG, int CB>
+template <int NG, int CB, bool TMA>
 __device__ __forceinline__ void sum_block(const DevPlan &P, const SumOp &op, const Fx &fx, const double *S, int lane, int j0, int r0, int r1,
-                                          V (&acc)[CB]) {
+                                          V (&acc)[CB], PotStage &st, const double *next_src, uint32_t next_bytes) {
     const int cols = op.cols;
     int32_t cp[NG > 0 ? NG : 1][CB];
     const int32_t *__restrict__ colpart = P.idx32 + op.colpart_off;
@@ -281,8 +373,9 @@ __device__ __forceinline__ void sum_block(const DevPlan &P, const SumOp &op, con
     }
     auto run = [&](auto um) {
         constexpr int UM = decltype(um)::value;
-        if (op.nfx > 1) sum_rows<NG, UM, CB, true>(P, op, fx, S, lane, j0, r0, r1, cp, acc);
-        else sum_rows<NG, UM, CB, false>(P, op, fx, S, lane, j0, r0, r1, cp, acc);
+        if (op.pot_off < 0) sum_rows<NG, UM, CB, 0, TMA>(P, op, fx, S, lane, j0, r0, r1, cp, acc, st, next_src, next_bytes);
+        else if (op.nfx > 1) sum_rows<NG, UM, CB, 2, TMA>(P, op, fx, S, lane, j0, r0, r1, cp, acc, st, next_src, next_bytes);
+        else sum_rows<NG, UM, CB, 1, TMA>(P, op, fx, S, lane, j0, r0, r1, cp, acc, st, next_src, next_bytes);
     };
     if constexpr (NG > 0 && NG <= 2 && CB >= 2) {
         switch (umask) {
@@ -303,16 +396,16 @@ __device__ __forceinline__ void sum_block(const DevPlan &P, const SumOp &op, con
     }
 }
 
-template <int CB>
+template <int CB, bool TMA>
 __device__ __forceinline__ void sum_block_any(const DevPlan &P, const SumOp &op, const Fx &fx, const double *S, int lane, int j0, int r0,
-                                              int r1, V (&acc)[CB]) {
+                                              int r1, V (&acc)[CB], PotStage &st, const double *next_src, uint32_t next_bytes) {
     switch (op.ng) {
-        case 0: sum_block<0, CB>(P, op, fx, S, lane, j0, r0, r1, acc); break;
-        case 1: sum_block<1, CB>(P, op, fx, S, lane, j0, r0, r1, acc); break;
-        case 2: sum_block<2, CB>(P, op, fx, S, lane, j0, r0, r1, acc); break;
-        case 3: sum_block<3, CB>(P, op, fx, S, lane, j0, r0, r1, acc); break;
-        case 4: sum_block<4, CB>(P, op, fx, S, lane, j0, r0, r1, acc); break;
-        default: sum_block<-1, CB>(P, op, fx, S, lane, j0, r0, r1, acc); break;
+        case 0: sum_block<0, CB, TMA>(P, op, fx, S, lane, j0, r0, r1, acc, st, next_src, next_bytes); break;
+        case 1: sum_block<1, CB, TMA>(P, op, fx, S, lane, j0, r0, r1, acc, st, next_src, next_bytes); break;
+        case 2: sum_block<2, CB, TMA>(P, op, fx, S, lane, j0, r0, r1, acc, st, next_src, next_bytes); break;
+        case 3: sum_block<3, CB, TMA>(P, op, fx, S, lane, j0, r0, r1, acc, st, next_src, next_bytes); break;
+        case 4: sum_block<4, CB, TMA>(P, op, fx, S, lane, j0, r0, r1, acc, st, next_src, next_bytes); break;
+        default: sum_block<-1, CB, TMA>(P, op, fx, S, lane, j0, r0, r1, acc, st, next_src, next_bytes); break;
     }
 }
 
@@ -379,6 +472,43 @@ __device__ __forceinline__ V store_unit(const DevPlan &P, const SumOp &op, doubl
             }
             vadd(nacc, a);
         }
+    return nacc;
+}
+
+// All units u = first, first + stride, ... < units of one op for one warp: the potentials of unit k+1 are on their way into
+// shared memory while unit k is summed. Returns this warp's share of the op's total (a collect op's norm).
+template <int CB, bool TMA>
+__device__ __forceinline__ V sum_units(const DevPlan &P, const SumOp &op, double *S, const uint8_t *pat, int lane, int first, int stride,
+                                       PotStage &st) {
+    const V scale = op_scale(P, op, S);
+    const Fx fx = op_fx(P, op, pat, lane);
+    const int units = (op.cols + CB - 1) / CB * op.chunks;
+    const bool staged = TMA && CB >= 2 && pot_staged(op);
+    V nacc = vset(0.0);
+    int j0, nc, ck, r0, r1;
+    const double *src = nullptr;
+    uint32_t bytes = 0;
+    if (first < units) {
+        sum_unit<CB>(P, op, first, j0, nc, ck, r0, r1);
+        if (staged) {
+            pot_unit_block<CB>(P, op, st, j0, r0, r1, src, bytes);
+            pot_issue(st, src, bytes, lane);
+        }
+    }
+    for (int u = first; u < units; u += stride) {
+        int j0n = 0, ncn = 0, ckn = 0, r0n = 0, r1n = 0;
+        src = nullptr;
+        if (u + stride < units) {
+            sum_unit<CB>(P, op, u + stride, j0n, ncn, ckn, r0n, r1n);
+            if (staged) pot_unit_block<CB>(P, op, st, j0n, r0n, r1n, src, bytes);
+        }
+        V acc[CB];
+#pragma unroll
+        for (int c = 0; c < CB; ++c) acc[c] = vset(0.0);
+        sum_block_any<CB, TMA>(P, op, fx, S, lane, j0, r0, r1, acc, st, src, bytes);
+        vadd(nacc, store_unit<CB>(P, op, S, pat, lane, j0, nc, ck, scale, acc));
+        j0 = j0n; nc = ncn; ck = ckn; r0 = r0n; r1 = r1n;
+    }
     return nacc;
 }
 

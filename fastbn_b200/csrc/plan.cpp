@@ -271,31 +271,27 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
             for (size_t k = tpos.size(); k-- > 0 && tpos[k] != i;) cst *= X.dims[tpos[k]];
             P.idx32.push_back(X.vars[i]); P.idx32.push_back((int32_t)cst); P.idx32.push_back(X.dims[i]);
         }
-        bool native = fold_pos.empty();
-        for (size_t i = 0; i < tpos.size(); ++i) native = native && tpos[i] == (int)(X.vars.size() - tpos.size() + i);
         if (c < 0) {
             op.pot_off = -1;  // separators carry no potentials (all ones in the reference)
-        } else if (native) {
-            op.pot_off = pot_off[c];
         } else {
-            // potX[(r*cols + j)*nfx + fx]: the folded row variables summed out under evidence pattern fx; a folded target
-            // variable zeroes the targets its pattern rules out
+            // potX in UNIT-MAJOR order: block b of cb adjacent targets, then row, then target inside the block, then pattern:
+            //   potX[(((j / cb) * rows + r) * cb + j % cb) * nfx + fx]
+            // so that the potentials of one unit of warp work (target block x row range) are ONE contiguous stream (fetched
+            // by cp.async.bulk into shared memory, ops.cuh) and a flat plan (cb = 1) reads them in record order. The last
+            // block is padded with zeros. Entry (r, j, fx): the folded row variables summed out under evidence pattern fx.
+            while (P.pot.size() & 1) P.pot.push_back(0.0);  // 16-byte alignment of every view (bulk copies)
             op.pot_off = (int64_t)P.pot.size();
-            P.pot.resize(P.pot.size() + (size_t)op.rows * op.cols * nfx);
+            const int64_t nblk = (op.cols + kColBlock - 1) / kColBlock;
+            P.pot.resize(P.pot.size() + (size_t)(nblk * op.rows * kColBlock * nfx), 0.0);
             double *dst = P.pot.data() + op.pot_off;
             const double *src = t.clique_potentials + pot_off[c];
             const std::vector<int32_t> froff = enumerate_offsets(X, frpos);
-            const std::vector<int> frdig = enumerate_digits(X, frpos), cdig = enumerate_digits(X, tpos);
+            const std::vector<int> frdig = enumerate_digits(X, frpos);
             const int nfr = (int)frpos.size(), nfold = (int)fold_pos.size();
-            // fold slot of every folded variable: index k in fold_pos; for row ones also the index among frpos, for target ones among tpos
-            std::vector<int> fr_slot(nfr), fc_slot, fc_tidx;
+            std::vector<int> fr_slot(nfr);  // index in fold_pos of every folded row variable
             for (int a = 0; a < nfr; ++a) fr_slot[a] = (int)(std::find(fold_pos.begin(), fold_pos.end(), frpos[a]) - fold_pos.begin());
-            for (int k = 0; k < nfold; ++k) {
-                auto it = std::find(tpos.begin(), tpos.end(), fold_pos[k]);
-                if (it != tpos.end()) { fc_slot.push_back(k); fc_tidx.push_back((int)(it - tpos.begin())); }
-            }
             std::vector<int> pat(nfold);
-            std::vector<char> combo_ok(froff.size());
+            std::vector<int32_t> combo;  // offsets of the folded-variable configurations pattern fx allows
             for (int64_t fx = 0; fx < nfx; ++fx) {
                 int64_t x = fx;
                 bool dead = false;  // a variable observed in no valid state: everything is zero
@@ -305,28 +301,22 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
                     x /= d + 2;
                     dead = dead || pat[k] == d + 1;
                 }
-                for (size_t q = 0; q < froff.size(); ++q) {
-                    bool ok = !dead;
+                combo.clear();
+                for (size_t q = 0; q < froff.size() && !dead; ++q) {
+                    bool ok = true;
                     for (int a = 0; a < nfr && ok; ++a) {
                         const int pk = pat[fr_slot[a]];
                         ok = pk == 0 || pk - 1 == frdig[q * nfr + a];
                     }
-                    combo_ok[q] = ok;
+                    if (ok) combo.push_back(froff[q]);
                 }
                 for (int64_t j = 0; j < op.cols; ++j) {
-                    bool colok = !dead;
-                    for (size_t a = 0; a < fc_slot.size() && colok; ++a) {
-                        const int pk = pat[fc_slot[a]];
-                        colok = pk == 0 || pk - 1 == cdig[(size_t)j * tpos.size() + fc_tidx[a]];
-                    }
+                    double *d2 = dst + ((j / kColBlock) * op.rows * kColBlock + j % kColBlock) * nfx + fx;
                     for (int64_t r = 0; r < op.rows; ++r) {
+                        const int64_t e0 = (int64_t)roff[(size_t)r] + coff[(size_t)j];
                         double sum = 0.0;
-                        if (colok) {
-                            const int64_t e0 = (int64_t)roff[(size_t)r] + coff[(size_t)j];
-                            for (size_t q = 0; q < froff.size(); ++q)
-                                if (combo_ok[q]) sum += src[e0 + froff[q]];
-                        }
-                        dst[(r * op.cols + j) * nfx + fx] = sum;
+                        for (int32_t o : combo) sum += src[e0 + o];
+                        d2[r * kColBlock * nfx] = sum;
                     }
                 }
             }
@@ -610,7 +600,7 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
                         int32_t m[7] = {0, 0, 0, 0, 0, 0, 0};
                         for (int g = 0; g < ng; ++g)
                             m[g] = P.idx32[(size_t)(op.rowpart_off + r * ng + g)] + P.idx32[(size_t)(op.colpart_off + j * ng + g)];
-                        const int64_t pi = op.pot_off < 0 ? one_idx : op.pot_off + (r * op.cols + j) * op.nfx;
+                        const int64_t pi = op.pot_off < 0 ? one_idx : op.pot_off + (j * op.rows + r) * op.nfx;  // cb = 1: target-major
                         P.flatc.push_back((int32_t)pi); P.flatc.push_back(m[0]); P.flatc.push_back(m[1]); P.flatc.push_back(m[2]);
                         if (ng > 3) { P.flatc.push_back(m[3]); P.flatc.push_back(m[4]); P.flatc.push_back(m[5]); P.flatc.push_back(m[6]); }
                     }

@@ -62,7 +62,8 @@ enum SumKind : int32_t { SUM_COLLECT = 0, SUM_DISTRIBUTE = 1, SUM_MARGINAL = 2 }
 //   or GATHERED as a unary message: the tile's lambda rows (lam_row0 + var offset + state: 1.0 allowed / 0.0 ruled out) are one
 //     more gather of the entry (used when the pattern table would get too big).
 struct SumOp {
-    int64_t pot_off;      // into pot[]: potX in VIEW order ((r*cols + j)*nfx + fx doubles), -1 = all ones
+    int64_t pot_off;      // into pot[]: potX, unit-major: (((j / cb) * rows + r) * cb + j % cb) * nfx + fx (16-byte aligned, last
+                          //   target block zero-padded), -1 = all ones
     int64_t fold_off;     // into idx32[]: nfold pairs {variable, pattern stride}
     int64_t cmask_off;    // into idx32[]: ncmask triples {variable, stride of its digit in the target index, dim}: uncovered TARGET
                           //   variables of a collect view; a finished sum is zeroed when the case observed another state

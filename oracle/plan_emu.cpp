@@ -77,7 +77,7 @@ extern "C" int emu_run(const fbn_tree_desc *tree, int team, int64_t n_cases, con
                                 v = P.pot[P.flatc[x] + fx];
                                 for (int g = 0; g < op.ng; ++g) v *= S[P.flatc[x + 1 + g]];  // {pot index, g0, g1, g2} {g3, g4, g5, g6}
                             } else {
-                                v = op.pot_off < 0 ? 1.0 : P.pot[op.pot_off + ((int64_t)r * op.cols + j) * op.nfx + fx];
+                                v = op.pot_off < 0 ? 1.0 : P.pot[op.pot_off + (((int64_t)(j / kColBlock) * op.rows + r) * kColBlock + j % kColBlock) * op.nfx + fx];
                                 for (int g = 0; g < op.ng; ++g)
                                     v *= S[P.idx32[op.rowpart_off + (int64_t)r * op.ng + g] + P.idx32[op.colpart_off + (int64_t)j * op.ng + g]];
                             }
