@@ -364,7 +364,8 @@ def run_workload(cx, name, steps, warmup, e2e_steps, cases=0, team=0, mode=0, ma
     info = plan.info
     sd = info.sum_dims
     n = cases or w["cases"]
-    waves = -(-((n + capi.TILE_CASES - 1) // capi.TILE_CASES) // info.resident_tiles)
+    tile_cases = info.tile_cases
+    waves = -(-((n + tile_cases - 1) // tile_cases) // info.resident_tiles)
     launches_per_step = info.launches_per_wave * waves if info.mode == capi.MODE_LEVEL else 1
     off_h, ev_h, ew_h, gpost, glab = make_batch(name, n, cx.rank)
     k = len(glab)
@@ -444,6 +445,21 @@ def run_workload(cx, name, steps, warmup, e2e_steps, cases=0, team=0, mode=0, ma
         e2e_s = float(t.item())
     e2e_value = cx.world * n * e2e_steps / e2e_s
     same = bool(np.array_equal(labels_p, labels_d.cpu().numpy()))
+    # the same call when the caller wants what PredictUseJTInfer returns (labels): posteriors never leave the device, 4 bytes per case back
+    lab_only = np.empty(n, np.int32)
+    plan.run(off_p, ev_p, ew_p, want_post=False, labels_out=labels_p)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        _, _, st_l = plan.run(off_p, ev_p, ew_p, want_post=False, labels_out=labels_p)
+    barrier()
+    e2e_l_s = time.perf_counter() - t0
+    if cx.world > 1:
+        t = torch.tensor([e2e_l_s], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_l_s = float(t.item())
+    e2e_labels_value = cx.world * n * e2e_steps / e2e_l_s
+    del lab_only
     e2e_max_abs = float(np.max(np.abs(post_p[:k] - gpost))) if k else 0.0
     ok = max_abs <= TOL and e2e_max_abs <= TOL and labels_equal and same
     if cx.world > 1:
@@ -452,7 +468,7 @@ def run_workload(cx, name, steps, warmup, e2e_steps, cases=0, team=0, mode=0, ma
         ok = float(t.item()) == 0.0
 
     if info.mode == capi.MODE_LEVEL:
-        kernel = "lvl_collect_kernel+lvl_pull_kernel (all launches of a step)"
+        kernel = "lvl_sum_kernel (all launches of a step)"
     else:
         kernel = plan.kernel_name
     traffic, tsrc = traffic_entry(name, info, kernel)
@@ -463,9 +479,11 @@ def run_workload(cx, name, steps, warmup, e2e_steps, cases=0, team=0, mode=0, ma
         "workload": w["desc"], "cases": n, "n_evidence": w["n_evidence"], "steps": steps, "warmup": warmup,
         "value": value, "unit": "cases/s", "ms_per_step": ms_per_step,
         "e2e": {"value": e2e_value, "unit": "cases/s", "steps": e2e_steps, "h2d_bytes_per_step": int(st.h2d_bytes),
-                "d2h_bytes_per_step": int(st.d2h_bytes), "launches_per_step": int(st.n_launches)},
+                "d2h_bytes_per_step": int(st.d2h_bytes), "launches_per_step": int(st.n_launches),
+                "labels_only": {"value": e2e_labels_value, "unit": "cases/s", "d2h_bytes_per_step": int(st_l.d2h_bytes),
+                                "note": "posteriors_out = NULL: what PredictUseJTInfer returns; not bound by the 8*sum_dims bytes per case of the posterior stream"}},
         "kernel": kernel, "kernel_ms": kern_ms, "mode": "level" if info.mode == capi.MODE_LEVEL else "fused",
-        "team_warps": info.team_warps, "resident_tiles": info.resident_tiles, "tile_cases": capi.TILE_CASES, "launches_per_step": launches_per_step,
+        "team_warps": info.team_warps, "resident_tiles": info.resident_tiles, "tile_cases": tile_cases, "launches_per_step": launches_per_step,
         "kernel_rev": info.kernel_rev,
         # DRAM-based roofline: ncu dram__bytes_read+write per case (profiles/traffic.json, same kernel revision) x cases / device time
         "dram_bytes_per_case": traffic, "dram_source": tsrc, "dram_gbs": dram_gbs, "dram_frac": dram_gbs / peak if dram_gbs else None,

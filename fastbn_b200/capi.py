@@ -125,7 +125,7 @@ class Plan:
     def kernel_name(self):
         """Name of the kernel a fused-mode plan launches (level mode launches one kernel per tree level)."""
         if self.info.mode == MODE_LEVEL:
-            return "lvl_collect_kernel+lvl_pull_kernel"
+            return "lvl_sum_kernel"
         return "jt_flat_kernel" if self.info.flat_records else "jt_fused_kernel<%d>" % self.info.team_warps
 
     def close(self):

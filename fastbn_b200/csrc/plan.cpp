@@ -212,7 +212,7 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
         if (!finish_table(lamtab[v], t.var_dims, nv, err)) return err;
     }
     std::vector<char> lam_needed(nv, 0);
-    static const int64_t kMaxFx = getenv("FBN_MAX_FX") ? std::max(1, atoi(getenv("FBN_MAX_FX"))) : 64;
+    const int64_t kMaxFx = getenv("FBN_MAX_FX") ? std::max(1, atoi(getenv("FBN_MAX_FX"))) : 64;  // evidence patterns per entry at most
 
     // ---- views -------------------------------------------------------------------------------------------------------
     // A view of table X (clique c >= 0, or a separator: c < 0) with the variables at positions `tpos` as targets.

@@ -168,3 +168,34 @@ def test_evaluate_pipeline_matches_reference_printout(plan, alarm_tree, want_pos
     other = np.array([int(l.split(" ")[0]) for l in open(os.path.join(GOLDEN, "alarm", "alarm_1k_p20")).read().strip().split("\n")], np.int32)
     _, _, sc2, _ = plan.evaluate(g["ev_off"], g["ev_vars"], g["ev_vals"], gold, other)
     assert sc2["n_correct"] == 513
+
+
+@pytest.mark.parametrize("team", [0, 4])
+def test_duplicate_conflicting_and_invalid_evidence(alarm_tree, team):
+    """same pair twice = once; two values for one variable, a value >= dim or < 0 = nothing consistent (NaN, label -1): the
+    CUDA path must give what the CPU oracle gives (the reference's DiscreteConfig is a set of pairs)"""
+    from test_plan_host import _odd_evidence
+    off, ev, ew = _odd_evidence()
+    o = jtoracle.Oracle(alarm_tree)
+    want, wlab = o.run_batch(off, ev, ew)
+    o.close()
+    p = capi.Plan(alarm_tree, device=0, team_warps=team)
+    labels, post, _ = p.run(off, ev, ew)
+    p.close()
+    assert np.array_equal(np.isnan(post), np.isnan(want))
+    assert np.nanmax(np.abs(post - want)) <= TOL and np.array_equal(labels, wlab)
+
+
+@pytest.mark.parametrize("max_fx", ["1", "8"])
+@pytest.mark.parametrize("team,mode", [(0, 0), (4, 0), (0, 2)])
+def test_lambda_gather_path(alarm_tree, team, mode, max_fx, monkeypatch):
+    """FBN_MAX_FX caps the evidence patterns per entry: uncovered variables beyond the cap are gathered as lambda rows (the path
+    big pattern tables take). Flat, fused and level kernels against the reference fixtures."""
+    monkeypatch.setenv("FBN_MAX_FX", max_fx)
+    p = capi.Plan(alarm_tree, device=0, team_warps=team, mode=mode)
+    for name in ["alarm_1k_ref", "alarm_edge_ref"]:
+        g = load_golden(name)
+        labels, post, _ = p.run(g["ev_off"], g["ev_vars"], g["ev_vals"])
+        assert np.array_equal(np.isnan(post), np.isnan(g["post"]))
+        assert np.nanmax(np.abs(post - g["post"])) <= TOL and np.array_equal(labels, g["labels"])
+    p.close()

@@ -94,7 +94,7 @@ def test_shape_batch_properties(name, n, nev):
     assert np.all(np.abs(sums[~is_ev] - 1.0) < 1e-10)
     assert np.all(sums[is_ev] == 0.0)
     assert np.array_equal(post[0], post[-1]) and labels[0] == labels[-1]
-    k = 24
+    k = 256  # seeded prefix through the CPU oracle (pinned bit-exact to the reference, tests/test_oracle.py)
     o = jtoracle.Oracle(t)
     opost, olab = o.run_batch(off[:k + 1], ev[:k * nev], ew[:k * nev])
     o.close()

@@ -82,7 +82,7 @@ def test_no_cpu_fallback_without_device(alarm_tree):
 @pytest.mark.parametrize("team", [32, -64])
 def test_plan_with_permuted_block_order_on_pigs_shape(team):
     """PIGS-shape (max clique 3^10): the planner visits the column blocks of big cliques in a locality order
-    (CollectOp::perm_off); the emulated plan must still reproduce the unmodified reference (fused team 32 and level mode)."""
+    (SumOp::perm_off); the emulated plan must still reproduce the unmodified reference (fused team 32 and level mode)."""
     from fastbn_b200 import hostapi
     m = hostapi.HostModel(os.path.join(ROOT, "tests", "golden", "synth", "pigs.xml"))
     t = m.tree()
@@ -133,3 +133,55 @@ def test_unit_order_of_a_phase_does_not_change_results(team, monkeypatch):
     assert info[1] == info0[1] and info[3] == info0[3]  # same units and partial slots, only their order differs
     t1 = emu.run(t, 1, *args)[2]
     assert info[5] >= t1[5] + info[4] * team  # tile rows: tables + messages + one norm row per (clique of a phase, warp)
+
+
+def _odd_evidence():
+    """duplicate pair (same value twice), conflicting values for one variable, a value >= dim, a negative value, a plain case"""
+    vl = [[5, 5, 9], [5, 5, 9], [7], [7], [3, 9]]
+    wl = [[1, 1, 0], [0, 1, 0], [9], [-1], [1, 2]]
+    off = np.concatenate([[0], np.cumsum([len(v) for v in vl])]).astype(np.int64)
+    return off, np.concatenate(vl).astype(np.int32), np.concatenate(wl).astype(np.int32)
+
+
+@pytest.mark.parametrize("team", [1, 4, -16])
+def test_evidence_patterns_duplicates_conflicts_and_invalid_values(alarm_tree, team):
+    """Evidence is a set of (variable, value) pairs in the reference (DiscreteConfig): the same pair twice is harmless, two
+    different values for one variable or a value outside [0, dim) leave nothing consistent (NaN posteriors, label -1). The
+    planner's evidence patterns (0 / 1 + state / dim + 1) must give exactly what the CPU oracle gives."""
+    from oracle import jtoracle
+    off, ev, ew = _odd_evidence()
+    o = jtoracle.Oracle(alarm_tree)
+    want, wlab = o.run_batch(off, ev, ew)
+    o.close()
+    post, lab, _ = emu.run(alarm_tree, team, off, ev, ew)
+    assert np.array_equal(np.isnan(post), np.isnan(want)) and np.isnan(want[1:4]).any(axis=1).all() and not np.isnan(want[[0, 4]]).any()
+    assert np.nanmax(np.abs(post - want)) <= 1e-12 and np.array_equal(lab, wlab)
+
+
+@pytest.mark.parametrize("max_fx", ["1", "8", "1024"])
+@pytest.mark.parametrize("team", [1, 8])
+def test_folded_and_gathered_evidence_agree(alarm_tree, team, max_fx, monkeypatch):
+    """An uncovered variable of a view is either folded into per-pattern potentials or gathered as lambda rows
+    (FBN_MAX_FX caps the patterns per entry: 1 = gather everything, 1024 = fold everything). Every split must reproduce the
+    reference, on ALARM and on the HEPAR2 shape."""
+    from fastbn_b200 import hostapi
+    monkeypatch.setenv("FBN_MAX_FX", max_fx)
+    g = load_golden("alarm_1k_ref")
+    n = 300
+    k = g["ev_off"][n]
+    post, lab, info = emu.run(alarm_tree, team, g["ev_off"][:n + 1], g["ev_vars"][:k], g["ev_vals"][:k])
+    assert np.nanmax(np.abs(post - g["post"][:n])) <= 1e-9 and np.array_equal(lab, g["labels"][:n])
+    assert (info[13] > 0) == (max_fx != "1024") and (info[12] > 0) == (max_fx != "1")  # lambda gathers / folded variables
+    g = load_golden("alarm_edge_ref")
+    post, lab, _ = emu.run(alarm_tree, team, g["ev_off"], g["ev_vars"], g["ev_vals"])
+    assert np.array_equal(np.isnan(post), np.isnan(g["post"])) and np.nanmax(np.abs(post - g["post"])) <= 1e-9
+    m = hostapi.HostModel(os.path.join(ROOT, "tests", "golden", "synth", "hepar2.xml"))
+    t = m.tree()
+    m.close()
+    g = load_golden(os.path.join("synth", "hepar2_ref"))
+    idx = list(range(8)) + list(range(256, 264))
+    off = np.concatenate([[0], np.cumsum([g["ev_off"][i + 1] - g["ev_off"][i] for i in idx])]).astype(np.int64)
+    ev = np.concatenate([g["ev_vars"][g["ev_off"][i]:g["ev_off"][i + 1]] for i in idx])
+    ew = np.concatenate([g["ev_vals"][g["ev_off"][i]:g["ev_off"][i + 1]] for i in idx])
+    post, lab, _ = emu.run(t, team, off, ev, ew)
+    assert np.nanmax(np.abs(post - g["post"][idx])) <= 1e-9 and np.array_equal(lab, g["labels"][idx])
