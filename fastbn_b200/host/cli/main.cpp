@@ -2,7 +2,10 @@
 // Same flags (-a -t -f0 -f3 -f4; the others are parsed and ignored), same default files, paths relative to
 // "../dataset/", same stdout lines. Algorithms other than 2 are outside this build and say so.
 // Extensions: -G <n> shards the test cases over n GPUs (or FASTBN_DEVICES=0,1,...); -o <file> writes the posteriors
-// in the reference's potential-table format (relative to ../dataset/ too); -D <dir> replaces the "../dataset/" prefix.
+// in the reference's potential-table format (relative to ../dataset/ too); -D <dir> replaces the "../dataset/" prefix;
+// -C keeps a binary cache of the parsed test cases beside the -f3 file (<file>.fbncache, validated by size + mtime).
+// -t N is accepted like in the reference; the GPU path has no use for it (the reference's OpenMP parallelism is INSIDE one
+// case). The CPU baseline for a given -t is a separate tool that drives the unmodified reference: tools/ref_cpu_baseline.py.
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -26,12 +29,13 @@ int main(int argc, char **argv) {
         };
         switch (argv[i][1]) {
             case 'h':
-                cout << "Usage: ./BayesianNetwork -a 2 [-t threads] [-f0 bn.xml] [-f3 test cases] [-f4 potential tables] [-G gpus] [-o out_pt] [-D dataset dir]" << endl;
+                cout << "Usage: ./BayesianNetwork -a 2 [-t threads] [-f0 bn.xml] [-f3 test cases] [-f4 potential tables] [-G gpus] [-o out_pt] [-D dataset dir] [-C]" << endl;
                 exit(0);
             case 'a': algorithm = atoi(need("a")); break;
             case 't': num_threads = atoi(need("t")); break;
             case 'q': case 'm': case 'l': case 'd': case 'g': need("x"); break;  // sampling / PC-stable options: ignored
             case 'G': n_gpus = atoi(need("G")); break;
+            case 'C': setenv("FASTBN_EVIDENCE_CACHE", "1", 1); break;
             case 'o': out_pt = need("o"); break;
             case 'D': prefix = need("D"); if (!prefix.empty() && prefix.back() != '/') prefix += '/'; break;
             case 'f':
@@ -76,8 +80,11 @@ int main(int argc, char **argv) {
         for (int d = 0; d < (n_gpus > 0 ? n_gpus : 1); ++d) vis += (d ? "," : "") + std::to_string(d);
         setenv("CUDA_VISIBLE_DEVICES", vis.c_str(), 0);
     }
-    // CUDA contexts come up in the background while the input files are parsed
-    std::thread([n_gpus] { for (int d = 0; d < (n_gpus > 0 ? n_gpus : 1); ++d) fbn_device_warmup(d); }).detach();
+    // CUDA contexts come up in the background while the input files are parsed. The thread is joined before the process ends,
+    // also on the loaders' error exits (exit(1) on a missing file or a malformed line runs the atexit hook).
+    static std::thread warm;
+    warm = std::thread([n_gpus] { for (int d = 0; d < (n_gpus > 0 ? n_gpus : 1); ++d) fbn_device_warmup(d); });
+    atexit([] { if (warm.joinable()) warm.join(); });
     Dataset *tester = new Dataset();
     CustomNetwork *network = new CustomNetwork(true);
     network->GetNetFromXMLBIFFile(net_file);
@@ -105,5 +112,6 @@ int main(int argc, char **argv) {
     delete inference;
     delete network;
     delete tester;
+    if (warm.joinable()) warm.join();
     return 0;
 }

@@ -32,6 +32,15 @@ Inference::Inference(Network *net, Dataset *dts, bool is_dense)
     var_offsets.assign(net->num_nodes + 1, 0);
     for (int v = 0; v < net->num_nodes; ++v) var_offsets[v + 1] = var_offsets[v] + net->FindNodePtrByIndex(v)->GetDomainSize();
     ground_truths.assign(dts->labels.begin(), dts->labels.end());
+    {   // a value outside the variable's domain silently wipes every table (NaN posteriors, label -1) exactly as in the
+        // reference; a malformed test file should at least be visible
+        int64_t bad = 0;
+        for (size_t k = 0; k < dts->ev_vars.size(); ++k) {
+            const int v = dts->ev_vars[k];
+            if (v >= 0 && v < net->num_nodes && (dts->ev_vals[k] < 0 || dts->ev_vals[k] >= var_offsets[v + 1] - var_offsets[v])) ++bad;
+        }
+        if (bad) fprintf(stderr, "Warning: %lld evidence value(s) outside the variable's domain: those cases have no consistent state (nan posteriors)\n", (long long)bad);
+    }
     if (!is_dense) {
         // DiscreteConfig is a std::set of (variable, value): ascending and without duplicates (src/Inference.cpp:21-33)
         ev_offsets.assign(1, 0);
@@ -432,7 +441,14 @@ vector<int> JunctionTree::PredictUseJTInfer(int) {
         probs_one_sample[v].assign(last_post.begin() + var_offsets[v], last_post.begin() + var_offsets[v + 1]);
     average_mse = mse / n;
     average_hd = hd / n;
-    if (!quiet) std::cout << "100.000000%..." << std::endl;
+    if (!quiet && n >= 20) {
+        // the reference prints one line per n/20 cases while it walks them (src/JunctionTree.cpp:1509-1524); here the whole
+        // batch is back at once, the same lines follow each other
+        const int every = n / 20;
+        for (int progress = every; progress <= n; progress += every)
+            fprintf(stdout, "%s\n", (std::to_string((double)progress / n * 100) + "%...").c_str());
+        fflush(stdout);
+    }
     std::cout << "average MSE = " << average_mse << std::endl;
     std::cout << "average HD = " << average_hd << std::endl;
     return predictions;
@@ -447,9 +463,21 @@ double JunctionTree::EvaluateAccuracy(string path, int num_threads) {
     double accuracy = Accuracy(pred);
     jt_seconds = now_s() - t0;
     std::cout << "==================================================" << std::endl;
-    std::cout << "jt: " << jt_seconds << " s "
-              << "device kernels: " << kernel_ms * 1e-3 << " s (" << devices.size() << " GPU" << (devices.size() > 1 ? "s" : "")
-              << ", " << (jt_seconds > 0 ? num_instances / jt_seconds : 0.0) << " cases/s)" << std::endl;
+    // the reference's timer block (src/JunctionTree.cpp:76-124), same names. What the names mean here: the whole batch is ONE
+    // pipelined call, evidence loading, message passing and the marginals + ArgMax + MSE/HD run inside the same kernels, so
+    // "msg passing" is the device time of those kernels (max over the devices), "load evidence" the rest of the call (staging
+    // and host<->device copies that the pipeline could not hide), "predict" and "reset" have no separate pass (0).
+    {
+        const double dev_s = std::min(jt_seconds, kernel_ms * 1e-3), rest = std::max(0.0, jt_seconds - dev_s);
+        auto pct = [&](double x) { return jt_seconds > 0 ? x / jt_seconds * 100 : 0.0; };
+        std::cout << "jt: " << jt_seconds << " s " << "removing reset: " << jt_seconds << " s " << "removing norm: " << jt_seconds << " s ";
+        std::cout << "load evidence: " << rest << " s (" << pct(rest) << "%) ";
+        std::cout << "msg passing: " << dev_s << " s (" << pct(dev_s) << "%) ";
+        std::cout << "reset: " << 0.0 << " s (" << 0.0 << "%) ";
+        std::cout << "predict: " << 0.0 << " s (" << 0.0 << "%)" << std::endl;
+        std::cout << "device kernels: " << kernel_ms * 1e-3 << " s (" << devices.size() << " GPU" << (devices.size() > 1 ? "s" : "") << ", "
+                  << (jt_seconds > 0 ? num_instances / jt_seconds : 0.0) << " cases/s)" << std::endl << std::endl;
+    }
     return accuracy;
 }
 

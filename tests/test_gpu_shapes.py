@@ -132,6 +132,10 @@ def test_cli_default_run_prints_reference_lines(tmp_path):
                  "maximum level of the junction tree = 15", "average MSE = 6.50867e-17", "average HD = 4.6999e-17", "accuracy = 1"]:
         assert line in r.stdout, line
     assert "jt: " in r.stdout
+    # the reference's progress lines (one per n/20 cases) and timer block names (src/JunctionTree.cpp:76-84, :1509-1524)
+    for line in ["Progress indicator: ", "5.000000%...", "100.000000%...", "load evidence: ", "msg passing: ", "reset: ", "predict: "]:
+        assert line in r.stdout, line
+    assert r.stdout.count("%...") == 20
     r = subprocess.run([exe, "-a", "2", "-t", "4", "-f3", "alarm/alarm_1k_p20"], cwd=bd, capture_output=True, text=True, timeout=300)
     assert "accuracy = 0.513" in r.stdout
     out = tmp_path / "out_pt"

@@ -90,6 +90,55 @@ def test_libsvm_loader_quirks(tmp_path):
     assert ev.tolist() == [2, 3, 4, 5] and ew.tolist() == [0, 1, 2, 1]
 
 
+def test_libsvm_loader_parallel_pieces_and_binary_cache(tmp_path, monkeypatch):
+    """A file of several MB is mmap'ed and parsed in pieces of whole lines by several threads: the result must be the
+    sequential one (incl. the dropped unterminated last line). With FASTBN_EVIDENCE_CACHE=1 the parsed arrays are kept in
+    <file>.fbncache, reused while the text file's size and mtime match, and rebuilt when the file changes."""
+    n = 400_000
+    tree = hostapi.HostModel(ALARM_XML)
+    dims = tree.tree()["var_dims"]
+    tree.close()
+    off, ev, ew = synth.uniform_evidence(dims, n, 7, seed=3)
+    labels = (np.arange(n) % 2).astype(np.int32)
+    p = str(tmp_path / "cases")
+    synth.write_libsvm(p, off, ev, ew, labels=labels)
+    with open(p, "a") as f:
+        f.write("1 3:1")  # unterminated last line: dropped (src/Dataset.cpp:179-227)
+    assert os.path.getsize(p) > (12 << 20)  # several 4 MB pieces
+    m = hostapi.HostModel(ALARM_XML, p)
+    o1, v1, w1, t1 = m.cases()
+    m.close()
+    assert np.array_equal(o1, off) and np.array_equal(v1, ev) and np.array_equal(w1, ew) and np.array_equal(t1, labels)
+    assert not os.path.exists(p + ".fbncache")  # opt-in
+    monkeypatch.setenv("FASTBN_EVIDENCE_CACHE", "1")
+    m = hostapi.HostModel(ALARM_XML, p)
+    m.close()
+    assert os.path.exists(p + ".fbncache")
+    stamp = os.path.getmtime(p + ".fbncache")
+    m = hostapi.HostModel(ALARM_XML, p)   # served from the cache
+    o2, v2, w2, t2 = m.cases()
+    m.close()
+    assert np.array_equal(o2, off) and np.array_equal(v2, ev) and np.array_equal(w2, ew) and np.array_equal(t2, labels)
+    assert os.path.getmtime(p + ".fbncache") == stamp
+    with open(p, "a") as f:
+        f.write(" 4:0\n0 2:1 \n")       # the text file changes: the cache no longer matches and is rebuilt
+    m = hostapi.HostModel(ALARM_XML, p)
+    o3, v3, w3, t3 = m.cases()
+    m.close()
+    assert len(t3) == n + 2 and t3[-2:].tolist() == [1, 0] and v3[-3:].tolist() == [3, 4, 2] and w3[-3:].tolist() == [1, 0, 1]
+    m = hostapi.HostModel(ALARM_XML, p)
+    o4, v4, w4, t4 = m.cases()
+    m.close()
+    assert np.array_equal(o4, o3) and np.array_equal(v4, v3) and np.array_equal(t4, t3)
+    with open(p + ".fbncache", "r+b") as f:  # a damaged cache is ignored, not trusted
+        f.seek(0)
+        f.write(b"garbage!")
+    m = hostapi.HostModel(ALARM_XML, p)
+    o5, v5, w5, t5 = m.cases()
+    m.close()
+    assert np.array_equal(o5, o3) and np.array_equal(v5, v3) and np.array_equal(w5, w3)
+
+
 def test_xmlbif_count_truncation_and_laplace():
     """(int)(p*10000) truncates (0.69 -> 6899) and P = (count+1)/(total+dim): no zero entries, SURVEY.md 8(c) quirk 1"""
     m = hostapi.HostModel(ALARM_XML)
