@@ -438,11 +438,11 @@ __device__ __forceinline__ V finish_target(const DevPlan &P, const SumOp &op, co
     vmul(acc, scale);
     const int32_t *__restrict__ cmk = P.idx32 + op.cmask_off;
     for (int k = 0; k < op.ncmask; ++k) {
-        const int v = __ldg(cmk + 3 * k), d = (j / __ldg(cmk + 3 * k + 1)) % __ldg(cmk + 3 * k + 2);
+        const int v = __ldg(cmk + k), want = __ldg(cmk + op.ncmask + j * op.ncmask + k);
 #pragma unroll
         for (int i = 0; i < kW; ++i) {
             const int pv = pat[v * kTileCases + lane * kW + i];
-            if (pv != 0 && pv != 1 + d) acc.x[i] = 0.0;
+            if (pv != 0 && pv != want) acc.x[i] = 0.0;
         }
     }
     return acc;

@@ -222,8 +222,10 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
         SumOp op = SumOp();
         op.kind = kind;
         auto is_target = [&](int i) { return std::find(tpos.begin(), tpos.end(), i) != tpos.end(); };
-        // uncovered variables: in none of the gathered tables. Target variables of distribute / marginal views need nothing
-        // (0 guard on the child's up message; an observed variable is reported as zeros).
+        // uncovered variables: in none of the gathered tables. Target variables of marginal views need nothing (an observed
+        // variable is reported as zeros); those of collect AND distribute views are checked once per finished sum, so that a
+        // down ratio is zero wherever the evidence rules its target out even without the 0 guard of TableDivision (the flat
+        // kernel drops that guard, flat_kernel.cu).
         std::vector<int> fold_pos, cmask_pos;
         int64_t nfx = 1;
         if (c >= 0) {
@@ -233,7 +235,7 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
                 for (const GatherSrc &g : gs) covered = covered || g.tab->find(X.vars[i]) >= 0;
                 if (covered) continue;
                 if (!is_target(i)) unc.push_back(i);
-                else if (kind == SUM_COLLECT) cmask_pos.push_back(i);  // checked once per finished sum, not per entry
+                else if (kind != SUM_MARGINAL) cmask_pos.push_back(i);  // checked once per finished sum, not per entry
             }
             std::stable_sort(unc.begin(), unc.end(), [&](int a, int b) { return X.dims[a] < X.dims[b]; });
             for (int i : unc) {
@@ -266,10 +268,16 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
         }
         op.cmask_off = (int64_t)P.idx32.size();
         op.ncmask = (int32_t)cmask_pos.size();
-        for (int i : cmask_pos) {
-            int64_t cst = 1;  // stride of the variable's digit in the target index (targets are enumerated row-major over tpos)
-            for (size_t k = tpos.size(); k-- > 0 && tpos[k] != i;) cst *= X.dims[tpos[k]];
-            P.idx32.push_back(X.vars[i]); P.idx32.push_back((int32_t)cst); P.idx32.push_back(X.dims[i]);
+        if (!cmask_pos.empty()) {  // the variables, then for every target its pattern byte "1 + digit" of each of them
+            for (int i : cmask_pos) P.idx32.push_back(X.vars[i]);
+            std::vector<int64_t> cst;  // stride of the variable's digit in the target index (targets are enumerated row-major over tpos)
+            for (int i : cmask_pos) {
+                int64_t s = 1;
+                for (size_t k = tpos.size(); k-- > 0 && tpos[k] != i;) s *= X.dims[tpos[k]];
+                cst.push_back(s);
+            }
+            for (int64_t j = 0; j < op.cols; ++j)
+                for (size_t k = 0; k < cmask_pos.size(); ++k) P.idx32.push_back(1 + (int32_t)((j / cst[k]) % X.dims[cmask_pos[k]]));
         }
         if (c < 0) {
             op.pot_off = -1;  // separators carry no potentials (all ones in the reference)

@@ -58,15 +58,16 @@ enum SumKind : int32_t { SUM_COLLECT = 0, SUM_DISTRIBUTE = 1, SUM_MARGINAL = 2 }
 //   FOLDED into the potentials: the planner sums the variable out of the view for every EVIDENCE PATTERN (0 = not observed,
 //     1 + d = observed in state d, dim + 1 = observed in no valid state) and stores nfx = prod (dim + 2) values per entry; a
 //     case looks its pattern index fx up once per op (fold list below, per-tile pattern bytes) and reads potX[entry*nfx + fx];
-//   (row variables only; an uncovered TARGET variable of a collect view is checked once per finished sum, cmask list below)
+//   (row variables only; an uncovered TARGET variable of a collect / distribute view is checked once per finished sum, cmask list below)
 //   or GATHERED as a unary message: the tile's lambda rows (lam_row0 + var offset + state: 1.0 allowed / 0.0 ruled out) are one
 //     more gather of the entry (used when the pattern table would get too big).
 struct SumOp {
     int64_t pot_off;      // into pot[]: potX, unit-major: (((j / cb) * rows + r) * cb + j % cb) * nfx + fx (16-byte aligned, last
                           //   target block zero-padded), -1 = all ones
     int64_t fold_off;     // into idx32[]: nfold pairs {variable, pattern stride}
-    int64_t cmask_off;    // into idx32[]: ncmask triples {variable, stride of its digit in the target index, dim}: uncovered TARGET
-                          //   variables of a collect view; a finished sum is zeroed when the case observed another state
+    int64_t cmask_off;    // into idx32[]: ncmask variables, then cols x ncmask pattern bytes (1 + the target's digit of the variable):
+                          //   uncovered TARGET variables of a collect / distribute view; a finished sum is zeroed when the case
+                          //   observed another state
     int64_t rowpart_off;  // into idx32[]: rows*ng  (absolute scratch row of gather g's source, row part)
     int64_t colpart_off;  // into idx32[]: cols*ng  (column part)
     int64_t invrow_off;   // into idx32[]: ninv absolute scratch rows whose product scales the sums (1/norm of cliques)

@@ -84,15 +84,15 @@ extern "C" int emu_run(const fbn_tree_desc *tree, int team, int64_t n_cases, con
                             acc += v;
                         }
                         acc *= scale;
-                        for (int k = 0; k < op.ncmask; ++k) {  // uncovered target variables of a collect view
-                            const int32_t *cmk = &P.idx32[op.cmask_off + 3 * k];
-                            const int pv = pat[cmk[0]], d = (j / cmk[1]) % cmk[2];
-                            if (pv != 0 && pv != 1 + d) acc = 0.0;
+                        for (int k = 0; k < op.ncmask; ++k) {  // uncovered target variables of a collect / distribute view
+                            const int32_t *cmk = &P.idx32[op.cmask_off];
+                            const int pv = pat[cmk[k]], want = cmk[op.ncmask + (int64_t)j * op.ncmask + k];
+                            if (pv != 0 && pv != want) acc = 0.0;
                         }
                         if (op.chunks > 1) {
                             part[op.pslot0 + j * op.chunks + ck] = acc;
                         } else if (op.kind == SUM_DISTRIBUTE) {
-                            S[op.dst_row + j] = S[op.aux_row + j] == 0.0 ? 0.0 : acc;  // TableDivision 0 guard
+                            S[op.dst_row + j] = (!use_flat && S[op.aux_row + j] == 0.0) ? 0.0 : acc;  // TableDivision 0 guard (the flat kernel has none)
                         } else {
                             S[op.dst_row + j] = acc;
                         }
