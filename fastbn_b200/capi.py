@@ -11,7 +11,7 @@ LIB_PATH = os.environ.get("FASTBN_B200_LIB") or os.path.join(_HERE, "libfastbn_b
 
 # every symbol include/fastbn_b200.h declares
 ABI_SYMBOLS = ["fbn_last_error", "fbn_device_count", "fbn_device_warmup", "fbn_plan_create", "fbn_plan_destroy", "fbn_plan_get_info",
-               "fbn_run", "fbn_run_device", "fbn_evaluate", "fbn_score_device",
+               "fbn_run", "fbn_run_device", "fbn_evaluate", "fbn_score_device", "fbn_score_device_static",
                "fbn_comm_unique_id", "fbn_comm_create", "fbn_comm_create_all", "fbn_reduce", "fbn_reduce_device", "fbn_comm_info",
                "fbn_comm_destroy"]
 
@@ -72,6 +72,7 @@ def load_library():
     L.fbn_run_device.argtypes = [C.c_void_p, C.c_int64] + [C.c_void_p] * 6 + [C.POINTER(Stats)]
     L.fbn_evaluate.argtypes = [C.c_void_p, C.c_int64] + [C.c_void_p] * 8 + [C.POINTER(Stats)]
     L.fbn_score_device.argtypes = [C.c_void_p, C.c_int64] + [C.c_void_p] * 6
+    L.fbn_score_device_static.argtypes = [C.c_int32, C.c_int64, C.c_int32] + [C.c_void_p] * 7
     L.fbn_comm_unique_id.argtypes = [C.c_void_p]
     L.fbn_comm_create.argtypes = [C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.POINTER(C.c_void_p)]
     L.fbn_comm_create_all.argtypes = [C.c_int32, C.c_void_p, C.POINTER(C.c_void_p)]
@@ -178,6 +179,17 @@ class Plan:
         out = np.zeros(4, np.float64)
         _check(self.L, self.L.fbn_score_device(self.h, n_cases, post_ptr, labels_ptr, golden_ptr, truths_ptr, _ptr(out), stream))
         return dict(n_correct=int(out[0]), n_total=int(out[1]), sum_mse=float(out[2]), sum_hd=float(out[3]))
+
+
+STATIC_SCORE_MAX_CASES = 65536  # FBN_STATIC_SCORE_MAX_CASES
+
+
+def score_device_static(device, n_cases, n_vars, var_offsets_ptr, post_ptr, labels_ptr, golden_ptr, truths_ptr, out4_ptr, stream=0):
+    """fbn_score_device_static: scoring without any allocation (static device scratch); every pointer is a device pointer,
+    the four results land in out4_ptr (device) in stream order."""
+    L = load_library()
+    _check(L, L.fbn_score_device_static(device, n_cases, n_vars, var_offsets_ptr, post_ptr, labels_ptr, golden_ptr, truths_ptr,
+                                        out4_ptr, stream))
 
 
 def comm_unique_id():

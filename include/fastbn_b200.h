@@ -157,6 +157,23 @@ int fbn_score_device(fbn_plan *plan, int64_t n_cases, const double *posteriors, 
                      const double *golden, const int32_t *truths, double *out4_host, void *stream);
 
 /*
+ * The scoring of fbn_score_device for callers that cannot allocate (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc). No counterpart in the reference.
+ * Needs no plan. Calls no cudaMalloc / cudaFree / allocating library routine and does not synchronise: the two kernels are
+ * enqueued on `stream` and the result {n_correct, n_total, sum_mse, sum_hd} is written to out4_device (DEVICE memory, 4 doubles).
+ * The per-case scratch that fbn_score_device allocates is a static __device__ array of FBN_STATIC_SCORE_MAX_CASES x 3 doubles
+ * (1.5 MiB, held by every GPU that loads the library until the process exits); n_cases beyond that is FBN_ERR_INVALID with a
+ * message. All calls share that array: calls that overlap on the GPU (different streams or host threads) race — serialise
+ * them. The first call on a device looks the array's device address up (cudaGetSymbolAddress): make it outside a capture.
+ * var_offsets: DEVICE array of n_vars + 1 int32 prefix sums of the variables' dims (var_offsets[n_vars] = sum_dims); the
+ * other arrays as in fbn_score_device, all device pointers on `device`.
+ */
+#define FBN_STATIC_SCORE_MAX_CASES 65536
+int fbn_score_device_static(int32_t device, int64_t n_cases, int32_t n_vars, const int32_t *var_offsets,
+                            const double *posteriors, const int32_t *labels, const double *golden, const int32_t *truths,
+                            double *out4_device, void *stream);
+
+/*
  * Multi-GPU: test cases are independent, so every GPU runs its own contiguous slice with a replicated plan and NO data-path
  * collective (reference loop src/JunctionTree.cpp:1517-1528 carries only the mse / hd accumulators between cases). The one
  * exchange step is the sum of out4 = {n_correct, n_total, sum_mse, sum_hd} over the ranks: ONE ncclAllReduce of four doubles
