@@ -10,3 +10,4 @@ for spec in "alarm 1000000" "hepar2 200000" "hepar2_50 200000" "pigs 60000" "mun
   ncu --metrics $M --clock-control none -c 400 --csv --log-file gpurun_out/${tag}_launches_$1.csv python tools/prof_run.py $1 $2 0 1 > gpurun_out/${tag}_ncu_$1.log 2>&1
   echo "$1 rc=$?"
 done
+python tools/update_traffic.py $tag gpurun_out && cp profiles/traffic.json gpurun_out/${tag}_traffic.json
