@@ -11,6 +11,7 @@
 
 #include "../../include/fastbn_b200.h"
 #include "plan.h"
+#include "resident.h"
 
 namespace fbn {
 size_t fused_smem_bytes(const DevPlan &P);
@@ -21,6 +22,9 @@ size_t flat_smem_bytes(const DevPlan &P);
 cudaError_t flat_prepare(const DevPlan &P, int smem_optin, int *blocks_per_sm);
 cudaError_t flat_launch(const DevPlan &P, int grid, double *scratch, int64_t n_cases, const int64_t *ev_off, int64_t ev_base,
                         const int32_t *ev_vars, const int32_t *ev_vals, int32_t *labels, double *post, cudaStream_t st);
+cudaError_t resident_prepare(int warps, int smem_optin);
+cudaError_t resident_launch(const ResDev &R, int warps, int grid, int64_t n_cases, const int64_t *ev_off, int64_t ev_base, const int32_t *ev_vars,
+                            const int32_t *ev_vals, int32_t *labels, double *post, cudaStream_t st);
 cudaError_t level_launch(const DevPlan &P, const std::vector<Phase> &phases, int resident, double *scratch, uint8_t *patG,
                          int64_t n_cases, const int64_t *ev_off, int64_t ev_base, const int32_t *ev_vars, const int32_t *ev_vals,
                          int32_t *labels, double *post, cudaStream_t st, int64_t *n_launch);
@@ -38,7 +42,7 @@ int fbn_set_error(int code, const std::string &msg) { return fail(code, msg); } 
 
 // Revision of the kernels' memory behaviour. bench.py attaches an ncu traffic figure (profiles/traffic.json) to a run only
 // when it was captured at the same revision: bump on every change that alters what the kernels read or write.
-static const int kKernelRev = 5;
+static const int kKernelRev = 6;
 #define CK(call)                                                                                       \
     do {                                                                                               \
         cudaError_t e__ = (call);                                                                      \
@@ -78,6 +82,9 @@ struct fbn_plan {
     double *scratch = nullptr;
     uint8_t *patG = nullptr;    // level mode: evidence pattern bytes of the resident tiles
     bool level = false;
+    bool resident = false;      // small tree run by jt_resident_kernel (tile state in shared memory, resident.h)
+    fbn::ResidentPlan rp;
+    fbn::ResDev rd;
     int launches_per_wave = 1;
     int64_t scratch_bytes = 0, plan_bytes = 0;
     cudaStream_t s_in = nullptr, s_k = nullptr, s_out = nullptr;
@@ -159,6 +166,8 @@ static cudaError_t launch_inference(fbn_plan *p, int64_t n_cases, const int64_t 
         return fbn::level_launch(p->dp, p->hp.phases, p->grid, p->scratch, p->patG, n_cases, ev_off, ev_base, ev_vars, ev_vals,
                                  labels, post, st, n_launch);
     *n_launch = 1;
+    if (p->resident)
+        return fbn::resident_launch(p->rd, p->rp.warps, p->grid, n_cases, ev_off, ev_base, ev_vars, ev_vals, labels, post, st);
     if (p->dp.flat)
         return fbn::flat_launch(p->dp, p->grid, p->scratch, n_cases, ev_off, ev_base, ev_vars, ev_vals, labels, post, st);
     return fbn::fused_launch(p->dp, p->grid, p->scratch, n_cases, ev_off, ev_base, ev_vars, ev_vals, labels, post, st);
@@ -237,7 +246,36 @@ extern "C" int fbn_plan_create(const fbn_tree_desc *tree, const fbn_plan_options
     cudaError_t ce;
     int64_t tile_bytes = (int64_t)h.tile_rows * fbn::kRowDoubles * 8;
     int64_t resident;
-    if (level) {
+    // Small trees (flat plans): when the LIVE message rows of a tile fit into one SM's shared memory the tile never touches HBM
+    // between its evidence and its posteriors (resident.h). Measured on B200 (ALARM): see DESIGN.md. FBN_NO_RESIDENT=1 keeps
+    // the one-warp-per-tile kernel with the tile state in HBM / L2.
+    if (!level && h.flat && !getenv("FBN_NO_RESIDENT")) {
+        int warps = 16;
+        if (const char *e = getenv("FBN_RES_WARPS")) warps = std::max(1, std::min(32, atoi(e)));
+        fbn::build_resident(h, warps, (int64_t)prop.sharedMemPerBlockOptin, p->rp);
+        if (p->rp.ok) {
+            const unsigned char *blob = nullptr;
+            std::vector<unsigned char> bytes((const unsigned char *)p->rp.blob.data(), (const unsigned char *)p->rp.blob.data() + p->rp.blob.size() * 4);
+            if ((rc = upload(p, bytes, &blob)) != FBN_OK) { fbn_plan_destroy(p); return rc; }
+            if ((rc = upload(p, p->rp.block_off, &p->rd.block_off)) != FBN_OK) { fbn_plan_destroy(p); return rc; }
+            if ((rc = upload(p, p->rp.lams, &p->rd.lams)) != FBN_OK) { fbn_plan_destroy(p); return rc; }
+            p->rd.n_lams = (int32_t)p->rp.lams.size();
+            p->rd.blob = blob; p->rd.vars = d.vars;
+            p->rd.n_blocks = p->rp.n_blocks; p->rd.n_vars = h.n_vars; p->rd.sum_dims = h.sum_dims; p->rd.query_var = h.query_var;
+            p->rd.L = fbn::res_smem_layout(p->rp.state_rows, h.n_vars, p->rp.max_block_bytes, p->rp.n_blocks, (int)p->rp.lams.size());
+            ce = fbn::resident_prepare(warps, (int)prop.sharedMemPerBlockOptin);
+            if (ce != cudaSuccess) {
+                fbn_plan_destroy(p);
+                return fail(FBN_ERR_CUDA, std::string("kernel setup failed (is this an sm_100 device?): ") + cudaGetErrorString(ce));
+            }
+            p->resident = true;
+        }
+    }
+    if (p->resident) {
+        tile_bytes = 512;   // no tile state in HBM
+        p->blocks_per_sm = 1;
+        resident = p->n_sms;
+    } else if (level) {
         int64_t want = kLevelResident;
         if (const char *e = getenv("FBN_LEVEL_RESIDENT")) want = std::max(1, atoi(e));
         resident = std::max<int64_t>(1, std::min<int64_t>(std::min<int64_t>(want, kLevelMaxResident), budget / tile_bytes));
@@ -333,7 +371,8 @@ extern "C" int fbn_plan_get_info(const fbn_plan *p, fbn_plan_info *o) {
     o->clique_entries = h.clique_entries; o->separator_entries = h.sep_entries; o->parent_entries = h.parent_entries;
     o->marginal_entries = h.marginal_entries; o->scratch_bytes = p->scratch_bytes; o->plan_bytes = p->plan_bytes;
     o->alg_bytes_per_case = h.alg_bytes_per_case; o->kernel_bytes_per_case = h.kernel_bytes_per_case;
-    o->flat_records = p->dp.flat;
+    o->flat_records = p->resident ? 2 : p->dp.flat;
+    if (p->resident) o->team_warps = p->rp.warps;
     o->tile_cases = fbn::kTileCases; o->view_entries = h.view_entries; o->gather_rows = h.gather_rows;
     o->kernel_rev = kKernelRev;
     return FBN_OK;

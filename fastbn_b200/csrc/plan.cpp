@@ -148,6 +148,7 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
     std::vector<int64_t> pot_off(nc + 1, 0);
     for (int c = 0; c < nc; ++c) pot_off[c + 1] = pot_off[c] + clq[c].size;
     P.clique_entries = pot_off[nc];
+    P.clique_off = pot_off;
 
     // ---- topology (MarkLevel, src/JunctionTree.cpp:137-181) ----
     std::vector<int> up_sep(nc, -1), depth(nc, -1);

@@ -170,6 +170,7 @@ struct HostPlan {
     int64_t folded_vars = 0, lambda_gathers = 0;  // uncovered (view, variable) pairs folded into pattern tables / gathered as lambda rows
     // per-variable marginal source, for tests: table index (clique c, or n_cliques + s)
     std::vector<int32_t> marg_source;
+    std::vector<int64_t> clique_off;   // [n_cliques + 1] offsets of the cliques' pristine potentials in pot[]
     double alg_bytes_per_case = 0, kernel_bytes_per_case = 0;
 };
 

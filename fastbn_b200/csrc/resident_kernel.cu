@@ -1,0 +1,389 @@
+// jt_resident_kernel: the junction-tree pipeline of SMALL trees with the whole tile state in shared memory (resident.h).
+//   One CTA per SM, persistent over tiles of 64 test cases (lane = 2 cases, 128-bit rows as everywhere, plan.h). The tile's
+//   live message rows (up messages, down ratios, 1/norm rows, unnormalised marginals) never leave shared memory; HBM sees the
+//   evidence coming in and the posteriors going out and nothing else. The constants of a phase (static per-warp work lists,
+//   per-entry records, pattern-folded potentials) arrive as ONE block per phase through cp.async.bulk + mbarrier (TMA) into a
+//   double buffer, requested one phase ahead, so the inner loop is: one broadcast LDS.128 (record), per-case LDS.64
+//   (potential under the case's evidence pattern), one LDS.128 per gathered message row, multiply-add.
+//   Same SumOps and the same arithmetic order per target as jt_flat_kernel (flat_kernel.cu): collect (reference
+//   src/JunctionTree.cpp:829-941, :1056-1148), distribute (:700-816, :1150-1238; division done algebraically), marginals
+//   (:1392-1454), Normalize (PotentialTableBase.cpp:433-445) as a 1/sum row, ArgMax (Inference.cpp:92-102).
+#include <cstdint>
+#include <type_traits>
+
+#include <cuda_runtime.h>
+
+#include "plan.h"
+#include "resident.h"
+
+namespace fbn {
+
+namespace {
+
+struct V2 {
+    double x, y;
+};
+
+__device__ __forceinline__ uint32_t lds32(uint32_t a) {
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ uint32_t lds16(uint32_t a) {
+    uint16_t v;
+    asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ uint4 lds128u(uint32_t a) {
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ double lds64(uint32_t a) {
+    double v;
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ V2 lds128(uint32_t a) {
+    V2 v;
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ void sts128(uint32_t a, V2 v) { asm volatile("st.shared.v2.f64 [%0], {%1, %2};" ::"r"(a), "d"(v.x), "d"(v.y) : "memory"); }
+
+// start the bulk copy of one constant block into a buffer; completion is counted in bytes on the buffer's mbarrier
+__device__ __forceinline__ void block_issue(uint32_t dst_s, const unsigned char *src, uint32_t bytes, uint32_t bar_s) {
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // the CTA's earlier reads of the buffer before the copy engine's write
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_s), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst_s), "l"(src), "r"(bytes),
+                 "r"(bar_s)
+                 : "memory");
+}
+__device__ __forceinline__ void block_wait(uint32_t bar_s, uint32_t parity) {
+    uint32_t done = 0;
+    while (!done) {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.b32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done)
+                     : "r"(bar_s), "r"(parity)
+                     : "memory");
+    }
+}
+
+// evidence patterns of one tile (ops.cuh: load_patterns), by ONE warp: a lane walks the pairs of its two cases (they are
+// adjacent in the CSR arrays) four at a time; pat_s must be zero. dims_s: one byte per variable.
+__device__ __forceinline__ void res_load_patterns(const ResDev &R, uint32_t pat_s, uint32_t dims_s, int64_t tile, int64_t n_cases,
+                                                  const int64_t *__restrict__ ev_off, int64_t ev_base, const int32_t *__restrict__ ev_vars,
+                                                  const int32_t *__restrict__ ev_vals, int lane) {
+    const int64_t c0 = tile * kTileCases + lane * 2;
+    if (c0 >= n_cases) return;
+    const int64_t k0 = ev_off[c0] - ev_base, kmid = ev_off[c0 + 1] - ev_base;
+    const int64_t k1 = c0 + 1 < n_cases ? ev_off[c0 + 2] - ev_base : kmid;
+    for (int64_t k = k0; k < k1; k += 4) {
+        int vv[4], ww[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int64_t kk = min(k + u, k1 - 1);
+            vv[u] = __ldg(ev_vars + kk);
+            ww[u] = __ldg(ev_vals + kk);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            if (k + u >= k1) break;
+            const int v = vv[u], val = ww[u];
+            if (v < 0 || v >= R.n_vars) continue;   // src/JunctionTree.cpp:326-331
+            uint32_t dim;
+            asm volatile("ld.shared.u8 %0, [%1];" : "=r"(dim) : "r"(dims_s + (uint32_t)v));
+            const uint32_t np = (val < 0 || val >= (int)dim) ? dim + 1 : 1 + (uint32_t)val;
+            const uint32_t a = pat_s + (uint32_t)v * kTileCases + lane * 2 + (k + u >= kmid ? 1 : 0);
+            uint32_t old;
+            asm volatile("ld.shared.u8 %0, [%1];" : "=r"(old) : "r"(a));
+            const uint32_t nw = (old == 0 || old == np) ? np : dim + 1;
+            asm volatile("st.shared.u8 [%0], %1;" ::"r"(a), "r"(nw) : "memory");
+        }
+    }
+}
+
+// lambda rows (evidence indicators 1.0 / 0.0 per state) of the variables some view gathers, from the pattern bytes `patl` of a
+// tile; the variables are dealt to the CTA's warps
+__device__ __forceinline__ void res_write_lams(uint32_t lams_s, int n_lams, uint32_t Sb, uint32_t patl, int warp, int T) {
+    for (int k = warp; k < n_lams; k += T) {
+        const uint4 l = lds128u(lams_s + 16 * k);   // variable, dim, state offset
+        const uint32_t pp = lds16(patl + l.x * kTileCases), q0 = pp & 255u, q1 = pp >> 8;
+        for (uint32_t d = 0; d < l.y; ++d) {
+            V2 x;
+            x.x = (q0 == 0 || q0 == 1 + d) ? 1.0 : 0.0;
+            x.y = (q1 == 0 || q1 == 1 + d) ? 1.0 : 0.0;
+            sts128(Sb + l.z + d * kResRowBytes, x);
+        }
+    }
+}
+
+// records per batch (all loads of a batch are issued before the first use): 16 warps x 128 registers take 4 / 2, 32 warps x 64
+// registers 2 / 1
+template <int NG, int MAXT>
+struct ResBatch {
+    static constexpr int value = MAXT <= 16 ? (NG <= 2 ? 4 : 2) : (NG <= 2 ? 2 : 1);
+};
+
+// N records from `rec` on: acc += potential(case) * product of the gathered message entries
+template <int NG, int N>
+__device__ __forceinline__ void res_batch(uint32_t rec, uint32_t pot0, uint32_t pot1, uint32_t Sb, V2 &acc) {
+    constexpr uint32_t kRec = NG > 3 ? 32u : 16u;
+    uint4 A[N], B[N];
+#pragma unroll
+    for (int b = 0; b < N; ++b) {
+        A[b] = lds128u(rec + b * kRec);
+        if (NG > 3) B[b] = lds128u(rec + b * kRec + 16);
+    }
+    double p0[N], p1[N];
+    V2 m[N][NG > 0 ? NG : 1];
+#pragma unroll
+    for (int b = 0; b < N; ++b) {
+        p0[b] = lds64(pot0 + A[b].x);
+        p1[b] = lds64(pot1 + A[b].x);
+        if (NG > 0) m[b][0] = lds128(Sb + A[b].y);
+        if (NG > 1) m[b][1] = lds128(Sb + A[b].z);
+        if (NG > 2) m[b][2] = lds128(Sb + A[b].w);
+        if (NG > 3) m[b][3] = lds128(Sb + B[b].x);
+    }
+#pragma unroll
+    for (int b = 0; b < N; ++b) {
+        double v0 = p0[b], v1 = p1[b];
+#pragma unroll
+        for (int g = 0; g < NG; ++g) { v0 *= m[b][g].x; v1 *= m[b][g].y; }
+        acc.x += v0; acc.y += v1;
+    }
+}
+
+// one SUM item: `n_targets` targets of one op, `rows` = Q * BATCH + REM records per target, target-major. REM is a template
+// parameter so that a target's records are whole batches: no per-record test for the end of a target.
+// CM: the op checks target variables against the evidence (per-target factor tables, resident.h).
+template <int NG, int BATCH, int REM, bool CM>
+__device__ __forceinline__ void res_sum(uint32_t blk, const uint4 a, const uint4 b4, uint32_t Sb, uint32_t patl) {
+    constexpr uint32_t kRec = NG > 3 ? 32u : 16u;
+    const uint32_t n_targets = a.z, q = a.w / BATCH, desc = blk + b4.y;
+    uint32_t dst = Sb + b4.x;
+    const uint32_t nfold = lds32(desc), ncm = CM ? lds32(desc + 4) : 0u;
+    uint32_t pot0 = blk, pot1 = blk;   // this lane's pattern slot of the potentials, case 0 / case 1
+    for (uint32_t k = 0; k < nfold; ++k) {
+        const uint32_t v = lds32(desc + 16 + 8 * k), st = lds32(desc + 20 + 8 * k);
+        const uint32_t pp = lds16(patl + v * kTileCases);
+        pot0 += (pp & 255u) * st;
+        pot1 += (pp >> 8) * st;
+    }
+    const uint32_t cmd = desc + 16 + ((8 * nfold + 15u) & ~15u);
+    uint32_t rec = blk + a.y, j = b4.z;
+    for (uint32_t t = 0; t < n_targets; ++t) {
+        V2 acc = {0.0, 0.0};
+        for (uint32_t i = 0; i < q; ++i) {
+            res_batch<NG, BATCH>(rec, pot0, pot1, Sb, acc);
+            rec += BATCH * kRec;
+        }
+        if constexpr (REM > 0) {
+            res_batch<NG, REM>(rec, pot0, pot1, Sb, acc);
+            rec += REM * kRec;
+        }
+        if (CM) {
+            for (uint32_t k = 0; k < ncm; ++k) {   // 1.0 / 0.0: does the case's evidence allow this target's state of the variable
+                const uint4 c = lds128u(cmd + 16 * k);   // variable, table, bytes per target
+                const uint32_t pp = lds16(patl + c.x * kTileCases), tj = blk + c.y + j * c.z;
+                acc.x *= lds64(tj + (pp & 255u) * 8);
+                acc.y *= lds64(tj + (pp >> 8) * 8);
+            }
+            ++j;
+        }
+        sts128(dst, acc);
+        dst += kResRowBytes;
+    }
+}
+
+template <int NG, int BATCH, bool CM>
+__device__ __forceinline__ void res_sum_rem(uint32_t blk, const uint4 a, const uint4 b4, uint32_t Sb, uint32_t patl) {
+    switch (a.w % BATCH) {
+        case 0: res_sum<NG, BATCH, 0, CM>(blk, a, b4, Sb, patl); break;
+        case 1: res_sum<NG, BATCH, 1 % BATCH, CM>(blk, a, b4, Sb, patl); break;
+        case 2: res_sum<NG, BATCH, 2 % BATCH, CM>(blk, a, b4, Sb, patl); break;
+        default: res_sum<NG, BATCH, 3 % BATCH, CM>(blk, a, b4, Sb, patl); break;
+    }
+}
+
+// ops with five to seven gathers per entry (cliques with more than four neighbours): plain loop
+__device__ __noinline__ void res_sum_generic(uint32_t blk, const uint4 a, const uint4 b4, uint32_t Sb, uint32_t patl, uint32_t ng) {
+    const uint32_t n_targets = a.z, rows = a.w, desc = blk + b4.y;
+    uint32_t dst = Sb + b4.x;
+    const uint32_t nfold = lds32(desc), ncm = lds32(desc + 4);
+    uint32_t pot0 = blk, pot1 = blk;
+    for (uint32_t k = 0; k < nfold; ++k) {
+        const uint32_t v = lds32(desc + 16 + 8 * k), st = lds32(desc + 20 + 8 * k);
+        const uint32_t pp = lds16(patl + v * kTileCases);
+        pot0 += (pp & 255u) * st;
+        pot1 += (pp >> 8) * st;
+    }
+    const uint32_t cmd = desc + 16 + ((8 * nfold + 15u) & ~15u);
+    uint32_t rec = blk + a.y, j = b4.z;
+    for (uint32_t t = 0; t < n_targets; ++t, ++j) {
+        V2 acc = {0.0, 0.0};
+        for (uint32_t r = 0; r < rows; ++r, rec += 32u) {
+            const uint32_t po = lds32(rec);
+            double v0 = lds64(pot0 + po), v1 = lds64(pot1 + po);
+            for (uint32_t g = 0; g < ng; ++g) {
+                const V2 m = lds128(Sb + lds32(rec + 4 + 4 * g));
+                v0 *= m.x; v1 *= m.y;
+            }
+            acc.x += v0; acc.y += v1;
+        }
+        for (uint32_t k = 0; k < ncm; ++k) {
+            const uint4 c = lds128u(cmd + 16 * k);
+            const uint32_t pp = lds16(patl + c.x * kTileCases), tj = blk + c.y + j * c.z;
+            acc.x *= lds64(tj + (pp & 255u) * 8);
+            acc.y *= lds64(tj + (pp >> 8) * 8);
+        }
+        sts128(dst, acc);
+        dst += kResRowBytes;
+    }
+}
+
+// OUT item: posteriors + label of one variable (GetProbabilitiesOneNode src/JunctionTree.cpp:1392-1454, Inference::ArgMax
+// src/Inference.cpp:92-102): normalise the unnormalised marginal rows, zeros for an observed variable
+__device__ __forceinline__ void res_out(const ResDev &R, const uint4 a, const uint4 b4, uint32_t Sb, uint32_t patl, int64_t tile, int64_t n_cases,
+                                        int lane, int32_t *__restrict__ labels, double *__restrict__ post) {
+    const uint32_t v = a.y, dim = a.z, off = a.w, mg = Sb + b4.x;   // ResItem: variable, dim, posterior column, marginal rows
+    const uint32_t pp = lds16(patl + v * kTileCases);
+    const bool obs0 = (pp & 255u) != 0, obs1 = (pp >> 8) != 0;
+    const int64_t c0 = tile * kTileCases + lane * 2;
+    const bool ok0 = c0 < n_cases, ok1 = c0 + 1 < n_cases;
+    double s0 = 0.0, s1 = 0.0;
+    for (uint32_t d = 0; d < dim; ++d) {
+        const V2 x = lds128(mg + d * kResRowBytes);
+        s0 += x.x; s1 += x.y;
+    }
+    double best0 = 0.0, best1 = 0.0;
+    int arg0 = -1, arg1 = -1;
+    double *q0 = post ? post + c0 * R.sum_dims + off : nullptr;
+    double *q1 = q0 ? q0 + R.sum_dims : nullptr;
+    for (uint32_t d = 0; d < dim; ++d) {
+        const V2 x = lds128(mg + d * kResRowBytes);
+        const double pr0 = obs0 ? 0.0 : x.x / s0, pr1 = obs1 ? 0.0 : x.y / s1;
+        if (q0 && ok0) q0[d] = pr0;
+        if (q1 && ok1) q1[d] = pr1;
+        if (pr0 > best0) { best0 = pr0; arg0 = (int)d; }
+        if (pr1 > best1) { best1 = pr1; arg1 = (int)d; }
+    }
+    if ((int)v == R.query_var && labels) {
+        if (ok0) labels[c0] = arg0;
+        if (ok1) labels[c0 + 1] = arg1;
+    }
+}
+
+}  // namespace
+
+template <int MAXT>
+__global__ void __launch_bounds__(MAXT * 32, 1) jt_resident_kernel(const ResDev R, int64_t n_cases, const int64_t *__restrict__ ev_off, int64_t ev_base,
+                                                                   const int32_t *__restrict__ ev_vars, const int32_t *__restrict__ ev_vals,
+                                                                   int32_t *__restrict__ labels, double *__restrict__ post, int64_t n_tiles) {
+    extern __shared__ __align__(128) unsigned char sm[];
+    const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(sm);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, T = blockDim.x >> 5;
+    const ResSmem L = R.L;
+    for (int v = threadIdx.x; v < R.n_vars; v += blockDim.x) sm[L.dims + v] = (unsigned char)R.vars[v].dim;
+    for (int b = threadIdx.x; b <= R.n_blocks; b += blockDim.x) reinterpret_cast<uint32_t *>(sm + L.boff)[b] = R.block_off[b];
+    for (int i = threadIdx.x; i < R.n_lams * 4; i += blockDim.x) reinterpret_cast<uint32_t *>(sm + L.lams)[i] = reinterpret_cast<const uint32_t *>(R.lams)[i];
+    const uint32_t pat_words = (L.pat1 - L.pat0) / 4;
+    for (uint32_t i = threadIdx.x; i < 2 * pat_words; i += blockDim.x) reinterpret_cast<uint32_t *>(sm + L.pat0)[i] = 0u;
+    const uint32_t bars = sbase + L.bars;
+    if (threadIdx.x == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bars));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bars + 8));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if ((int64_t)blockIdx.x >= n_tiles) return;
+    const uint32_t dims_s = sbase + L.dims;
+    const uint32_t *boff = reinterpret_cast<const uint32_t *>(sm + L.boff);
+    if (warp == 0) res_load_patterns(R, sbase + L.pat0, dims_s, blockIdx.x, n_cases, ev_off, ev_base, ev_vars, ev_vals, lane);
+    if (threadIdx.x == 0) block_issue(sbase + L.buf0, R.blob, boff[1] - boff[0], bars);
+    const uint32_t Sb = sbase + L.state + lane * 16;   // this lane's two cases of state row 0
+    if (R.n_lams) {
+        __syncthreads();
+        res_write_lams(sbase + L.lams, R.n_lams, Sb, sbase + L.pat0 + lane * 2, warp, T);
+    }
+    __syncthreads();
+
+    uint32_t g = 0;   // blocks consumed so far: buffer g & 1, mbarrier parity (g >> 1) & 1
+    int it = 0;
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+        const uint32_t pat_cur = sbase + ((it & 1) ? L.pat1 : L.pat0), pat_nxt = sbase + ((it & 1) ? L.pat0 : L.pat1);
+        const uint32_t patl = pat_cur + lane * 2;
+        const int64_t next_tile = tile + gridDim.x;
+        for (int b = 0; b < R.n_blocks; ++b, ++g) {
+            if (threadIdx.x == 0) {   // request the next block: its buffer was last read before the CTA barrier that ended block g - 1
+                const int nb = b + 1 < R.n_blocks ? b + 1 : (next_tile < n_tiles ? 0 : -1);
+                if (nb >= 0) block_issue(sbase + (((g + 1) & 1) ? L.buf1 : L.buf0), R.blob + boff[nb], boff[nb + 1] - boff[nb], bars + 8 * ((g + 1) & 1));
+            }
+            block_wait(bars + 8 * (g & 1), (g >> 1) & 1);
+            const uint32_t blk = sbase + ((g & 1) ? L.buf1 : L.buf0);
+            const uint4 hdr = lds128u(blk);   // n_items, -, items_off, bytes
+            const uint32_t i0 = lds32(blk + 16 + 4 * warp), i1 = lds32(blk + 20 + 4 * warp);
+            // the last block sums nothing: the next tile's lambda rows can be written (its patterns came in an earlier block)
+            if (R.n_lams && b == R.n_blocks - 1 && next_tile < n_tiles) res_write_lams(sbase + L.lams, R.n_lams, Sb, pat_nxt + lane * 2, warp, T);
+            for (uint32_t i = i0; i < i1; ++i) {
+                const uint32_t ia = blk + hdr.z + i * 32;
+                const uint4 a = lds128u(ia), b4 = lds128u(ia + 16);
+                const uint32_t kind = a.x & 255u, ng = a.x >> 8;
+                if (kind == RES_SUM) {
+                    switch (ng) {
+                        case 0: res_sum_rem<0, ResBatch<0, MAXT>::value, false>(blk, a, b4, Sb, patl); break;
+                        case 1: res_sum_rem<1, ResBatch<1, MAXT>::value, false>(blk, a, b4, Sb, patl); break;
+                        case 2: res_sum_rem<2, ResBatch<2, MAXT>::value, false>(blk, a, b4, Sb, patl); break;
+                        case 3: res_sum_rem<3, ResBatch<3, MAXT>::value, false>(blk, a, b4, Sb, patl); break;
+                        case 4: res_sum_rem<4, ResBatch<4, MAXT>::value, false>(blk, a, b4, Sb, patl); break;
+                        default: res_sum_generic(blk, a, b4, Sb, patl, ng); break;
+                    }
+                } else if (kind == RES_SUMC) {   // with per-target evidence checks: leaf-side views, few gathers
+                    switch (ng) {
+                        case 0: res_sum_rem<0, 2, true>(blk, a, b4, Sb, patl); break;
+                        case 1: res_sum_rem<1, 2, true>(blk, a, b4, Sb, patl); break;
+                        case 2: res_sum_rem<2, 2, true>(blk, a, b4, Sb, patl); break;
+                        case 3: res_sum_rem<3, 2, true>(blk, a, b4, Sb, patl); break;
+                        case 4: res_sum_rem<4, 2, true>(blk, a, b4, Sb, patl); break;
+                        default: res_sum_generic(blk, a, b4, Sb, patl, ng); break;
+                    }
+                } else if (kind == RES_OUT) {
+                    res_out(R, a, b4, Sb, patl, tile, n_cases, lane, labels, post);
+                } else if (next_tile < n_tiles) {   // RES_EVID: the next tile's patterns into the other pattern buffer
+                    for (uint32_t w = lane; w < pat_words; w += 32) asm volatile("st.shared.u32 [%0], %1;" ::"r"(pat_nxt + 4 * w), "r"(0u) : "memory");
+                    __syncwarp();
+                    res_load_patterns(R, pat_nxt, dims_s, next_tile, n_cases, ev_off, ev_base, ev_vars, ev_vals, lane);
+                }
+            }
+            __syncthreads();
+        }
+    }
+}
+
+// ---- launch helpers (called from capi.cu) ------------------------------------------------------------------------
+static int res_maxt(int warps) { return warps <= 8 ? 8 : (warps <= 16 ? 16 : 32); }
+
+cudaError_t resident_prepare(int warps, int smem_optin) {
+    switch (res_maxt(warps)) {
+        case 8: return cudaFuncSetAttribute(jt_resident_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin);
+        case 16: return cudaFuncSetAttribute(jt_resident_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin);
+        default: return cudaFuncSetAttribute(jt_resident_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin);
+    }
+}
+
+cudaError_t resident_launch(const ResDev &R, int warps, int grid, int64_t n_cases, const int64_t *ev_off, int64_t ev_base, const int32_t *ev_vars,
+                            const int32_t *ev_vals, int32_t *labels, double *post, cudaStream_t st) {
+    const int64_t n_tiles = (n_cases + kTileCases - 1) / kTileCases;
+    if (n_tiles == 0) return cudaSuccess;
+    if (grid > n_tiles) grid = (int)n_tiles;
+    const size_t smem = R.L.total;
+    switch (res_maxt(warps)) {
+        case 8: jt_resident_kernel<8><<<grid, warps * 32, smem, st>>>(R, n_cases, ev_off, ev_base, ev_vars, ev_vals, labels, post, n_tiles); break;
+        case 16: jt_resident_kernel<16><<<grid, warps * 32, smem, st>>>(R, n_cases, ev_off, ev_base, ev_vars, ev_vals, labels, post, n_tiles); break;
+        default: jt_resident_kernel<32><<<grid, warps * 32, smem, st>>>(R, n_cases, ev_off, ev_base, ev_vars, ev_vals, labels, post, n_tiles); break;
+    }
+    return cudaGetLastError();
+}
+
+}  // namespace fbn

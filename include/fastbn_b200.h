@@ -90,7 +90,8 @@ typedef struct fbn_plan_info {
     int64_t plan_bytes;          /* device bytes of per-tree constants */
     double alg_bytes_per_case;   /* SURVEY.md 8(d) algorithmic bytes per case (fixed-shape fp64 tables), evidence excluded */
     double kernel_bytes_per_case;/* bytes the fused kernel itself moves per case (scratch r/w + output) */
-    int32_t flat_records;        /* 1: small tree run by jt_flat_kernel (one warp per tile, per-entry records), else 0 */
+    int32_t flat_records;        /* small trees, per-entry records: 1 = jt_flat_kernel (one warp per tile, tile state in HBM / L2),
+                                    2 = jt_resident_kernel (one CTA per tile, the tile's live messages in shared memory); else 0 */
     int32_t kernel_rev;          /* revision of the kernels' memory behaviour: ncu traffic figures are valid for one revision only */
     int32_t tile_cases;          /* test cases per tile (32 lanes x cases per lane) */
     int32_t reserved;

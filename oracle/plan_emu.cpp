@@ -128,3 +128,101 @@ extern "C" int emu_run(const fbn_tree_desc *tree, int team, int64_t n_cases, con
     }
     return 0;
 }
+
+// ---- resident-tile plan (fastbn_b200/csrc/resident.h): interprets the per-phase constant blocks exactly as
+//      jt_resident_kernel does (items warp by warp), one case at a time. The state is poisoned before every case and sized to
+//      the plan's live-row high-water mark, so a wrong live range shows up in the results.
+#include "../fastbn_b200/csrc/resident.h"
+
+extern "C" int emu_run_resident(const fbn_tree_desc *tree, int warps, int64_t smem_limit, int64_t n_cases, const int64_t *ev_off,
+                                const int32_t *ev_vars, const int32_t *ev_vals, int32_t *labels, double *post, int64_t *info /* 16 */) {
+    HostPlan P;
+    g_err = build_plan(*tree, 1, P, false);
+    if (!g_err.empty()) return 1;
+    ResidentPlan R;
+    build_resident(P, warps, smem_limit, R);
+    if (info) {
+        info[0] = R.ok ? 1 : 0; info[1] = R.state_rows; info[2] = R.max_block_bytes; info[3] = R.smem_bytes; info[4] = R.n_blocks;
+        info[5] = R.n_items; info[6] = (int64_t)(R.balance * 1000); info[7] = P.tile_rows; info[8] = (int64_t)R.blob.size() * 4;
+        info[9] = (int64_t)P.pot.size();
+    }
+    if (!R.ok) { g_err = R.why; return 2; }
+    const int rowb = kResRowBytes;
+    std::vector<double> S((size_t)R.state_rows);
+    std::vector<int> pat((size_t)P.n_vars);
+    int64_t n_evid_items = 0;
+    for (int64_t cs = 0; cs < n_cases; ++cs) {
+        std::fill(S.begin(), S.end(), -12345.0);
+        std::fill(pat.begin(), pat.end(), 0);
+        for (int64_t k = ev_off[cs]; k < ev_off[cs + 1]; ++k) {
+            int v = ev_vars[k], val = ev_vals[k];
+            if (v < 0 || v >= P.n_vars) continue;
+            const int dim = P.vars[v].dim;
+            const int np = (val < 0 || val >= dim) ? dim + 1 : 1 + val;
+            pat[v] = (pat[v] == 0 || pat[v] == np) ? np : dim + 1;
+        }
+        std::vector<char> seen((size_t)P.n_vars, 0);
+        for (const ResLam &l : R.lams)
+            for (uint32_t d = 0; d < l.dim; ++d) S[l.state_off / rowb + d] = (pat[l.var] == 0 || pat[l.var] == (int)(1 + d)) ? 1.0 : 0.0;
+        for (int b = 0; b < R.n_blocks; ++b) {
+            const uint32_t *blk = R.blob.data() + R.block_off[(size_t)b] / 4;
+            const unsigned char *bytes = reinterpret_cast<const unsigned char *>(blk);
+            if (blk[3] != R.block_off[(size_t)b + 1] - R.block_off[(size_t)b]) { g_err = "block size mismatch"; return 3; }
+            const ResItem *items = reinterpret_cast<const ResItem *>(bytes + blk[2]);
+            // a block's items run concurrently on the GPU: none may read what another one of the same block writes. Writes go
+            // to a copy that replaces the state at the block's barrier.
+            std::vector<double> W(S);
+            for (int w = 0; w < warps; ++w)
+                for (uint32_t it = blk[4 + w]; it < blk[4 + w + 1]; ++it) {
+                    const ResItem &I = items[it];
+                    const uint32_t kind = I.kind_ng & 255u, ng = I.kind_ng >> 8;
+                    if (kind == RES_EVID) { if (cs == 0) ++n_evid_items; continue; }
+                    if (kind != RES_OUT && kind != RES_SUM && kind != RES_SUMC) { g_err = "unknown item kind"; return 6; }
+                    if (kind == RES_OUT) {
+                        const int v = (int)I.rec_off, dim = (int)I.n_targets, off = (int)I.rows;
+                        const double *mg = &S[I.dst_off / rowb];
+                        double sum = 0.0;
+                        for (int d = 0; d < dim; ++d) sum += mg[d];
+                        double best = 0.0;
+                        int arg = -1;
+                        for (int d = 0; d < dim; ++d) {
+                            double pr = pat[v] ? 0.0 : mg[d] / sum;
+                            if (post) post[cs * P.sum_dims + off + d] = pr;
+                            if (pr > best) { best = pr; arg = d; }
+                        }
+                        if (v == P.query_var && labels) labels[cs] = arg;
+                        seen[(size_t)v] = 1;
+                        continue;
+                    }
+                    const uint32_t *fd = reinterpret_cast<const uint32_t *>(bytes + I.desc_off);
+                    uint32_t fx = 0;
+                    for (uint32_t k = 0; k < fd[0]; ++k) fx += (uint32_t)pat[fd[4 + 2 * k]] * fd[5 + 2 * k];
+                    const uint32_t ncm = fd[1], *cm = fd + 4 + ((2 * fd[0] + 3) & ~3u);
+                    if ((ncm != 0) != (kind == RES_SUMC)) { g_err = "item kind does not match the op's checks"; return 7; }
+                    const uint32_t stride = ng > 3 ? 8 : 4;
+                    const uint32_t *rec = reinterpret_cast<const uint32_t *>(bytes + I.rec_off);
+                    for (uint32_t j = 0; j < I.n_targets; ++j) {
+                        double acc = 0.0;
+                        for (uint32_t r = 0; r < I.rows; ++r) {
+                            const uint32_t *q = rec + ((size_t)j * I.rows + r) * stride;
+                            double v;
+                            memcpy(&v, bytes + q[0] + fx, 8);
+                            for (uint32_t g = 0; g < ng; ++g) v *= S[q[1 + g] / rowb];
+                            acc += v;
+                        }
+                        for (uint32_t k = 0; k < ncm; ++k) {   // per-target factor tables [target][pattern]
+                            double f;
+                            memcpy(&f, bytes + cm[4 * k + 1] + (size_t)(I.j0 + j) * cm[4 * k + 2] + (size_t)pat[cm[4 * k]] * 8, 8);
+                            acc *= f;
+                        }
+                        W[I.dst_off / rowb + j] = acc;
+                    }
+                }
+            S.swap(W);
+        }
+        for (int v = 0; v < P.n_vars; ++v)
+            if (!seen[(size_t)v]) { g_err = "variable without an OUT item"; return 4; }
+    }
+    if (n_cases > 0 && n_evid_items != 1) { g_err = "schedule must hold exactly one EVID item"; return 5; }
+    return 0;
+}

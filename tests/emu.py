@@ -45,3 +45,24 @@ def run(t, team, ev_off, ev_vars, ev_vals):
     if rc:
         raise ValueError(L.emu_last_error().decode())
     return post, lab, info
+
+
+def run_resident(t, warps, ev_off, ev_vars, ev_vals, smem_limit=232448):
+    """The resident-tile plan (fastbn_b200/csrc/resident.h) of tree t interpreted on the CPU.
+    Returns (post, labels, info) or raises ValueError(message): info = [ok, state_rows, max_block_bytes, smem_bytes, n_blocks,
+    n_items, balance * 1000, flat tile_rows, constant bytes]."""
+    L = _lib()
+    d, keep = tree_desc(t)
+    n = len(ev_off) - 1
+    sd = int(np.sum(t["var_dims"]))
+    post = np.zeros((n, sd))
+    lab = np.zeros(n, np.int32)
+    info = np.zeros(16, np.int64)
+    eo = np.ascontiguousarray(ev_off, np.int64)
+    ev = np.ascontiguousarray(ev_vars, np.int32)
+    ew = np.ascontiguousarray(ev_vals, np.int32)
+    p = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+    rc = L.emu_run_resident(C.byref(d), warps, C.c_int64(smem_limit), C.c_int64(n), p(eo), p(ev), p(ew), p(lab), p(post), p(info))
+    if rc:
+        raise ValueError(L.emu_last_error().decode())
+    return post, lab, info

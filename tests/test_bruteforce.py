@@ -89,14 +89,22 @@ def test_oracle_agrees_with_joint_enumeration(tmp_path, spec):
     for team in (1, 4, -8):
         post2, lab2, _ = emu.run(tree, team, ev_off, ev_vars, ev_vals)
         assert np.max(np.abs(post2 - want)) <= 1e-12 and np.array_equal(lab2, lab)
+    post2, lab2, _ = emu.run_resident(tree, 16, ev_off, ev_vars, ev_vals)  # the resident-tile plan (shared-memory state)
+    assert np.max(np.abs(post2 - want)) <= 1e-12 and np.array_equal(lab2, lab)
 
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("spec", NETS)
 def test_cuda_path_agrees_with_joint_enumeration(tmp_path, spec):
     tree, ev_off, ev_vars, ev_vals, want = small_case(tmp_path, spec, n_cases=200)
-    for kw in (dict(), dict(team_warps=4), dict(team_warps=8, mode=capi.MODE_LEVEL)):  # flat, fused and level kernels
-        p = capi.Plan(tree, device=0, **kw)
+    import os
+    for kw in (dict(), dict(flat=True), dict(team_warps=4), dict(team_warps=8, mode=capi.MODE_LEVEL)):  # resident, flat, fused and level kernels
+        if kw.pop("flat", False):
+            os.environ["FBN_NO_RESIDENT"] = "1"
+        try:
+            p = capi.Plan(tree, device=0, **kw)
+        finally:
+            os.environ.pop("FBN_NO_RESIDENT", None)
         labels, post, _ = p.run(ev_off, ev_vars, ev_vals)
         p.close()
         assert np.max(np.abs(post - want)) <= 1e-12, kw

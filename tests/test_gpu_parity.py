@@ -199,3 +199,45 @@ def test_lambda_gather_path(alarm_tree, team, mode, max_fx, monkeypatch):
         assert np.array_equal(np.isnan(post), np.isnan(g["post"]))
         assert np.nanmax(np.abs(post - g["post"])) <= TOL and np.array_equal(labels, g["labels"])
     p.close()
+
+
+@pytest.mark.parametrize("warps", ["8", "16", "32"])
+def test_resident_kernel_many_waves_against_oracle(alarm_tree, warps, monkeypatch):
+    """jt_resident_kernel (tile state in shared memory, constants by cp.async.bulk, one CTA per SM): 30 001 cases = more than three
+    waves of tiles per CTA plus a ragged last tile, ragged evidence (0..12 pairs per case), EVERY case against the CPU oracle, so
+    that the pattern double buffer, the next-tile evidence item and the mbarrier phases of later tiles are checked too"""
+    monkeypatch.setenv("FBN_RES_WARPS", warps)
+    p = capi.Plan(alarm_tree, device=0)
+    assert p.info.flat_records == 2 and p.info.team_warps == int(warps)
+    n = 30001
+    rng = np.random.default_rng(5)
+    counts = rng.integers(0, 13, n)
+    off = np.concatenate([[0], np.cumsum(counts)]).astype(np.int64)
+    nv = len(alarm_tree["var_dims"])
+    ev = rng.integers(0, nv, off[-1]).astype(np.int32)
+    ew = (rng.random(off[-1]) * alarm_tree["var_dims"][ev]).astype(np.int32)
+    labels, post, _ = p.run(off, ev, ew)
+    p.close()
+    o = jtoracle.Oracle(alarm_tree)
+    want, wlab = o.run_batch(off, ev, ew)
+    o.close()
+    assert np.array_equal(np.isnan(post), np.isnan(want))
+    assert np.nanmax(np.abs(post - want)) <= TOL and np.array_equal(labels, wlab)
+
+
+def test_resident_and_flat_kernels_agree(alarm_tree, monkeypatch):
+    """FBN_NO_RESIDENT=1 keeps the one-warp-per-tile kernel (tile state in HBM / L2): same fixtures, and both kernels within 1e-12
+    of each other (they differ only in where Normalize is applied)"""
+    g = load_golden("alarm_synth_4k_ref")
+    p = capi.Plan(alarm_tree, device=0)
+    assert p.info.flat_records == 2
+    l1, p1, _ = p.run(g["ev_off"], g["ev_vars"], g["ev_vals"])
+    p.close()
+    monkeypatch.setenv("FBN_NO_RESIDENT", "1")
+    p = capi.Plan(alarm_tree, device=0)
+    assert p.info.flat_records == 1
+    l2, p2, _ = p.run(g["ev_off"], g["ev_vars"], g["ev_vals"])
+    p.close()
+    for lab, post in ((l1, p1), (l2, p2)):
+        assert np.nanmax(np.abs(post - g["post"])) <= TOL and np.array_equal(lab, g["labels"])
+    assert np.nanmax(np.abs(p1 - p2)) <= 1e-12

@@ -11,6 +11,7 @@ import pytest
 import emu
 from conftest import ROOT, load_golden
 from fastbn_b200 import capi
+from oracle import jtoracle
 
 
 @pytest.mark.parametrize("team", [1, 2, 8, 32])
@@ -185,3 +186,45 @@ def test_folded_and_gathered_evidence_agree(alarm_tree, team, max_fx, monkeypatc
     ew = np.concatenate([g["ev_vals"][g["ev_off"][i]:g["ev_off"][i + 1]] for i in idx])
     post, lab, _ = emu.run(t, team, off, ev, ew)
     assert np.nanmax(np.abs(post - g["post"][idx])) <= 1e-9 and np.array_equal(lab, g["labels"][idx])
+
+
+# ---- resident-tile plan (fastbn_b200/csrc/resident.cpp), interpreted block by block like jt_resident_kernel ----
+@pytest.mark.parametrize("warps", [1, 8, 16, 32])
+def test_resident_plan_reproduces_reference(alarm_tree, warps):
+    """live-range row allocation (the emulator's state has only the plan's live rows and is poisoned per case), static per-warp
+    schedule, Normalize left to the final marginals, per-target factor tables: reference fixtures incl. the NaN patterns"""
+    for name in ["alarm_1k_ref", "alarm_edge_ref"]:
+        g = load_golden(name)
+        post, lab, info = emu.run_resident(alarm_tree, warps, g["ev_off"], g["ev_vars"], g["ev_vals"])
+        assert np.array_equal(np.isnan(post), np.isnan(g["post"]))
+        assert np.nanmax(np.abs(post - g["post"])) <= 1e-9
+        assert np.array_equal(lab, g["labels"])
+        assert info[0] == 1 and info[1] < info[7] // 2   # ALARM: 775 scratch rows -> fewer than half live at once
+        assert info[3] <= 232448   # fits one SM's shared memory
+
+
+@pytest.mark.parametrize("max_fx", ["1", "8"])
+def test_resident_plan_with_lambda_rows(alarm_tree, max_fx, monkeypatch):
+    """views that gather evidence indicators (pattern tables capped by FBN_MAX_FX): lambda rows keep state rows for good"""
+    monkeypatch.setenv("FBN_MAX_FX", max_fx)
+    for name in ["alarm_1k_ref", "alarm_edge_ref"]:
+        g = load_golden(name)
+        post, lab, info = emu.run_resident(alarm_tree, 16, g["ev_off"], g["ev_vars"], g["ev_vals"])
+        assert np.array_equal(np.isnan(post), np.isnan(g["post"]))
+        assert np.nanmax(np.abs(post - g["post"])) <= 1e-9 and np.array_equal(lab, g["labels"])
+
+
+def test_resident_plan_odd_evidence_and_eligibility(alarm_tree):
+    off, ev, ew = _odd_evidence()
+    o = jtoracle.Oracle(alarm_tree)
+    want, wlab = o.run_batch(off, ev, ew)
+    o.close()
+    post, lab, _ = emu.run_resident(alarm_tree, 16, off, ev, ew)
+    assert np.array_equal(np.isnan(post), np.isnan(want))
+    assert np.nanmax(np.abs(post - want)) <= 1e-9 and np.array_equal(lab, wlab)
+    with pytest.raises(ValueError, match="shared memory"):   # a device with less shared memory: not eligible, the flat kernel runs the tree
+        emu.run_resident(alarm_tree, 16, off, ev, ew, smem_limit=100000)
+    t = dict(alarm_tree)
+    t["clique_potentials"] = alarm_tree["clique_potentials"] * 1e-40   # unnormalised messages could underflow: not eligible
+    with pytest.raises(ValueError, match="range of a double"):
+        emu.run_resident(t, 16, off, ev, ew)

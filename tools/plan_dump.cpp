@@ -1,5 +1,6 @@
-// Developer tool: prints the phase structure of a fused / level plan (ops, units, entries per phase, per-warp balance).
+// Developer tool: prints the structure of a plan (row regions, constants, ops per phase, entries, live message rows).
 // Build: g++ -O2 -std=c++17 -I include -I fastbn_b200/csrc tools/plan_dump.cpp fastbn_b200/csrc/plan.cpp -shared -fPIC -o build/tools/libplan_dump.so
+// Use:   python tools/plan_dump.py <workload> [team] [level]
 #include <algorithm>
 #include <cstdio>
 #include <vector>
@@ -11,47 +12,65 @@ extern "C" int plan_dump(const fbn_tree_desc *tree, int team, int level, int ver
     fbn::HostPlan h;
     std::string err = fbn::build_plan(*tree, team, h, level != 0);
     if (!err.empty()) { fprintf(stderr, "%s\n", err.c_str()); return 1; }
-    printf("team %d cb %d phases %zu tile_rows %d clique_entries %lld smem: mask_words %d normslots %d pslots %d\n", h.team, h.cb,
-           h.phases.size(), h.tile_rows, (long long)h.clique_entries, h.max_mask_words, h.max_normslots, h.max_pslots);
-    double tot = 0, totmax = 0;
+    printf("team %d cb %d flat %d phases %zu ops %zu tile_rows %d (mup %d dn %d inv %d mg %d lam %d part %d normpart %d)\n", h.team, h.cb, (int)h.flat,
+           h.phases.size(), h.ops.size(), h.tile_rows, h.mup_row0, h.dn_row0, h.inv_row0, h.mg_row0, h.lam_row0, h.part_row0, h.normpart_row0);
+    printf("cliques %d seps %d vars %d sum_dims %d clique_entries %lld sep_entries %lld view_entries %lld gather_rows %lld\n", h.n_cliques, h.n_seps,
+           h.n_vars, h.sum_dims, (long long)h.clique_entries, (long long)h.sep_entries, (long long)h.view_entries, (long long)h.gather_rows);
+    printf("constants: pot %zu doubles (%.1f KB) idx32 %zu (%.1f KB) flatc %zu (%.1f KB) lamvars %zu\n", h.pot.size(), h.pot.size() * 8 / 1024.0,
+           h.idx32.size(), h.idx32.size() * 4 / 1024.0, h.flatc.size(), h.flatc.size() * 4 / 1024.0, h.lamvars.size());
     for (size_t pi = 0; pi < h.phases.size(); ++pi) {
         const fbn::Phase &p = h.phases[pi];
-        std::vector<double> w(h.team, 0.0);
-        double entries = 0;
-        int units = 0, maxop = 0;
+        long long entries = 0, maxop = 0, targets = 0;
+        int nk[3] = {0, 0, 0};
         for (int oi = p.op_begin; oi < p.op_end; ++oi) {
-            int id = h.oplist[oi];
-            if (p.kind == 0) {
-                const fbn::CollectOp &op = h.cops[id];
-                int nu = (op.cols + h.cb - 1) / h.cb * op.chunks;
-                for (int u = 0; u < nu; ++u) {
-                    int ck = u % op.chunks;
-                    int r0 = ck * op.rows_per_chunk, r1 = std::min(op.rows, r0 + op.rows_per_chunk);
-                    double e = (double)(r1 - r0) * std::min(h.cb, op.cols) * (1 + op.nchild);
-                    w[(u + op.rot) % h.team] += e;
-                    entries += e;
-                }
-                units += nu;
-                maxop = std::max(maxop, op.rows * op.cols);
-            } else if (id >= 0) {
-                const fbn::PullOp &op = h.pops[id];
-                int nu = (op.nT + h.cb - 1) / h.cb * op.chunks;
-                for (int u = 0; u < nu; ++u) {
-                    int ck = u % op.chunks;
-                    int r0 = ck * op.rows_per_chunk, r1 = std::min(op.nR, r0 + op.rows_per_chunk);
-                    double e = (double)(r1 - r0) * std::min(h.cb, op.nT) * 2;
-                    w[(u + op.rot) % h.team] += e;
-                    entries += e;
-                }
-                units += nu;
-                maxop = std::max(maxop, op.nT * op.nR);
-            }
+            const fbn::SumOp &op = h.ops[h.oplist[oi]];
+            entries += (long long)op.rows * op.cols;
+            maxop = std::max(maxop, (long long)op.rows * op.cols);
+            targets += op.cols;
+            nk[op.kind]++;
+            if (verbose > 1)
+                printf("    op %3d kind %d rows %5d cols %4d ng %d nfx %3d nfold %d ncmask %d ninv %d chunks %d dst %d\n", h.oplist[oi], op.kind, op.rows, op.cols,
+                       op.ng, op.nfx, op.nfold, op.ncmask, op.ninv, op.chunks, op.dst_row);
         }
-        double mx = *std::max_element(w.begin(), w.end());
-        tot += entries; totmax += mx * h.team;
-        if (verbose) printf("ph %3zu kind %d ops %3d units %5d fins %3d loads %9.0f max/warp %8.0f eff %.2f maxop %d\n", pi, p.kind, p.op_end - p.op_begin, units,
-               p.fin_end - p.fin_begin, entries, mx, entries / (mx * h.team + 1e-9), maxop);
+        if (verbose)
+            printf("ph %3zu kind %d ops %3d (collect %d distribute %d marginal %d) targets %4lld entries %7lld maxop %6lld units %d fins %d\n", pi, p.kind,
+                   p.op_end - p.op_begin, nk[0], nk[1], nk[2], targets, entries, maxop, p.n_units, p.fin_end - p.fin_begin);
     }
-    printf("total loads %.0f  sum(max*team) %.0f  balance efficiency %.3f\n", tot, totmax, tot / totmax);
+    return 0;
+}
+
+#include "resident.h"
+// resident-tile schedule of the tree: per block the work of every warp in model instructions
+extern "C" int resident_dump(const fbn_tree_desc *tree, int warps, int verbose) {
+    fbn::HostPlan h;
+    std::string err = fbn::build_plan(*tree, 1, h, false);
+    if (!err.empty()) { fprintf(stderr, "%s\n", err.c_str()); return 1; }
+    if (verbose > 1)
+        for (size_t o = 0; o < h.ops.size(); ++o) {
+            const fbn::SumOp &op = h.ops[o];
+            printf("    op %3zu kind %d rows %5d cols %4d ng %d nfx %3d nfold %d ncmask %d\n", o, op.kind, op.rows, op.cols, op.ng, op.nfx, op.nfold, op.ncmask);
+        }
+    fbn::ResidentPlan R;
+    fbn::build_resident(h, warps, 232448, R);
+    printf("resident: ok %d (%s) warps %d blocks %d state_rows %d (%.1f KB) max_block %d B smem %lld B items %d balance %.3f constants %.1f KB pot %.1f KB\n", (int)R.ok,
+           R.why.c_str(), R.warps, R.n_blocks, R.state_rows, R.state_rows * 0.5, R.max_block_bytes, (long long)R.smem_bytes, R.n_items, R.balance,
+           R.blob.size() * 4 / 1024.0, h.pot.size() * 8 / 1024.0);
+    if (!R.ok) return 2;
+    for (int b = 0; b < R.n_blocks && verbose; ++b) {
+        const uint32_t *blk = R.blob.data() + R.block_off[b] / 4;
+        const fbn::ResItem *items = reinterpret_cast<const fbn::ResItem *>(reinterpret_cast<const unsigned char *>(blk) + blk[2]);
+        printf("block %2d bytes %6u items %3u | entries per warp:", b, blk[3], blk[0]);
+        for (int w = 0; w < warps; ++w) {
+            unsigned e = 0, n = 0;
+            for (uint32_t i = blk[4 + w]; i < blk[4 + w + 1]; ++i) {
+                if ((items[i].kind_ng & 255) == fbn::RES_SUM || (items[i].kind_ng & 255) == fbn::RES_SUMC) e += items[i].n_targets * items[i].rows;
+                else if ((items[i].kind_ng & 255) == fbn::RES_OUT) e += 1000;
+                else e += 50000;
+                ++n;
+            }
+            printf(" %u/%u", e, n);
+        }
+        printf("\n");
+    }
     return 0;
 }
