@@ -260,6 +260,13 @@ extern "C" int fbn_plan_create(const fbn_tree_desc *tree, const fbn_plan_options
             if ((rc = upload(p, p->rp.block_off, &p->rd.block_off)) != FBN_OK) { fbn_plan_destroy(p); return rc; }
             if ((rc = upload(p, p->rp.lams, &p->rd.lams)) != FBN_OK) { fbn_plan_destroy(p); return rc; }
             p->rd.n_lams = (int32_t)p->rp.lams.size();
+            p->rd.clk = nullptr;
+            if (getenv("FBN_RES_CLOCK")) {   // developer knob: cycles per block of CTA 0, printed when the plan is destroyed
+                std::vector<long long> z(4 * 2048 + 4, 0);
+                const long long *dz = nullptr;
+                if ((rc = upload(p, z, &dz)) != FBN_OK) { fbn_plan_destroy(p); return rc; }
+                p->rd.clk = const_cast<long long *>(dz);
+            }
             p->rd.blob = blob; p->rd.vars = d.vars;
             p->rd.n_blocks = p->rp.n_blocks; p->rd.n_vars = h.n_vars; p->rd.sum_dims = h.sum_dims; p->rd.query_var = h.query_var;
             p->rd.L = fbn::res_smem_layout(p->rp.state_rows, h.n_vars, p->rp.max_block_bytes, p->rp.n_blocks, (int)p->rp.lams.size());
@@ -346,6 +353,28 @@ extern "C" void fbn_plan_destroy(fbn_plan *p) {
     DeviceGuard guard;
     cudaSetDevice(p->device);
     cudaDeviceSynchronize();
+    if (p->resident && p->rd.clk) {
+        std::vector<long long> c(4 * 2048);
+        const int nb = p->rp.n_blocks;
+        if (cudaMemcpy(c.data(), p->rd.clk, c.size() * 8, cudaMemcpyDeviceToHost) == cudaSuccess && c[4 * (size_t)nb] != 0) {
+            // tiles 1.. of CTA 0 (the first one includes the start-up), thread 0: cycles for requesting the next block + waiting
+            // for this one, for warp 0's items, at the CTA barrier
+            const int tiles = std::min(2048 / nb - 1, 40);
+            fprintf(stderr, "FBN_RES_CLOCK (CTA 0, warp 0, mean over tiles 1..%d): block: issue+wait / items / barrier cycles\n", tiles - 1);
+            double tot = 0;
+            for (int b = 0; b < nb; ++b) {
+                double w = 0, it = 0, br = 0;
+                int n = 0;
+                for (int k = 1; k < tiles; ++k) {
+                    const size_t g = (size_t)k * nb + b;
+                    if (c[4 * g + 4] == 0) break;
+                    w += (double)(c[4 * g + 1] - c[4 * g]); it += (double)(c[4 * g + 2] - c[4 * g + 1]); br += (double)(c[4 * g + 4] - c[4 * g + 2]); ++n;
+                }
+                if (n) { fprintf(stderr, "  block %2d: %6.0f / %6.0f / %6.0f\n", b, w / n, it / n, br / n); tot += (w + it + br) / n; }
+            }
+            fprintf(stderr, "  tile: %.0f cycles\n", tot);
+        }
+    }
     for (void *d : p->dev_allocs) cudaFree(d);
     cudaFree(p->scratch);
     cudaFree(p->patG);

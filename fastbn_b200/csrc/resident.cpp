@@ -29,12 +29,13 @@ struct Piece {
 
 // instruction-count model of the kernel's loops (two cases per lane): only the ratios matter
 double sum_piece_cost(const SumOp &op, int targets) {
-    const double setup = 60.0 + 12.0 * op.nfold + 10.0 * op.ncmask;
-    const double per_target = 8.0 + 12.0 * op.ncmask;
-    const double per_entry = 5.0 + 4.0 * op.ng + (op.ng > 3 ? 1.0 : 0.0);
+    // measured on B200 (ncu, ALARM): ~100 instructions per item, ~20 per record with two gathers, ~10 per checked target variable
+    const double setup = 100.0 + 12.0 * op.nfold + 6.0 * op.ncmask;
+    const double per_target = 8.0 + 10.0 * op.ncmask;
+    const double per_entry = 10.0 + 5.0 * op.ng + (op.ng > 3 ? 1.0 : 0.0);
     return setup + targets * (per_target + per_entry * op.rows);
 }
-double out_cost(int dim) { return 60.0 + 70.0 * dim; }
+double out_cost(int dim) { return 180.0 + 20.0 * dim; }
 constexpr double kEvidCost = 1200.0;
 
 }  // namespace
@@ -89,6 +90,7 @@ void build_resident(const HostPlan &P, int warps, int64_t smem_limit, ResidentPl
         const SumOp &op = P.ops[o];
         if (op_phase[o] < 0) return fail("op outside every phase");
         if (op.chunks != 1 || op.ng > 7 || op.flat_off < 0) return fail("op without flat records");
+        if (op.ncmask > kResMaxChecks) return fail("view checks more than " + std::to_string(kResMaxChecks) + " target variables against the evidence");
         for (int r = op.dst_row; r < op.dst_row + op.cols; ++r) {
             if (r < 0 || r >= P.tile_rows || row2obj[(size_t)r] != -1) return fail("two ops write one row");
             row2obj[(size_t)r] = (int)objs.size();
@@ -250,7 +252,7 @@ void build_resident(const HostPlan &P, int warps, int64_t smem_limit, ResidentPl
         std::map<int, uint32_t> desc_off, rec_off, pot_off, tab_off;
         for (int o : bops) {
             desc_off[o] = cur;
-            cur += (4u + ((2u * (uint32_t)P.ops[(size_t)o].nfold + 3u) & ~3u) + 4u * (uint32_t)P.ops[(size_t)o].ncmask) * 4u;
+            cur += ((4u + 2u * (uint32_t)P.ops[(size_t)o].nfold + (uint32_t)P.ops[(size_t)o].ncmask + 3u) & ~3u) * 4u;
         }
         for (int o : bops) {
             const SumOp &op = P.ops[(size_t)o];
@@ -265,12 +267,10 @@ void build_resident(const HostPlan &P, int warps, int64_t smem_limit, ResidentPl
             pot_off[o] = cur;
             cur += (((uint32_t)op.rows * (uint32_t)op.cols * (uint32_t)op.nfx * 8u) + 15u) & ~15u;
         }
-        for (int o : bops) {   // factor tables of the checked target variables, one after the other
+        for (int o : bops) {   // per target: the pattern byte it wants of every checked variable
             const SumOp &op = P.ops[(size_t)o];
             tab_off[o] = cur;
-            for (int k = 0; k < op.ncmask; ++k)
-                cur += (uint32_t)op.cols * (uint32_t)(P.vars[(size_t)P.idx32[(size_t)(op.cmask_off + k)]].dim + 2) * 8u;
-            cur = (cur + 15u) & ~15u;
+            cur += (((uint32_t)op.cols * (uint32_t)op.ncmask * 4u) + 15u) & ~15u;
         }
         const uint32_t block_bytes = cur;
         if (block_bytes >= (1u << 20)) return fail("constant block of a phase exceeds the mbarrier transaction range");
@@ -316,20 +316,10 @@ void build_resident(const HostPlan &P, int warps, int64_t smem_limit, ResidentPl
                 d[4 + 2 * i] = (uint32_t)P.idx32[(size_t)(op.fold_off + 2 * i)];
                 d[5 + 2 * i] = (uint32_t)P.idx32[(size_t)(op.fold_off + 2 * i + 1)] * 8u;
             }
-            {
-                uint32_t at = tab_off[o];
-                for (int k = 0; k < op.ncmask; ++k) {
-                    const int v = P.idx32[(size_t)(op.cmask_off + k)], np = P.vars[(size_t)v].dim + 2;
-                    uint32_t *c = d + 4 + ((2 * op.nfold + 3) & ~3) + 4 * k;   // 16-byte aligned
-                    c[0] = (uint32_t)v; c[1] = at; c[2] = (uint32_t)np * 8u; c[3] = 0;
-                    double *tab = reinterpret_cast<double *>(blk.data() + at / 4);
-                    for (int j = 0; j < op.cols; ++j) {
-                        const int want = P.idx32[(size_t)(op.cmask_off + op.ncmask + (int64_t)j * op.ncmask + k)];
-                        for (int pt = 0; pt < np; ++pt) tab[(size_t)j * np + pt] = (pt == 0 || pt == want) ? 1.0 : 0.0;
-                    }
-                    at += (uint32_t)op.cols * (uint32_t)np * 8u;
-                }
-            }
+            d[2] = tab_off[o];
+            for (int k = 0; k < op.ncmask; ++k) d[4 + 2 * op.nfold + k] = (uint32_t)P.idx32[(size_t)(op.cmask_off + k)];
+            for (int64_t i = 0; i < (int64_t)op.cols * op.ncmask; ++i)
+                blk[(size_t)(tab_off[o] / 4 + i)] = (uint32_t)P.idx32[(size_t)(op.cmask_off + op.ncmask + i)];
             uint32_t *rec = blk.data() + rec_off[o] / 4;
             const int stride = op.ng > 3 ? 8 : 4;
             for (int64_t e = 0; e < (int64_t)op.rows * op.cols; ++e) {

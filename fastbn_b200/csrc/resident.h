@@ -5,7 +5,8 @@
 // the previous phase is computed.
 //
 // Built from a FLAT plan (plan.h, team 1: one record per view entry) by build_resident():
-//   * the per-target evidence checks of a view (cmask, plan.h) become small factor tables [target][pattern] of 1.0 / 0.0;
+//   * the per-target evidence checks of a view (cmask, plan.h: at most kResMaxChecks variables) read the case's pattern bytes
+//     once per item, not per target;
 //   * Normalize (PotentialTableBase.cpp:433-445) is left to the final marginals: a bound over the cliques' potentials shows
 //     that no message can leave the range of a double (else the tree is not eligible and the flat kernel runs it), so there
 //     are no 1/norm rows, no scaling and no second barrier per collect level; ops nobody reads (the root's collect) are dropped;
@@ -31,13 +32,11 @@ enum ResItemKind : uint32_t { RES_SUM = 0, RES_OUT = 1, RES_EVID = 2, RES_SUMC =
 //   [0] n_items  [1] 0  [2] items_off  [3] block_bytes
 //   [4 .. 4 + warps]  warp_begin[w]: first item of warp w (items of a warp are adjacent), warp_begin[warps] = n_items
 //   items    : ResItem (32 B each)
-//   descs    : per op {nfold, ncm, 0, 0} + nfold x {variable, pattern stride in BYTES} (padded to 16 bytes) + ncm x {variable,
-//              table offset, bytes per target, 0}
+//   descs    : per op {nfold, ncm, want_off, 0} + nfold x {variable, pattern stride in BYTES} + ncm checked target variables,
+//              padded to 16 bytes; want_off -> cols x ncm words: the pattern byte (1 + state) target j has of checked variable k
 //   records  : per entry, target-major: int4 {pot_off, state offsets of gathers 0..2} (+ int4 {gathers 3..6} when the op has
 //              more than 3 gathers)
 //   pots     : doubles (nfx per entry), 16-byte aligned per op
-//   tables   : per op and checked target variable: doubles [target][pattern 0 .. dim + 1]: 1.0 where the pattern allows the
-//              target's state of the variable, else 0.0 (the finished sum is multiplied by it)
 struct ResItem {
     uint32_t kind_ng;    // kind | ng << 8
     uint32_t rec_off;    // SUM: first record.                     OUT: variable
@@ -49,6 +48,7 @@ struct ResItem {
     uint32_t pad1;
 };
 
+constexpr int kResMaxChecks = 3;   // checked target variables per op the kernel keeps in registers
 constexpr int kResRowBytes = kRowDoubles * 8;   // bytes of one state row (64 cases)
 
 // lambda rows of one variable (evidence indicators 1.0 / 0.0 per state, gathered like a message by the views that could not
@@ -103,6 +103,7 @@ struct ResDev {
     const uint32_t *block_off;     // [n_blocks + 1]
     const VarInfo *vars;
     const ResLam *lams;
+    long long *clk;                // developer knob FBN_RES_CLOCK: CTA 0 records clock64() at every block boundary of its first tiles
     int32_t n_blocks, n_vars, sum_dims, query_var, n_lams;
     ResSmem L;
 };

@@ -18,6 +18,11 @@
 
 namespace fbn {
 
+#ifndef FBN_RES_CLOCK_BUILD
+#define FBN_RES_CLOCK_BUILD 0   // developer builds (tools/build_variant.sh ... -DFBN_RES_CLOCK_BUILD=1): FBN_RES_CLOCK=1 records cycles per block
+#endif
+constexpr bool kResClock = FBN_RES_CLOCK_BUILD != 0;
+
 namespace {
 
 struct V2 {
@@ -53,7 +58,8 @@ __device__ __forceinline__ void sts128(uint32_t a, V2 v) { asm volatile("st.shar
 
 // start the bulk copy of one constant block into a buffer; completion is counted in bytes on the buffer's mbarrier
 __device__ __forceinline__ void block_issue(uint32_t dst_s, const unsigned char *src, uint32_t bytes, uint32_t bar_s) {
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // the CTA's earlier reads of the buffer before the copy engine's write
+    // (no proxy fence: the buffer was only READ through the generic proxy, and those reads are ordered before this point by the
+    // CTA barrier; measured: the fence cost ~270 cycles per block on the issuing warp's critical path)
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_s), "r"(bytes) : "memory");
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst_s), "l"(src), "r"(bytes),
                  "r"(bar_s)
@@ -122,73 +128,126 @@ __device__ __forceinline__ void res_write_lams(uint32_t lams_s, int n_lams, uint
 // registers 2 / 1
 template <int NG, int MAXT>
 struct ResBatch {
-    static constexpr int value = MAXT <= 16 ? (NG <= 2 ? 4 : 2) : (NG <= 2 ? 2 : 1);
+    static constexpr int value = MAXT <= 16 ? (NG <= 2 ? 4 : 2) : (MAXT <= 24 ? 2 : (NG <= 2 ? 2 : 1));
 };
 
-// N records from `rec` on: acc += potential(case) * product of the gathered message entries
-template <int NG, int N>
-__device__ __forceinline__ void res_batch(uint32_t rec, uint32_t pot0, uint32_t pot1, uint32_t Sb, V2 &acc) {
-    constexpr uint32_t kRec = NG > 3 ? 32u : 16u;
-    uint4 A[N], B[N];
-#pragma unroll
-    for (int b = 0; b < N; ++b) {
-        A[b] = lds128u(rec + b * kRec);
-        if (NG > 3) B[b] = lds128u(rec + b * kRec + 16);
-    }
-    double p0[N], p1[N];
-    V2 m[N][NG > 0 ? NG : 1];
-#pragma unroll
-    for (int b = 0; b < N; ++b) {
-        p0[b] = lds64(pot0 + A[b].x);
-        p1[b] = lds64(pot1 + A[b].x);
-        if (NG > 0) m[b][0] = lds128(Sb + A[b].y);
-        if (NG > 1) m[b][1] = lds128(Sb + A[b].z);
-        if (NG > 2) m[b][2] = lds128(Sb + A[b].w);
-        if (NG > 3) m[b][3] = lds128(Sb + B[b].x);
-    }
-#pragma unroll
-    for (int b = 0; b < N; ++b) {
-        double v0 = p0[b], v1 = p1[b];
-#pragma unroll
-        for (int g = 0; g < NG; ++g) { v0 *= m[b][g].x; v1 *= m[b][g].y; }
-        acc.x += v0; acc.y += v1;
-    }
-}
-
-// one SUM item: `n_targets` targets of one op, `rows` = Q * BATCH + REM records per target, target-major. REM is a template
-// parameter so that a target's records are whole batches: no per-record test for the end of a target.
-// CM: the op checks target variables against the evidence (per-target factor tables, resident.h).
-template <int NG, int BATCH, int REM, bool CM>
-__device__ __forceinline__ void res_sum(uint32_t blk, const uint4 a, const uint4 b4, uint32_t Sb, uint32_t patl) {
-    constexpr uint32_t kRec = NG > 3 ? 32u : 16u;
-    const uint32_t n_targets = a.z, q = a.w / BATCH, desc = blk + b4.y;
-    uint32_t dst = Sb + b4.x;
-    const uint32_t nfold = lds32(desc), ncm = CM ? lds32(desc + 4) : 0u;
-    uint32_t pot0 = blk, pot1 = blk;   // this lane's pattern slot of the potentials, case 0 / case 1
+// this lane's pattern slots of an op's potentials (one per case): block base + sum over the folded variables of pattern x stride
+__device__ __noinline__ uint2 res_fold(uint32_t blk, uint32_t desc, uint32_t patl) {
+    const uint32_t nfold = lds32(desc);
+    uint32_t pot0 = blk, pot1 = blk;
+#pragma unroll 1
     for (uint32_t k = 0; k < nfold; ++k) {
         const uint32_t v = lds32(desc + 16 + 8 * k), st = lds32(desc + 20 + 8 * k);
         const uint32_t pp = lds16(patl + v * kTileCases);
         pot0 += (pp & 255u) * st;
         pot1 += (pp >> 8) * st;
     }
-    const uint32_t cmd = desc + 16 + ((8 * nfold + 15u) & ~15u);
+    return make_uint2(pot0, pot1);
+}
+
+// one SUM item: the `n_targets` x `rows` records of a piece as ONE stream, target-major, in batches of BATCH records whose loads
+// are all issued before the first use; a batch may span targets (their sums overlap in time: a warp that finished one target
+// at a time spent most of its cycles waiting for a chain of dependent shared-memory loads), the end of a target is a
+// warp-uniform counter. One compact body per NG: the code of all item kinds must stay in the instruction cache, the warps of
+// a CTA run different kinds at the same time (a first version with one fully unrolled body per (gathers, remainder, checks)
+// was 380 KB of SASS and lost 13 % of the warp time to instruction fetches).
+template <int NG, int BATCH>
+__device__ __noinline__ void res_sum(uint32_t blk, const uint4 a, const uint4 b4, uint32_t Sb, uint32_t patl, bool cm) {
+    constexpr uint32_t kRec = NG > 3 ? 32u : 16u;
+    const uint32_t rows = a.w, desc = blk + b4.y;
+    uint32_t n = a.z * rows, dst = Sb + b4.x;
+    const uint2 pots = res_fold(blk, desc, patl);
+    const uint32_t pot0 = pots.x, pot1 = pots.y;
+    uint32_t rec = blk + a.y, r = 0;
+    // checked target variables (at most kResMaxChecks): this lane's two pattern bytes of each, read once per item; per finished
+    // target the byte the target wants (a word per target and variable); cw = 0: no checks
+    uint32_t cw = 0, ncm = 0, c0 = 0, c1 = 0, c2 = 0;
+    if (cm) {
+        const uint4 h = lds128u(desc);   // nfold, ncm, want_off
+        ncm = h.y;
+        const uint32_t cv = desc + 16 + 8 * h.x;
+        cw = blk + h.z + b4.z * ncm * 4;
+        c0 = lds16(patl + lds32(cv) * kTileCases);
+        if (ncm > 1) c1 = lds16(patl + lds32(cv + 4) * kTileCases);
+        if (ncm > 2) c2 = lds16(patl + lds32(cv + 8) * kTileCases);
+    }
+    auto check = [&](uint32_t c, uint32_t want, V2 &x) {
+        const uint32_t q0 = c & 255u, q1 = c >> 8;
+        if (q0 != 0 && q0 != want) x.x = 0.0;
+        if (q1 != 0 && q1 != want) x.y = 0.0;
+    };
+    V2 acc = {0.0, 0.0};
+    auto batch = [&](auto nb) {
+        constexpr int N = decltype(nb)::value;
+        uint4 A[N], B[N];
+#pragma unroll
+        for (int b = 0; b < N; ++b) {
+            A[b] = lds128u(rec + b * kRec);
+            if (NG > 3) B[b] = lds128u(rec + b * kRec + 16);
+        }
+        double p0[N], p1[N];
+        V2 m[N][NG > 0 ? NG : 1];
+#pragma unroll
+        for (int b = 0; b < N; ++b) {
+            p0[b] = lds64(pot0 + A[b].x);
+            p1[b] = lds64(pot1 + A[b].x);
+            if (NG > 0) m[b][0] = lds128(Sb + A[b].y);
+            if (NG > 1) m[b][1] = lds128(Sb + A[b].z);
+            if (NG > 2) m[b][2] = lds128(Sb + A[b].w);
+            if (NG > 3) m[b][3] = lds128(Sb + B[b].x);
+        }
+#pragma unroll
+        for (int b = 0; b < N; ++b) {
+            double v0 = p0[b], v1 = p1[b];
+#pragma unroll
+            for (int g = 0; g < NG; ++g) { v0 *= m[b][g].x; v1 *= m[b][g].y; }
+            acc.x += v0; acc.y += v1;
+            if (++r == rows) {   // end of target j
+                if (cw) {
+                    check(c0, lds32(cw), acc);
+                    if (ncm > 1) check(c1, lds32(cw + 4), acc);
+                    if (ncm > 2) check(c2, lds32(cw + 8), acc);
+                    cw += 4 * ncm;
+                }
+                sts128(dst, acc);
+                dst += kResRowBytes;
+                r = 0;
+                acc.x = 0.0; acc.y = 0.0;
+            }
+        }
+        rec += N * kRec;
+    };
+#pragma unroll 1
+    for (; n >= BATCH; n -= BATCH) batch(std::integral_constant<int, BATCH>());
+    if constexpr (BATCH > 1) {
+#pragma unroll 1
+        for (; n > 0; --n) batch(std::integral_constant<int, 1>());
+    }
+}
+
+// ops with five to seven gathers per entry (cliques with more than four neighbours): plain loop
+__device__ __noinline__ void res_sum_generic(uint32_t blk, const uint4 a, const uint4 b4, uint32_t Sb, uint32_t patl, uint32_t ng, bool cm) {
+    const uint32_t n_targets = a.z, rows = a.w, desc = blk + b4.y;
+    uint32_t dst = Sb + b4.x;
+    const uint2 pots = res_fold(blk, desc, patl);
     uint32_t rec = blk + a.y, j = b4.z;
     for (uint32_t t = 0; t < n_targets; ++t) {
         V2 acc = {0.0, 0.0};
-        for (uint32_t i = 0; i < q; ++i) {
-            res_batch<NG, BATCH>(rec, pot0, pot1, Sb, acc);
-            rec += BATCH * kRec;
+        for (uint32_t r = 0; r < rows; ++r, rec += 32u) {
+            const uint32_t po = lds32(rec);
+            double v0 = lds64(pots.x + po), v1 = lds64(pots.y + po);
+            for (uint32_t g = 0; g < ng; ++g) {
+                const V2 m = lds128(Sb + lds32(rec + 4 + 4 * g));
+                v0 *= m.x; v1 *= m.y;
+            }
+            acc.x += v0; acc.y += v1;
         }
-        if constexpr (REM > 0) {
-            res_batch<NG, REM>(rec, pot0, pot1, Sb, acc);
-            rec += REM * kRec;
-        }
-        if (CM) {
-            for (uint32_t k = 0; k < ncm; ++k) {   // 1.0 / 0.0: does the case's evidence allow this target's state of the variable
-                const uint4 c = lds128u(cmd + 16 * k);   // variable, table, bytes per target
-                const uint32_t pp = lds16(patl + c.x * kTileCases), tj = blk + c.y + j * c.z;
-                acc.x *= lds64(tj + (pp & 255u) * 8);
-                acc.y *= lds64(tj + (pp >> 8) * 8);
+        if (cm) {
+            const uint4 h = lds128u(desc);   // nfold, ncm, want_off
+            for (uint32_t k = 0; k < h.y; ++k) {
+                const uint32_t c = lds16(patl + lds32(desc + 16 + 8 * h.x + 4 * k) * kTileCases), want = lds32(blk + h.z + (j * h.y + k) * 4);
+                if ((c & 255u) != 0 && (c & 255u) != want) acc.x = 0.0;
+                if ((c >> 8) != 0 && (c >> 8) != want) acc.y = 0.0;
             }
             ++j;
         }
@@ -197,55 +256,9 @@ __device__ __forceinline__ void res_sum(uint32_t blk, const uint4 a, const uint4
     }
 }
 
-template <int NG, int BATCH, bool CM>
-__device__ __forceinline__ void res_sum_rem(uint32_t blk, const uint4 a, const uint4 b4, uint32_t Sb, uint32_t patl) {
-    switch (a.w % BATCH) {
-        case 0: res_sum<NG, BATCH, 0, CM>(blk, a, b4, Sb, patl); break;
-        case 1: res_sum<NG, BATCH, 1 % BATCH, CM>(blk, a, b4, Sb, patl); break;
-        case 2: res_sum<NG, BATCH, 2 % BATCH, CM>(blk, a, b4, Sb, patl); break;
-        default: res_sum<NG, BATCH, 3 % BATCH, CM>(blk, a, b4, Sb, patl); break;
-    }
-}
-
-// ops with five to seven gathers per entry (cliques with more than four neighbours): plain loop
-__device__ __noinline__ void res_sum_generic(uint32_t blk, const uint4 a, const uint4 b4, uint32_t Sb, uint32_t patl, uint32_t ng) {
-    const uint32_t n_targets = a.z, rows = a.w, desc = blk + b4.y;
-    uint32_t dst = Sb + b4.x;
-    const uint32_t nfold = lds32(desc), ncm = lds32(desc + 4);
-    uint32_t pot0 = blk, pot1 = blk;
-    for (uint32_t k = 0; k < nfold; ++k) {
-        const uint32_t v = lds32(desc + 16 + 8 * k), st = lds32(desc + 20 + 8 * k);
-        const uint32_t pp = lds16(patl + v * kTileCases);
-        pot0 += (pp & 255u) * st;
-        pot1 += (pp >> 8) * st;
-    }
-    const uint32_t cmd = desc + 16 + ((8 * nfold + 15u) & ~15u);
-    uint32_t rec = blk + a.y, j = b4.z;
-    for (uint32_t t = 0; t < n_targets; ++t, ++j) {
-        V2 acc = {0.0, 0.0};
-        for (uint32_t r = 0; r < rows; ++r, rec += 32u) {
-            const uint32_t po = lds32(rec);
-            double v0 = lds64(pot0 + po), v1 = lds64(pot1 + po);
-            for (uint32_t g = 0; g < ng; ++g) {
-                const V2 m = lds128(Sb + lds32(rec + 4 + 4 * g));
-                v0 *= m.x; v1 *= m.y;
-            }
-            acc.x += v0; acc.y += v1;
-        }
-        for (uint32_t k = 0; k < ncm; ++k) {
-            const uint4 c = lds128u(cmd + 16 * k);
-            const uint32_t pp = lds16(patl + c.x * kTileCases), tj = blk + c.y + j * c.z;
-            acc.x *= lds64(tj + (pp & 255u) * 8);
-            acc.y *= lds64(tj + (pp >> 8) * 8);
-        }
-        sts128(dst, acc);
-        dst += kResRowBytes;
-    }
-}
-
 // OUT item: posteriors + label of one variable (GetProbabilitiesOneNode src/JunctionTree.cpp:1392-1454, Inference::ArgMax
 // src/Inference.cpp:92-102): normalise the unnormalised marginal rows, zeros for an observed variable
-__device__ __forceinline__ void res_out(const ResDev &R, const uint4 a, const uint4 b4, uint32_t Sb, uint32_t patl, int64_t tile, int64_t n_cases,
+__device__ __noinline__ void res_out(const ResDev &R, const uint4 a, const uint4 b4, uint32_t Sb, uint32_t patl, int64_t tile, int64_t n_cases,
                                         int lane, int32_t *__restrict__ labels, double *__restrict__ post) {
     const uint32_t v = a.y, dim = a.z, off = a.w, mg = Sb + b4.x;   // ResItem: variable, dim, posterior column, marginal rows
     const uint32_t pp = lds16(patl + v * kTileCases);
@@ -257,13 +270,16 @@ __device__ __forceinline__ void res_out(const ResDev &R, const uint4 a, const ui
         const V2 x = lds128(mg + d * kResRowBytes);
         s0 += x.x; s1 += x.y;
     }
+    // one division per case, then products (a division per state costs ~35 instructions; x * (1 / s) is within one ulp of x / s).
+    // 0 / 0 (evidence with probability zero) must stay NaN as in the reference: 1 / 0 = inf, 0 * inf = NaN
+    const double r0 = 1.0 / s0, r1 = 1.0 / s1;
     double best0 = 0.0, best1 = 0.0;
     int arg0 = -1, arg1 = -1;
     double *q0 = post ? post + c0 * R.sum_dims + off : nullptr;
     double *q1 = q0 ? q0 + R.sum_dims : nullptr;
     for (uint32_t d = 0; d < dim; ++d) {
         const V2 x = lds128(mg + d * kResRowBytes);
-        const double pr0 = obs0 ? 0.0 : x.x / s0, pr1 = obs1 ? 0.0 : x.y / s1;
+        const double pr0 = obs0 ? 0.0 : x.x * r0, pr1 = obs1 ? 0.0 : x.y * r1;
         if (q0 && ok0) q0[d] = pr0;
         if (q1 && ok1) q1[d] = pr1;
         if (pr0 > best0) { best0 = pr0; arg0 = (int)d; }
@@ -316,11 +332,13 @@ __global__ void __launch_bounds__(MAXT * 32, 1) jt_resident_kernel(const ResDev 
         const uint32_t patl = pat_cur + lane * 2;
         const int64_t next_tile = tile + gridDim.x;
         for (int b = 0; b < R.n_blocks; ++b, ++g) {
-            if (threadIdx.x == 0) {   // request the next block: its buffer was last read before the CTA barrier that ended block g - 1
+            if (kResClock && R.clk && blockIdx.x == 0 && threadIdx.x == 0 && g < 2048) R.clk[4 * g] = clock64();
+            if (threadIdx.x == blockDim.x - 32) {   // (the last warp: longest-processing-time-first gives it the lightest load) request the next block: its buffer was last read before the CTA barrier that ended block g - 1
                 const int nb = b + 1 < R.n_blocks ? b + 1 : (next_tile < n_tiles ? 0 : -1);
                 if (nb >= 0) block_issue(sbase + (((g + 1) & 1) ? L.buf1 : L.buf0), R.blob + boff[nb], boff[nb + 1] - boff[nb], bars + 8 * ((g + 1) & 1));
             }
             block_wait(bars + 8 * (g & 1), (g >> 1) & 1);
+            if (kResClock && R.clk && blockIdx.x == 0 && threadIdx.x == 0 && g < 2048) R.clk[4 * g + 1] = clock64();
             const uint32_t blk = sbase + ((g & 1) ? L.buf1 : L.buf0);
             const uint4 hdr = lds128u(blk);   // n_items, -, items_off, bytes
             const uint32_t i0 = lds32(blk + 16 + 4 * warp), i1 = lds32(blk + 20 + 4 * warp);
@@ -330,23 +348,15 @@ __global__ void __launch_bounds__(MAXT * 32, 1) jt_resident_kernel(const ResDev 
                 const uint32_t ia = blk + hdr.z + i * 32;
                 const uint4 a = lds128u(ia), b4 = lds128u(ia + 16);
                 const uint32_t kind = a.x & 255u, ng = a.x >> 8;
-                if (kind == RES_SUM) {
+                if (kind == RES_SUM || kind == RES_SUMC) {
+                    const bool cm = kind == RES_SUMC;   // with per-target evidence checks
                     switch (ng) {
-                        case 0: res_sum_rem<0, ResBatch<0, MAXT>::value, false>(blk, a, b4, Sb, patl); break;
-                        case 1: res_sum_rem<1, ResBatch<1, MAXT>::value, false>(blk, a, b4, Sb, patl); break;
-                        case 2: res_sum_rem<2, ResBatch<2, MAXT>::value, false>(blk, a, b4, Sb, patl); break;
-                        case 3: res_sum_rem<3, ResBatch<3, MAXT>::value, false>(blk, a, b4, Sb, patl); break;
-                        case 4: res_sum_rem<4, ResBatch<4, MAXT>::value, false>(blk, a, b4, Sb, patl); break;
-                        default: res_sum_generic(blk, a, b4, Sb, patl, ng); break;
-                    }
-                } else if (kind == RES_SUMC) {   // with per-target evidence checks: leaf-side views, few gathers
-                    switch (ng) {
-                        case 0: res_sum_rem<0, 2, true>(blk, a, b4, Sb, patl); break;
-                        case 1: res_sum_rem<1, 2, true>(blk, a, b4, Sb, patl); break;
-                        case 2: res_sum_rem<2, 2, true>(blk, a, b4, Sb, patl); break;
-                        case 3: res_sum_rem<3, 2, true>(blk, a, b4, Sb, patl); break;
-                        case 4: res_sum_rem<4, 2, true>(blk, a, b4, Sb, patl); break;
-                        default: res_sum_generic(blk, a, b4, Sb, patl, ng); break;
+                        case 0: res_sum<0, ResBatch<0, MAXT>::value>(blk, a, b4, Sb, patl, cm); break;
+                        case 1: res_sum<1, ResBatch<1, MAXT>::value>(blk, a, b4, Sb, patl, cm); break;
+                        case 2: res_sum<2, ResBatch<2, MAXT>::value>(blk, a, b4, Sb, patl, cm); break;
+                        case 3: res_sum<3, ResBatch<3, MAXT>::value>(blk, a, b4, Sb, patl, cm); break;
+                        case 4: res_sum<4, ResBatch<4, MAXT>::value>(blk, a, b4, Sb, patl, cm); break;
+                        default: res_sum_generic(blk, a, b4, Sb, patl, ng, cm); break;
                     }
                 } else if (kind == RES_OUT) {
                     res_out(R, a, b4, Sb, patl, tile, n_cases, lane, labels, post);
@@ -356,18 +366,20 @@ __global__ void __launch_bounds__(MAXT * 32, 1) jt_resident_kernel(const ResDev 
                     res_load_patterns(R, pat_nxt, dims_s, next_tile, n_cases, ev_off, ev_base, ev_vars, ev_vals, lane);
                 }
             }
+            if (kResClock && R.clk && blockIdx.x == 0 && threadIdx.x == 0 && g < 2048) R.clk[4 * g + 2] = clock64();
             __syncthreads();
         }
     }
 }
 
 // ---- launch helpers (called from capi.cu) ------------------------------------------------------------------------
-static int res_maxt(int warps) { return warps <= 8 ? 8 : (warps <= 16 ? 16 : 32); }
+static int res_maxt(int warps) { return warps <= 8 ? 8 : (warps <= 16 ? 16 : (warps <= 24 ? 24 : 32)); }
 
 cudaError_t resident_prepare(int warps, int smem_optin) {
     switch (res_maxt(warps)) {
         case 8: return cudaFuncSetAttribute(jt_resident_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin);
         case 16: return cudaFuncSetAttribute(jt_resident_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin);
+        case 24: return cudaFuncSetAttribute(jt_resident_kernel<24>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin);
         default: return cudaFuncSetAttribute(jt_resident_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin);
     }
 }
@@ -381,6 +393,7 @@ cudaError_t resident_launch(const ResDev &R, int warps, int grid, int64_t n_case
     switch (res_maxt(warps)) {
         case 8: jt_resident_kernel<8><<<grid, warps * 32, smem, st>>>(R, n_cases, ev_off, ev_base, ev_vars, ev_vals, labels, post, n_tiles); break;
         case 16: jt_resident_kernel<16><<<grid, warps * 32, smem, st>>>(R, n_cases, ev_off, ev_base, ev_vars, ev_vals, labels, post, n_tiles); break;
+        case 24: jt_resident_kernel<24><<<grid, warps * 32, smem, st>>>(R, n_cases, ev_off, ev_base, ev_vars, ev_vals, labels, post, n_tiles); break;
         default: jt_resident_kernel<32><<<grid, warps * 32, smem, st>>>(R, n_cases, ev_off, ev_base, ev_vars, ev_vals, labels, post, n_tiles); break;
     }
     return cudaGetLastError();

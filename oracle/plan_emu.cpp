@@ -197,7 +197,7 @@ extern "C" int emu_run_resident(const fbn_tree_desc *tree, int warps, int64_t sm
                     const uint32_t *fd = reinterpret_cast<const uint32_t *>(bytes + I.desc_off);
                     uint32_t fx = 0;
                     for (uint32_t k = 0; k < fd[0]; ++k) fx += (uint32_t)pat[fd[4 + 2 * k]] * fd[5 + 2 * k];
-                    const uint32_t ncm = fd[1], *cm = fd + 4 + ((2 * fd[0] + 3) & ~3u);
+                    const uint32_t ncm = fd[1], *cm = fd + 4 + 2 * fd[0], *want = reinterpret_cast<const uint32_t *>(bytes + fd[2]);
                     if ((ncm != 0) != (kind == RES_SUMC)) { g_err = "item kind does not match the op's checks"; return 7; }
                     const uint32_t stride = ng > 3 ? 8 : 4;
                     const uint32_t *rec = reinterpret_cast<const uint32_t *>(bytes + I.rec_off);
@@ -210,10 +210,9 @@ extern "C" int emu_run_resident(const fbn_tree_desc *tree, int warps, int64_t sm
                             for (uint32_t g = 0; g < ng; ++g) v *= S[q[1 + g] / rowb];
                             acc += v;
                         }
-                        for (uint32_t k = 0; k < ncm; ++k) {   // per-target factor tables [target][pattern]
-                            double f;
-                            memcpy(&f, bytes + cm[4 * k + 1] + (size_t)(I.j0 + j) * cm[4 * k + 2] + (size_t)pat[cm[4 * k]] * 8, 8);
-                            acc *= f;
+                        for (uint32_t k = 0; k < ncm; ++k) {   // checked target variables: zero where the case observed another state
+                            const int pv = pat[cm[k]];
+                            if (pv != 0 && pv != (int)want[(size_t)(I.j0 + j) * ncm + k]) acc = 0.0;
                         }
                         W[I.dst_off / rowb + j] = acc;
                     }

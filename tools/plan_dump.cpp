@@ -74,3 +74,29 @@ extern "C" int resident_dump(const fbn_tree_desc *tree, int warps, int verbose) 
     }
     return 0;
 }
+
+// how the gathers of a flat plan depend on rows / targets: entries x gathers by category, and what hoisting would leave
+extern "C" int gather_stats(const fbn_tree_desc *tree) {
+    fbn::HostPlan h;
+    std::string err = fbn::build_plan(*tree, 1, h, false);
+    if (!err.empty()) { fprintf(stderr, "%s\n", err.c_str()); return 1; }
+    long long both = 0, rowonly = 0, colonly = 0, none = 0, entries = 0, hoisted = 0, potless = 0, nofold = 0;
+    for (const fbn::SumOp &op : h.ops) {
+        entries += (long long)op.rows * op.cols;
+        if (op.pot_off < 0) potless += (long long)op.rows * op.cols;
+        else if (op.nfold == 0) nofold += (long long)op.rows * op.cols;
+        for (int g = 0; g < op.ng; ++g) {
+            bool rv = false, cv = false;
+            for (int r = 1; r < op.rows; ++r) rv = rv || h.idx32[op.rowpart_off + (long long)r * op.ng + g] != h.idx32[op.rowpart_off + g];
+            for (int j = 1; j < op.cols; ++j) cv = cv || h.idx32[op.colpart_off + (long long)j * op.ng + g] != h.idx32[op.colpart_off + g];
+            const long long e = (long long)op.rows * op.cols;
+            if (rv && cv) { both += e; hoisted += e; }
+            else if (rv) { rowonly += e; hoisted += e; }   // target-independent: reloaded per target unless targets are blocked
+            else if (cv) { colonly += e; hoisted += op.cols; }   // row-independent: once per target
+            else { none += e; hoisted += 1; }
+        }
+    }
+    printf("entries %lld (no potential %lld, unfolded potential %lld)  gathers: row+target %lld, row only %lld, target only %lld, constant %lld -> %lld loads after hoisting the row-independent ones out of the row loop\n",
+           entries, potless, nofold, both, rowonly, colonly, none, hoisted);
+    return 0;
+}

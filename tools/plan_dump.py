@@ -22,7 +22,9 @@ verbose = int(sys.argv[4]) if len(sys.argv) > 4 else 1
 d, keep = emu.tree_desc(bench.load_tree(w))
 sys.stdout.flush()
 L = C.CDLL(so)
-if team < 0:
+if team == 0:
+    L.gather_stats(C.byref(d))
+elif team < 0:
     L.resident_dump(C.byref(d), -team, verbose)  # negative team: the resident-tile schedule for -team warps
 else:
     L.plan_dump(C.byref(d), team, level, verbose)
