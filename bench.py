@@ -355,6 +355,19 @@ def traffic_entry(workload, info, kernel):
     return float(tj["dram_bytes_per_case"]), tj.get("source")
 
 
+def smem_entry(workload, info):
+    """ncu-measured shared-memory traffic per case (l1tex__data_pipe_lsu_wavefronts_mem_shared x 128 B, one --set full capture;
+    profiles/traffic.json, same kernel revision): the on-chip roofline of jt_resident_kernel, whose tile state never leaves
+    shared memory. (None, None) when absent or stale."""
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if not os.path.exists(tpath):
+        return None, None
+    tj = json.load(open(tpath)).get(workload) or {}
+    if "smem_bytes_per_case" not in tj or tj.get("smem_kernel_rev") != info.kernel_rev or tj.get("smem_team_warps") != info.team_warps:
+        return None, None
+    return float(tj["smem_bytes_per_case"]), tj.get("smem_source")
+
+
 def run_workload(cx, name, steps, warmup, e2e_steps, cases=0, team=0, mode=0, max_resident=0):
     """Device-resident arm, parity prefix, e2e arm of one workload on this rank. Returns the workload's result dict (complete on rank 0)."""
     torch, dist, capi = cx.torch, cx.dist, cx.capi
@@ -475,6 +488,16 @@ def run_workload(cx, name, steps, warmup, e2e_steps, cases=0, team=0, mode=0, ma
     peak, peak_src = cx.peak
     alg_gbs = info.alg_bytes_per_case * n / (kern_ms * 1e-3) / 1e9
     dram_gbs = traffic * n / (kern_ms * 1e-3) / 1e9 if traffic else None
+    smem_b, smem_src = smem_entry(name, info)
+    on_chip = None
+    if smem_b:
+        # shared-memory bandwidth: 128 B per clock and SM (B300_MICROARCH.md: smem crossbar) at the SM clock sampled during the run
+        clk = cx.sampler.summary(t_wall0, t_wall1)
+        smem_peak = torch.cuda.get_device_properties(dev).multi_processor_count * 128.0 * (clk.get("sm_mhz") or clk.get("sm_max_mhz") or 0) * 1e6 / 1e9
+        smem_gbs = smem_b * n / (kern_ms * 1e-3) / 1e9
+        on_chip = {"bound": "shared-memory bandwidth", "smem_bytes_per_case": smem_b, "achieved": smem_gbs, "peak": smem_peak, "unit": "GB/s",
+                   "frac": smem_gbs / smem_peak if smem_peak else None, "source": smem_src,
+                   "peak_source": "n_sms x 128 B/clk x SM clock sampled during the run"}
     res = {
         "workload": w["desc"], "cases": n, "n_evidence": w["n_evidence"], "steps": steps, "warmup": warmup,
         "value": value, "unit": "cases/s", "ms_per_step": ms_per_step,
@@ -490,10 +513,11 @@ def run_workload(cx, name, steps, warmup, e2e_steps, cases=0, team=0, mode=0, ma
         # algorithmic-equivalent figure of SURVEY.md 8(d): bytes the reference's table passes would move; NOT a utilisation (> 1: the kernels fuse passes)
         "alg_bytes_per_case": info.alg_bytes_per_case, "alg_gbs": alg_gbs, "alg_frac": alg_gbs / peak,
         "kernel_bytes_per_case": info.kernel_bytes_per_case,
+        "on_chip": on_chip,
         "parity_prefix": {"cases": k, "max_abs": max_abs, "e2e_max_abs": e2e_max_abs, "labels_equal": labels_equal,
                           "labels_e2e_equal_device": same, "tol": TOL, "golden": WORKLOADS[name]["golden"][0] + ".npz", "ok": ok},
         "labelled_cases": int(round(counts[0])), "total_cases": int(round(counts[1])),
-        "l2": "per-step working set (tile scratch + evidence + posteriors) %.0f MB > 126 MB L2"
+        "l2": "per-step working set (tile scratch in HBM + evidence + posteriors) %.0f MB > 126 MB L2"
               % ((info.scratch_bytes + off_h.nbytes + ev_h.nbytes + ew_h.nbytes + n * sd * 8 + n * 4) / 1e6),
         "clocks": cx.sampler.summary(t_wall0, t_wall1),
         "_window": (t_wall0, t_wall1), "_ok": ok,
@@ -598,7 +622,9 @@ def main():
                          "traffic_source": head["dram_source"], "peak_source": peak_src, "kernel": head["kernel"], "kernel_ms": head["kernel_ms"],
                          "dram_bytes_per_case": head["dram_bytes_per_case"],
                          "alg_bytes_per_case": head["alg_bytes_per_case"], "alg_equiv_gbs": head["alg_gbs"], "alg_frac": head["alg_frac"],
-                         "kernel_bytes_per_case": head["kernel_bytes_per_case"]},
+                         "kernel_bytes_per_case": head["kernel_bytes_per_case"],
+                         # the resident-tile kernel moves only evidence + posteriors through HBM; what bounds it is on the chip
+                         "on_chip": head["on_chip"]},
             "e2e": head["e2e"],
             "parity_prefix": head["parity_prefix"],
             "workloads": others,

@@ -127,6 +127,8 @@ class Plan:
         """Name of the kernel a fused-mode plan launches (level mode launches one kernel per tree level)."""
         if self.info.mode == MODE_LEVEL:
             return "lvl_sum_kernel"
+        if self.info.flat_records == 2:
+            return "jt_resident_kernel"
         return "jt_flat_kernel" if self.info.flat_records else "jt_fused_kernel<%d>" % self.info.team_warps
 
     def close(self):

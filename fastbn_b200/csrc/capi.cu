@@ -250,7 +250,7 @@ extern "C" int fbn_plan_create(const fbn_tree_desc *tree, const fbn_plan_options
     // between its evidence and its posteriors (resident.h). Measured on B200 (ALARM): see DESIGN.md. FBN_NO_RESIDENT=1 keeps
     // the one-warp-per-tile kernel with the tile state in HBM / L2.
     if (!level && h.flat && !getenv("FBN_NO_RESIDENT")) {
-        int warps = 16;
+        int warps = 24;   // measured on B200 (ALARM, M cases/s): 8 warps 199, 16: 258, 24: 268, 32: 265
         if (const char *e = getenv("FBN_RES_WARPS")) warps = std::max(1, std::min(32, atoi(e)));
         fbn::build_resident(h, warps, (int64_t)prop.sharedMemPerBlockOptin, p->rp);
         if (p->rp.ok) {
@@ -401,7 +401,10 @@ extern "C" int fbn_plan_get_info(const fbn_plan *p, fbn_plan_info *o) {
     o->marginal_entries = h.marginal_entries; o->scratch_bytes = p->scratch_bytes; o->plan_bytes = p->plan_bytes;
     o->alg_bytes_per_case = h.alg_bytes_per_case; o->kernel_bytes_per_case = h.kernel_bytes_per_case;
     o->flat_records = p->resident ? 2 : p->dp.flat;
-    if (p->resident) o->team_warps = p->rp.warps;
+    if (p->resident) {
+        o->team_warps = p->rp.warps;
+        o->kernel_bytes_per_case = 8.0 * h.sum_dims + 4.0;   // the tile state never leaves shared memory: posteriors + label out (+ the evidence in)
+    }
     o->tile_cases = fbn::kTileCases; o->view_entries = h.view_entries; o->gather_rows = h.gather_rows;
     o->kernel_rev = kKernelRev;
     return FBN_OK;

@@ -206,7 +206,7 @@ void build_resident(const HostPlan &P, int warps, int64_t smem_limit, ResidentPl
     // not the last block: the next tile's lambda rows are written there, from the patterns the EVID item has loaded
     const int evid_block = (int)(std::max_element(work.begin(), work.end() - 1) - work.begin());
     work[(size_t)evid_block] += kEvidCost;
-    static const double kGrain = getenv("FBN_RES_GRAIN") ? atof(getenv("FBN_RES_GRAIN")) : 120.0;
+    static const double kGrain = getenv("FBN_RES_GRAIN") ? atof(getenv("FBN_RES_GRAIN")) : 200.0;   // measured on B200 (ALARM, 24 warps): 60 -> 264, 120 -> 264, 200 -> 268 M cases/s
     for (int b = 0; b < R.n_blocks; ++b) {
         const double grain = std::max(kGrain, work[(size_t)b] / warps / 2.0);   // aimed cost of a piece
         for (int o : blk_ops[(size_t)b]) {

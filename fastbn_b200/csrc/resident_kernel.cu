@@ -158,6 +158,8 @@ __device__ __noinline__ void res_sum(uint32_t blk, const uint4 a, const uint4 b4
     uint32_t n = a.z * rows, dst = Sb + b4.x;
     const uint2 pots = res_fold(blk, desc, patl);
     const uint32_t pot0 = pots.x, pot1 = pots.y;
+    // (measured and rejected: one potential load for both cases when the view has no folded variable, 4 of 5 ALARM entries:
+    // the warp-uniform branch costs more than the load, 256 against 268 M cases/s)
     uint32_t rec = blk + a.y, r = 0;
     // checked target variables (at most kResMaxChecks): this lane's two pattern bytes of each, read once per item; per finished
     // target the byte the target wants (a word per target and variable); cw = 0: no checks
@@ -341,9 +343,11 @@ __global__ void __launch_bounds__(MAXT * 32, 1) jt_resident_kernel(const ResDev 
             if (kResClock && R.clk && blockIdx.x == 0 && threadIdx.x == 0 && g < 2048) R.clk[4 * g + 1] = clock64();
             const uint32_t blk = sbase + ((g & 1) ? L.buf1 : L.buf0);
             const uint4 hdr = lds128u(blk);   // n_items, -, items_off, bytes
-            const uint32_t i0 = lds32(blk + 16 + 4 * warp), i1 = lds32(blk + 20 + 4 * warp);
             // the last block sums nothing: the next tile's lambda rows can be written (its patterns came in an earlier block)
             if (R.n_lams && b == R.n_blocks - 1 && next_tile < n_tiles) res_write_lams(sbase + L.lams, R.n_lams, Sb, pat_nxt + lane * 2, warp, T);
+            const uint32_t i0 = lds32(blk + 16 + 4 * warp), i1 = lds32(blk + 20 + 4 * warp);
+            // (measured and rejected: the warps taking the items from a queue, an atomic counter in shared memory, instead of the
+            // planner's static lists: 228-238 M ALARM cases/s against 258-268 M, the counter serialises the warps at every block start)
             for (uint32_t i = i0; i < i1; ++i) {
                 const uint32_t ia = blk + hdr.z + i * 32;
                 const uint4 a = lds128u(ia), b4 = lds128u(ia + 16);

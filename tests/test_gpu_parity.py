@@ -201,7 +201,7 @@ def test_lambda_gather_path(alarm_tree, team, mode, max_fx, monkeypatch):
     p.close()
 
 
-@pytest.mark.parametrize("warps", ["8", "16", "32"])
+@pytest.mark.parametrize("warps", ["8", "16", "24", "32"])
 def test_resident_kernel_many_waves_against_oracle(alarm_tree, warps, monkeypatch):
     """jt_resident_kernel (tile state in shared memory, constants by cp.async.bulk, one CTA per SM): 30 001 cases = more than three
     waves of tiles per CTA plus a ragged last tile, ragged evidence (0..12 pairs per case), EVERY case against the CPU oracle, so

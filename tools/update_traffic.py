@@ -44,5 +44,24 @@ def main(tag, d="gpurun_out"):
     json.dump(tj, open(tpath, "w"), indent=1)
 
 
+def smem(workload, rep, cases, team):
+    """--smem <workload> <file.ncu-rep> <cases> <team warps>: shared-memory bytes per case of the (single) profiled launch = LSU wavefronts x 128 B"""
+    import subprocess
+    rows = list(csv.reader(subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout.splitlines()))
+    i = rows[0].index("l1tex__data_pipe_lsu_wavefronts_mem_shared.sum")
+    waves = float(rows[2][i].replace(",", ""))
+    rev = int(re.search(r"kKernelRev\s*=\s*(\d+)", open(os.path.join(ROOT, "fastbn_b200", "csrc", "capi.cu")).read()).group(1))
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    tj = json.load(open(tpath))
+    tj.setdefault(workload, {}).update({
+        "smem_bytes_per_case": waves * 128.0 / cases, "smem_kernel_rev": rev, "smem_team_warps": team,
+        "smem_source": "%s (ncu --set full, l1tex__data_pipe_lsu_wavefronts_mem_shared.sum x 128 B over one %d-case launch)" % (os.path.basename(rep), cases)})
+    print(workload, tj[workload])
+    json.dump(tj, open(tpath, "w"), indent=1)
+
+
 if __name__ == "__main__":
-    main(sys.argv[1], sys.argv[2] if len(sys.argv) > 2 else "gpurun_out")
+    if sys.argv[1] == "--smem":
+        smem(sys.argv[2], sys.argv[3], int(sys.argv[4]), int(sys.argv[5]))
+    else:
+        main(sys.argv[1], sys.argv[2] if len(sys.argv) > 2 else "gpurun_out")
