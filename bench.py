@@ -551,6 +551,12 @@ def main():
     import torch.distributed as dist
     from fastbn_b200 import capi
 
+    # stdout carries ONE JSON line: whatever libraries print on their own (NCCL writes "NCCL version ..." to stdout when the box
+    # sets NCCL_DEBUG=VERSION) goes to stderr; the saved descriptor gets the line at the end
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
+
     cx = Ctx()
     cx.torch, cx.dist, cx.capi = torch, dist, capi
     cx.world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -642,7 +648,8 @@ def main():
                     line["cpu_baseline"]["config1"] = c1
             for nm, o in others.items():
                 o["cpu_baseline"] = cpu_baseline_block(nm, cores)
-        print(json.dumps(line), flush=True)
+        sys.stdout.flush()
+        os.write(json_fd, (json.dumps(line) + "\n").encode())
     if comm is not None:
         comm.close()
     if cx.world > 1:
