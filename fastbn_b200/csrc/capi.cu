@@ -249,7 +249,7 @@ extern "C" int fbn_plan_create(const fbn_tree_desc *tree, const fbn_plan_options
     // Small trees (flat plans): when the LIVE message rows of a tile fit into one SM's shared memory the tile never touches HBM
     // between its evidence and its posteriors (resident.h). Measured on B200 (ALARM): see DESIGN.md. FBN_NO_RESIDENT=1 keeps
     // the one-warp-per-tile kernel with the tile state in HBM / L2.
-    if (!level && h.flat && !getenv("FBN_NO_RESIDENT")) {
+    if (!level && h.flat && fbn::kW == 2 && !getenv("FBN_NO_RESIDENT")) {   // (the resident kernel is written for two cases per lane)
         int warps = 24;   // measured on B200 (ALARM, M cases/s): 8 warps 199, 16: 258, 24: 268, 32: 265
         if (const char *e = getenv("FBN_RES_WARPS")) warps = std::max(1, std::min(32, atoi(e)));
         fbn::build_resident(h, warps, (int64_t)prop.sharedMemPerBlockOptin, p->rp);
@@ -262,7 +262,7 @@ extern "C" int fbn_plan_create(const fbn_tree_desc *tree, const fbn_plan_options
             p->rd.n_lams = (int32_t)p->rp.lams.size();
             p->rd.clk = nullptr;
             if (getenv("FBN_RES_CLOCK")) {   // developer knob: cycles per block of CTA 0, printed when the plan is destroyed
-                std::vector<long long> z(4 * 2048 + 4, 0);
+                std::vector<long long> z(4 * 2048 + 4 + 64, 0);
                 const long long *dz = nullptr;
                 if ((rc = upload(p, z, &dz)) != FBN_OK) { fbn_plan_destroy(p); return rc; }
                 p->rd.clk = const_cast<long long *>(dz);
@@ -373,6 +373,12 @@ extern "C" void fbn_plan_destroy(fbn_plan *p) {
                 if (n) { fprintf(stderr, "  block %2d: %6.0f / %6.0f / %6.0f\n", b, w / n, it / n, br / n); tot += (w + it + br) / n; }
             }
             fprintf(stderr, "  tile: %.0f cycles\n", tot);
+            static const char *seg[] = {"barrier->before wait", "wait for block", "header + list", "item load + dispatch", "fold", "check setup", "record loop",
+                                        "items done", "CTA barrier"};
+            std::vector<long long> sc(40);
+            if (cudaMemcpy(sc.data(), p->rd.clk + 8100, 40 * 8, cudaMemcpyDeviceToHost) == cudaSuccess)
+                for (int k = 0; k < 9; ++k)
+                    if (sc[20 + k]) fprintf(stderr, "  segment %-22s: %8.0f cycles mean x %lld\n", seg[k], (double)sc[k] / sc[20 + k], sc[20 + k]);
         }
     }
     for (void *d : p->dev_allocs) cudaFree(d);

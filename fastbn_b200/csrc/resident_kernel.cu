@@ -22,6 +22,19 @@ namespace fbn {
 #define FBN_RES_CLOCK_BUILD 0   // developer builds (tools/build_variant.sh ... -DFBN_RES_CLOCK_BUILD=1): FBN_RES_CLOCK=1 records cycles per block
 #endif
 constexpr bool kResClock = FBN_RES_CLOCK_BUILD != 0;
+#if FBN_RES_CLOCK_BUILD
+// developer build: cycles of thread 0 of CTA 0 per segment of a phase (summed over all phases and tiles)
+__shared__ long long s_clk_t, s_clk_sum[16], s_clk_cnt[16];
+#define RES_STAMP(k)                                                     \
+    do {                                                                 \
+        if (blockIdx.x == 0 && threadIdx.x == 0) {                       \
+            const long long n__ = clock64();                             \
+            s_clk_sum[k] += n__ - s_clk_t; s_clk_cnt[k] += 1; s_clk_t = n__; \
+        }                                                                \
+    } while (0)
+#else
+#define RES_STAMP(k) do { } while (0)
+#endif
 
 namespace {
 
@@ -156,7 +169,9 @@ __device__ __noinline__ void res_sum(uint32_t blk, const uint4 a, const uint4 b4
     constexpr uint32_t kRec = NG > 3 ? 32u : 16u;
     const uint32_t rows = a.w, desc = blk + b4.y;
     uint32_t n = a.z * rows, dst = Sb + b4.x;
+    RES_STAMP(3);
     const uint2 pots = res_fold(blk, desc, patl);
+    RES_STAMP(4);
     const uint32_t pot0 = pots.x, pot1 = pots.y;
     // (measured and rejected: one potential load for both cases when the view has no folded variable, 4 of 5 ALARM entries:
     // the warp-uniform branch costs more than the load, 256 against 268 M cases/s)
@@ -173,20 +188,18 @@ __device__ __noinline__ void res_sum(uint32_t blk, const uint4 a, const uint4 b4
         if (ncm > 1) c1 = lds16(patl + lds32(cv + 4) * kTileCases);
         if (ncm > 2) c2 = lds16(patl + lds32(cv + 8) * kTileCases);
     }
+    RES_STAMP(5);
     auto check = [&](uint32_t c, uint32_t want, V2 &x) {
         const uint32_t q0 = c & 255u, q1 = c >> 8;
         if (q0 != 0 && q0 != want) x.x = 0.0;
         if (q1 != 0 && q1 != want) x.y = 0.0;
     };
     V2 acc = {0.0, 0.0};
-    auto batch = [&](auto nb) {
+    // a batch = N records: their data loads are all issued before the first use; the RECORDS of the next full batch are requested
+    // before this batch's arithmetic (they do not depend on it), which takes one shared-memory round trip out of every batch
+    auto batch = [&](auto nb, uint4 (&A)[decltype(nb)::value], uint4 (&B)[decltype(nb)::value], uint32_t next_rec, auto prefetch) {
         constexpr int N = decltype(nb)::value;
-        uint4 A[N], B[N];
-#pragma unroll
-        for (int b = 0; b < N; ++b) {
-            A[b] = lds128u(rec + b * kRec);
-            if (NG > 3) B[b] = lds128u(rec + b * kRec + 16);
-        }
+        constexpr bool kPrefetch = decltype(prefetch)::value;
         double p0[N], p1[N];
         V2 m[N][NG > 0 ? NG : 1];
 #pragma unroll
@@ -197,6 +210,13 @@ __device__ __noinline__ void res_sum(uint32_t blk, const uint4 a, const uint4 b4
             if (NG > 1) m[b][1] = lds128(Sb + A[b].z);
             if (NG > 2) m[b][2] = lds128(Sb + A[b].w);
             if (NG > 3) m[b][3] = lds128(Sb + B[b].x);
+        }
+        if (kPrefetch) {
+#pragma unroll
+            for (int b = 0; b < N; ++b) {
+                A[b] = lds128u(next_rec + b * kRec);
+                if (NG > 3) B[b] = lds128u(next_rec + b * kRec + 16);
+            }
         }
 #pragma unroll
         for (int b = 0; b < N; ++b) {
@@ -217,14 +237,35 @@ __device__ __noinline__ void res_sum(uint32_t blk, const uint4 a, const uint4 b4
                 acc.x = 0.0; acc.y = 0.0;
             }
         }
-        rec += N * kRec;
     };
+    auto load_records = [&](auto nb, uint4 (&A)[decltype(nb)::value], uint4 (&B)[decltype(nb)::value]) {
+#pragma unroll
+        for (int b = 0; b < decltype(nb)::value; ++b) {
+            A[b] = lds128u(rec + b * kRec);
+            if (NG > 3) B[b] = lds128u(rec + b * kRec + 16);
+        }
+    };
+    if (n >= BATCH) {
+        uint4 A[BATCH], B[BATCH];
+        load_records(std::integral_constant<int, BATCH>(), A, B);
 #pragma unroll 1
-    for (; n >= BATCH; n -= BATCH) batch(std::integral_constant<int, BATCH>());
+        for (; n >= BATCH; n -= BATCH) {
+            const uint32_t cur = rec;
+            rec += BATCH * kRec;
+            // the last full batch re-reads its own records (valid addresses, values unused) instead of branching
+            batch(std::integral_constant<int, BATCH>(), A, B, n >= 2 * BATCH ? rec : cur, std::true_type());
+        }
+    }
     if constexpr (BATCH > 1) {
 #pragma unroll 1
-        for (; n > 0; --n) batch(std::integral_constant<int, 1>());
+        for (; n > 0; --n) {
+            uint4 A[1], B[1];
+            load_records(std::integral_constant<int, 1>(), A, B);
+            rec += kRec;
+            batch(std::integral_constant<int, 1>(), A, B, rec, std::false_type());
+        }
     }
+    RES_STAMP(6);
 }
 
 // ops with five to seven gathers per entry (cliques with more than four neighbours): plain loop
@@ -309,6 +350,12 @@ __global__ void __launch_bounds__(MAXT * 32, 1) jt_resident_kernel(const ResDev 
     const uint32_t pat_words = (L.pat1 - L.pat0) / 4;
     for (uint32_t i = threadIdx.x; i < 2 * pat_words; i += blockDim.x) reinterpret_cast<uint32_t *>(sm + L.pat0)[i] = 0u;
     const uint32_t bars = sbase + L.bars;
+#if FBN_RES_CLOCK_BUILD
+    if (threadIdx.x == 0) {
+        for (int k = 0; k < 16; ++k) { s_clk_sum[k] = 0; s_clk_cnt[k] = 0; }
+        s_clk_t = clock64();
+    }
+#endif
     if (threadIdx.x == 0) {
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bars));
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bars + 8));
@@ -339,7 +386,9 @@ __global__ void __launch_bounds__(MAXT * 32, 1) jt_resident_kernel(const ResDev 
                 const int nb = b + 1 < R.n_blocks ? b + 1 : (next_tile < n_tiles ? 0 : -1);
                 if (nb >= 0) block_issue(sbase + (((g + 1) & 1) ? L.buf1 : L.buf0), R.blob + boff[nb], boff[nb + 1] - boff[nb], bars + 8 * ((g + 1) & 1));
             }
+            RES_STAMP(0);
             block_wait(bars + 8 * (g & 1), (g >> 1) & 1);
+            RES_STAMP(1);
             if (kResClock && R.clk && blockIdx.x == 0 && threadIdx.x == 0 && g < 2048) R.clk[4 * g + 1] = clock64();
             const uint32_t blk = sbase + ((g & 1) ? L.buf1 : L.buf0);
             const uint4 hdr = lds128u(blk);   // n_items, -, items_off, bytes
@@ -350,6 +399,7 @@ __global__ void __launch_bounds__(MAXT * 32, 1) jt_resident_kernel(const ResDev 
             // planner's static lists: 228-238 M ALARM cases/s against 258-268 M, the counter serialises the warps at every block start)
             for (uint32_t i = i0; i < i1; ++i) {
                 const uint32_t ia = blk + hdr.z + i * 32;
+                RES_STAMP(2);
                 const uint4 a = lds128u(ia), b4 = lds128u(ia + 16);
                 const uint32_t kind = a.x & 255u, ng = a.x >> 8;
                 if (kind == RES_SUM || kind == RES_SUMC) {
@@ -371,20 +421,35 @@ __global__ void __launch_bounds__(MAXT * 32, 1) jt_resident_kernel(const ResDev 
                 }
             }
             if (kResClock && R.clk && blockIdx.x == 0 && threadIdx.x == 0 && g < 2048) R.clk[4 * g + 2] = clock64();
+            RES_STAMP(7);
             __syncthreads();
+            RES_STAMP(8);
         }
     }
+#if FBN_RES_CLOCK_BUILD
+    if (R.clk && blockIdx.x == 0 && threadIdx.x == 0)
+        for (int k = 0; k < 16; ++k) { R.clk[8100 + k] = s_clk_sum[k]; R.clk[8120 + k] = s_clk_cnt[k]; }
+#endif
 }
 
 // ---- launch helpers (called from capi.cu) ------------------------------------------------------------------------
 static int res_maxt(int warps) { return warps <= 8 ? 8 : (warps <= 16 ? 16 : (warps <= 24 ? 24 : 32)); }
 
+template <int MAXT>
+static cudaError_t res_prep(int smem_optin) {
+    cudaFuncAttributes fa;
+    cudaError_t e = cudaFuncGetAttributes(&fa, jt_resident_kernel<MAXT>);
+    if (e != cudaSuccess) return e;
+    // per function and per context: the device's opt-in maximum minus the kernel's static shared memory (none in product builds)
+    return cudaFuncSetAttribute(jt_resident_kernel<MAXT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin - (int)fa.sharedSizeBytes);
+}
+
 cudaError_t resident_prepare(int warps, int smem_optin) {
     switch (res_maxt(warps)) {
-        case 8: return cudaFuncSetAttribute(jt_resident_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin);
-        case 16: return cudaFuncSetAttribute(jt_resident_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin);
-        case 24: return cudaFuncSetAttribute(jt_resident_kernel<24>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin);
-        default: return cudaFuncSetAttribute(jt_resident_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin);
+        case 8: return res_prep<8>(smem_optin);
+        case 16: return res_prep<16>(smem_optin);
+        case 24: return res_prep<24>(smem_optin);
+        default: return res_prep<32>(smem_optin);
     }
 }
 
