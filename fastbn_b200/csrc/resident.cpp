@@ -197,6 +197,10 @@ void build_resident(const HostPlan &P, int warps, int64_t smem_limit, ResidentPl
     // the live ranges above are in PHASES; blocks follow the phase order and an OUT item runs in the block after its marginal
     // op's, i.e. not later than phase + 1 of the range. (A skipped empty phase only shortens the distance.)
     R.n_blocks = (int)blk_ops.size();
+    // a CTA barrier per phase: deep trees with little to sum per level (a chain of small cliques) are better off with one warp
+    // per tile (jt_flat_kernel). ALARM: 166 view entries per phase
+    const int64_t kMinWork = getenv("FBN_RES_MIN_WORK") ? atoll(getenv("FBN_RES_MIN_WORK")) : 48;   // tests force small nets through with 0
+    if (P.view_entries < kMinWork * R.n_blocks) return fail("too little work per phase for a CTA: " + std::to_string(P.view_entries) + " view entries in " + std::to_string(R.n_blocks) + " phases");
     std::vector<std::vector<Piece>> pieces((size_t)R.n_blocks);
     std::vector<double> work((size_t)R.n_blocks, 0.0);
     for (int b = 0; b < R.n_blocks; ++b) {
@@ -206,7 +210,7 @@ void build_resident(const HostPlan &P, int warps, int64_t smem_limit, ResidentPl
     // not the last block: the next tile's lambda rows are written there, from the patterns the EVID item has loaded
     const int evid_block = (int)(std::max_element(work.begin(), work.end() - 1) - work.begin());
     work[(size_t)evid_block] += kEvidCost;
-    static const double kGrain = getenv("FBN_RES_GRAIN") ? atof(getenv("FBN_RES_GRAIN")) : 200.0;   // measured on B200 (ALARM, 24 warps): 60 -> 264, 120 -> 264, 200 -> 268 M cases/s
+    const double kGrain = getenv("FBN_RES_GRAIN") ? atof(getenv("FBN_RES_GRAIN")) : 200.0;   // measured on B200 (ALARM, 24 warps): 60 -> 264, 120 -> 264, 200 -> 268 M cases/s
     for (int b = 0; b < R.n_blocks; ++b) {
         const double grain = std::max(kGrain, work[(size_t)b] / warps / 2.0);   // aimed cost of a piece
         for (int o : blk_ops[(size_t)b]) {

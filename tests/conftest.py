@@ -9,6 +9,12 @@ if ROOT not in sys.path:
 GOLDEN = os.path.join(ROOT, "tests", "golden")
 
 
+# the resident-tile planner declines trees with little work per phase (jt_flat_kernel is faster there); the tests want the tiny
+# brute-force nets to go through jt_resident_kernel as well (read at plan creation by fastbn_b200/csrc/resident.cpp; the tests of
+# the rule itself remove it).
+os.environ.setdefault("FBN_RES_MIN_WORK", "0")
+
+
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
 

@@ -241,3 +241,26 @@ def test_resident_and_flat_kernels_agree(alarm_tree, monkeypatch):
     for lab, post in ((l1, p1), (l2, p2)):
         assert np.nanmax(np.abs(post - g["post"])) <= TOL and np.array_equal(lab, g["labels"])
     assert np.nanmax(np.abs(p1 - p2)) <= 1e-12
+
+
+def test_deep_chain_runs_the_flat_kernel(tmp_path, monkeypatch):
+    """a small tree the resident planner declines (a chain of 150 small cliques: one CTA barrier per level): AUTO falls back to
+    jt_flat_kernel; results against the CPU oracle"""
+    from fastbn_b200 import hostapi
+    monkeypatch.delenv("FBN_RES_MIN_WORK", raising=False)
+    var_dims, parents, cpts = synth.window_network(150, (2, 3), 1, 1, 21)
+    xml = str(tmp_path / "chain.xml")
+    synth.write_xmlbif(xml, var_dims, parents, cpts)
+    m = hostapi.HostModel(xml)
+    tree = m.tree()
+    m.close()
+    off, ev, ew = synth.uniform_evidence(tree["var_dims"], 3000, 20, seed=3)
+    p = capi.Plan(tree, device=0)
+    assert p.info.flat_records == 1
+    labels, post, _ = p.run(off, ev, ew)
+    p.close()
+    o = jtoracle.Oracle(tree)
+    want, wlab = o.run_batch(off, ev, ew)
+    o.close()
+    assert np.array_equal(np.isnan(post), np.isnan(want))
+    assert np.nanmax(np.abs(post - want)) <= TOL and np.array_equal(labels, wlab)

@@ -228,3 +228,23 @@ def test_resident_plan_odd_evidence_and_eligibility(alarm_tree):
     t["clique_potentials"] = alarm_tree["clique_potentials"] * 1e-40   # unnormalised messages could underflow: not eligible
     with pytest.raises(ValueError, match="range of a double"):
         emu.run_resident(t, 16, off, ev, ew)
+
+
+def test_resident_plan_declines_deep_chains(tmp_path, monkeypatch):
+    """a chain of 150 small cliques: one CTA barrier per tree level would dominate -> not eligible, jt_flat_kernel runs such trees"""
+    from fastbn_b200 import hostapi, synth
+    monkeypatch.delenv("FBN_RES_MIN_WORK", raising=False)
+    var_dims, parents, cpts = synth.window_network(150, (2, 3), 1, 1, 21)
+    xml = str(tmp_path / "chain.xml")
+    synth.write_xmlbif(xml, var_dims, parents, cpts)
+    m = hostapi.HostModel(xml)
+    tree = m.tree()
+    m.close()
+    off, ev, ew = synth.uniform_evidence(tree["var_dims"], 8, 20, seed=3)
+    with pytest.raises(ValueError, match="too little work per phase"):
+        emu.run_resident(tree, 24, off, ev, ew)
+    post, lab, _ = emu.run(tree, 1, off, ev, ew)   # the flat plan of the same tree against the oracle
+    o = jtoracle.Oracle(tree)
+    want, wlab = o.run_batch(off, ev, ew)
+    o.close()
+    assert np.nanmax(np.abs(post - want)) <= 1e-9 and np.array_equal(lab, wlab)
