@@ -27,6 +27,57 @@ def uniform_evidence(var_dims, n_cases, n_evidence, seed, sort_vars=True):
     return ev_off, ev_vars.reshape(-1), ev_vals.reshape(-1).astype(np.int32)
 
 
+def read_xmlbif(path):
+    """(var_dims, parents, cpts) of an XMLBIF file as the reference reads it: variables in file order, <TABLE> with the FOR variable
+    most significant, then the <GIVEN>s in file order (src/XMLBIFParser.cpp). Probabilities as printed (no count truncation /
+    smoothing: used for sampling only)."""
+    import xml.etree.ElementTree as ET
+    net = ET.parse(path).getroot().find("NETWORK")
+    names, dims = [], []
+    for v in net.findall("VARIABLE"):
+        names.append(v.find("NAME").text.strip())
+        dims.append(len(v.findall("VALUE")) or len(v.findall("OUTCOME")))
+    idx = {nm: i for i, nm in enumerate(names)}
+    parents, cpts = [None] * len(names), [None] * len(names)
+    for pr in list(net.findall("PROBABILITY")) + list(net.findall("DEFINITION")):
+        v = idx[pr.find("FOR").text.strip()]
+        pa = [idx[g.text.strip()] for g in pr.findall("GIVEN")]
+        tab = np.array([float(x) for x in pr.find("TABLE").text.split()], np.float64)
+        parents[v] = pa
+        cpts[v] = tab.reshape(dims[v], -1)
+    return np.array(dims, np.int32), parents, cpts
+
+
+def forward_sampled_evidence(xml_path, n_cases, n_evidence, seed):
+    """SURVEY.md 8(d) config 2, second set: every case is a forward sample of the network (ancestral order), of which n_evidence
+    distinct non-query variables (uniform from 1..n-1, sorted) are observed. Returns (ev_off, ev_vars, ev_vals)."""
+    var_dims, parents, cpts = read_xmlbif(xml_path)
+    n = len(var_dims)
+    rng = np.random.Generator(np.random.MT19937(seed))
+    state = np.full((n_cases, n), -1, np.int64)
+    done = np.zeros(n, bool)
+    while not done.all():
+        progressed = False
+        for v in range(n):
+            if done[v] or not all(done[p] for p in parents[v]):
+                continue
+            cfg = np.zeros(n_cases, np.int64)
+            for p in parents[v]:  # first GIVEN most significant
+                cfg = cfg * int(var_dims[p]) + state[:, p]
+            cdf = np.cumsum(cpts[v][:, cfg], axis=0)  # (dim, n_cases)
+            u = rng.random(n_cases) * cdf[-1]
+            state[:, v] = np.minimum((u[None, :] >= cdf).sum(axis=0), int(var_dims[v]) - 1)
+            done[v] = progressed = True
+        if not progressed:
+            raise ValueError("cycle in the network")
+    n_evidence = int(min(n_evidence, n - 1))
+    keys = rng.random((n_cases, n - 1))
+    ev_vars = (np.sort(np.argpartition(keys, n_evidence - 1, axis=1)[:, :n_evidence], axis=1) + 1).astype(np.int32)
+    ev_vals = np.take_along_axis(state, ev_vars.astype(np.int64), axis=1).astype(np.int32)
+    ev_off = np.arange(n_cases + 1, dtype=np.int64) * n_evidence
+    return ev_off, ev_vars.reshape(-1), ev_vals.reshape(-1)
+
+
 def write_libsvm(path, ev_off, ev_vars, ev_vals, labels=None):
     """'label idx:val idx:val ... \\n' per case (trailing space like the shipped files; src/Dataset.cpp:162-262)."""
     n = len(ev_off) - 1

@@ -264,3 +264,25 @@ def test_deep_chain_runs_the_flat_kernel(tmp_path, monkeypatch):
     o.close()
     assert np.array_equal(np.isnan(post), np.isnan(want))
     assert np.nanmax(np.abs(post - want)) <= TOL and np.array_equal(labels, wlab)
+
+
+def test_forward_sampled_set_10k_against_oracle(alarm_tree):
+    """the second evidence set (values forward-sampled from the network, seed 20260102) and the parity
+    subset of the first 10 000 cases through the oracle: labels bit-identical, posteriors <= 1e-9"""
+    off, ev, ew = synth.forward_sampled_evidence(os.path.join(GOLDEN, "alarm", "alarm.xml"), 10000, 7, 20260102)
+    p = capi.Plan(alarm_tree, device=0)
+    labels, post, _ = p.run(off, ev, ew)
+    p.close()
+    o = jtoracle.Oracle(alarm_tree)
+    want, wlab = o.run_batch(off, ev, ew)
+    o.close()
+    assert not np.isnan(post).any()   # a forward sample never has probability zero
+    assert np.max(np.abs(post - want)) <= TOL and np.array_equal(labels, wlab)
+    off, ev, ew = synth.uniform_evidence(alarm_tree["var_dims"], 10000, 7, seed=20260101)   # the first set
+    p = capi.Plan(alarm_tree, device=0)
+    labels, post, _ = p.run(off, ev, ew)
+    p.close()
+    o = jtoracle.Oracle(alarm_tree)
+    want, wlab = o.run_batch(off, ev, ew)
+    o.close()
+    assert np.nanmax(np.abs(post - want)) <= TOL and np.array_equal(labels, wlab)

@@ -248,3 +248,22 @@ def test_resident_plan_declines_deep_chains(tmp_path, monkeypatch):
     want, wlab = o.run_batch(off, ev, ew)
     o.close()
     assert np.nanmax(np.abs(post - want)) <= 1e-9 and np.array_equal(lab, wlab)
+
+
+def test_forward_sampled_evidence_set(alarm_tree):
+    """the second evidence set of SURVEY.md 8(d) config 2 (forward samples of the network): 7 distinct non-query variables per case,
+    states inside the domains, typical evidence (no case of probability zero); flat and resident plans against the oracle"""
+    from fastbn_b200 import synth
+    from conftest import GOLDEN
+    import os
+    off, ev, ew = synth.forward_sampled_evidence(os.path.join(GOLDEN, "alarm", "alarm.xml"), 600, 7, 20260102)
+    assert np.array_equal(np.diff(off), np.full(600, 7))
+    e2 = ev.reshape(600, 7)
+    assert (np.diff(e2, axis=1) > 0).all() and e2.min() >= 1 and e2.max() <= 36
+    assert (ew >= 0).all() and (ew < alarm_tree["var_dims"][ev]).all()
+    o = jtoracle.Oracle(alarm_tree)
+    want, wlab = o.run_batch(off, ev, ew)
+    o.close()
+    assert not np.isnan(want).any()
+    for post, lab in (emu.run(alarm_tree, 1, off, ev, ew)[:2], emu.run_resident(alarm_tree, 24, off, ev, ew)[:2]):
+        assert np.max(np.abs(post - want)) <= 1e-9 and np.array_equal(lab, wlab)
