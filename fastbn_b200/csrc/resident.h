@@ -1,4 +1,4 @@
-// Resident-tile plan: small trees whose LIVE messages of a 64-case tile fit into one SM's shared memory (ALARM: 169 KB).
+// Resident-tile plan: small trees whose LIVE messages of a 64-case tile fit into one SM's shared memory (ALARM: 174 KB).
 // jt_resident_kernel (resident_kernel.cu) then runs a tile with one CTA per SM and never touches HBM between the evidence
 // it reads and the posteriors it writes: message rows live in shared memory, and the per-tree constants of a phase (work
 // items, per-entry records, potentials) are streamed into a double-buffered shared-memory block by cp.async.bulk (TMA) while
@@ -26,7 +26,7 @@
 
 namespace fbn {
 
-enum ResItemKind : uint32_t { RES_SUM = 0, RES_OUT = 1, RES_EVID = 2, RES_SUMC = 3 /* SUM with per-target factor tables */ };
+enum ResItemKind : uint32_t { RES_SUM = 0, RES_OUT = 1, RES_EVID = 2, RES_SUMC = 3 /* SUM whose op checks target variables against the evidence */ };
 
 // Block of one phase (uint32 words; all *_off are BYTE offsets from the block start unless they say "state"):
 //   [0] n_items  [1] 0  [2] items_off  [3] block_bytes
@@ -61,7 +61,7 @@ struct ResidentPlan {
     bool ok = false;
     std::string why;                 // why the tree is not eligible (ok == false)
     int warps = 0;                   // warps per CTA the schedule was made for
-    int n_blocks = 0;                // phases of the flat plan + 1 (the last block holds the OUT items of the last phase)
+    int n_blocks = 0;                // phases of the flat plan with needed ops + 1 (the last block holds the OUT items of the last phase)
     int state_rows = 0;              // shared-memory rows of the tile state (high-water mark of the live rows)
     int max_block_bytes = 0;
     std::vector<uint32_t> blob;      // all blocks, each 16-byte aligned
@@ -103,7 +103,7 @@ struct ResDev {
     const uint32_t *block_off;     // [n_blocks + 1]
     const VarInfo *vars;
     const ResLam *lams;
-    long long *clk;                // developer knob FBN_RES_CLOCK: CTA 0 records clock64() at every block boundary of its first tiles
+    long long *clk;                // developer builds (-DFBN_RES_CLOCK_BUILD=1) with FBN_RES_CLOCK=1: cycle stamps of CTA 0, else NULL
     int32_t n_blocks, n_vars, sum_dims, query_var, n_lams;
     ResSmem L;
 };

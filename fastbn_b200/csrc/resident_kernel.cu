@@ -1,13 +1,13 @@
 // jt_resident_kernel: the junction-tree pipeline of SMALL trees with the whole tile state in shared memory (resident.h).
 //   One CTA per SM, persistent over tiles of 64 test cases (lane = 2 cases, 128-bit rows as everywhere, plan.h). The tile's
-//   live message rows (up messages, down ratios, 1/norm rows, unnormalised marginals) never leave shared memory; HBM sees the
+//   live message rows (up messages, down ratios, unnormalised marginals) never leave shared memory; HBM sees the
 //   evidence coming in and the posteriors going out and nothing else. The constants of a phase (static per-warp work lists,
 //   per-entry records, pattern-folded potentials) arrive as ONE block per phase through cp.async.bulk + mbarrier (TMA) into a
 //   double buffer, requested one phase ahead, so the inner loop is: one broadcast LDS.128 (record), per-case LDS.64
 //   (potential under the case's evidence pattern), one LDS.128 per gathered message row, multiply-add.
 //   Same SumOps and the same arithmetic order per target as jt_flat_kernel (flat_kernel.cu): collect (reference
 //   src/JunctionTree.cpp:829-941, :1056-1148), distribute (:700-816, :1150-1238; division done algebraically), marginals
-//   (:1392-1454), Normalize (PotentialTableBase.cpp:433-445) as a 1/sum row, ArgMax (Inference.cpp:92-102).
+//   (:1392-1454), Normalize (PotentialTableBase.cpp:433-445) once, on the final marginals (resident.h), ArgMax (Inference.cpp:92-102).
 #include <cstdint>
 #include <type_traits>
 
