@@ -16,6 +16,6 @@ python bench.py > gpurun_out/${tag}_bench_all_configs.json 2> gpurun_out/${tag}_
 python - <<P
 import json
 d=json.load(open("gpurun_out/${tag}_bench_all_configs.json"))
-print("ALARM", d["value"], "e2e", d["e2e"]["value"], "labels-only", d["e2e"]["labels_only"]["value"], d["roofline"]["frac"], (d["roofline"].get("on_chip") or {}).get("frac"), d["parity_prefix"]["ok"])
+print("ALARM", d["value"], "e2e", d["e2e"]["value"], "full posteriors", d["e2e"]["full_posteriors"]["value"], d["roofline"]["frac"], (d["roofline"].get("on_chip") or {}).get("frac"), d["parity_prefix"]["ok"])
 for k,v in d["workloads"].items(): print(k, v["value"], v["e2e"]["value"], v["dram_frac"], v["parity_prefix"]["ok"])
 P
