@@ -23,16 +23,9 @@ namespace {
 #ifndef FBN_FLAT_BATCH
 #define FBN_FLAT_BATCH 2   // measured on B200 (ALARM, 64 registers x 32 warps per SM): batch 2 158 M cases/s, batch 4 (spills) 125 M
 #endif
-#ifndef FBN_FLAT_GUARD
-// The 0 guard of TableDivision (PotentialTable.cpp:718-734: ratio = 0 where the child's up message is 0) is NOT applied by
-// this kernel. A down ratio is only ever multiplied into entries of the child's clique (and into the child's up message for a
-// separator marginal): where the up message entry is 0, every one of those entries is already 0 (a sum of non-negative terms),
-// so the guarded and the unguarded ratio give the same finite products; targets the evidence itself rules out are zeroed by
-// the per-target evidence check of distribute views (plan.cpp, cmask). The guard costs one dependent 128-bit load per target
-// and a select per case: ALARM 151 M -> 172 M cases/s without it (B200, round 2). The fused and level kernels keep the guard
-// (ops.cuh, store_unit); oracle/plan_emu.cpp mirrors both. -DFBN_FLAT_GUARD=1 brings it back.
-#define FBN_FLAT_GUARD 0
-#endif
+// The 0 guard of TableDivision is not applied by any kernel (plan.h): the down ratios of targets the evidence rules out are zeroed
+// by the per-target evidence check of distribute views (finish_target). Without the guard's dependent load per target: ALARM
+// 151 M -> 172 M cases/s (B200, round 2).
 // records per batch: their loads are all issued before the first use. Ops with many gathers per entry take smaller batches
 // (the gathered vectors of a batch live in registers: batch x gathers x 2*kW registers).
 template <int NG>
@@ -52,12 +45,8 @@ __device__ __forceinline__ void flat_sum(const DevPlan &P, const SumOp &__restri
 #pragma unroll
     for (int i = 0; i < kW; ++i) potl[i] = P.pot + fx.x[i];
     const int rows = op.rows, cols = op.cols, n = rows * cols;
-    const bool guard = FBN_FLAT_GUARD && op.kind == SUM_DISTRIBUTE;
     double *dst = row_ptr(S, op.dst_row);
-    const double *aux = row_ptr(S, guard ? op.aux_row : op.dst_row);
     int r = 0, j = 0;
-    V up = vset(1.0);  // the child's up message entry of the current target, requested when the target begins (0 guard)
-    if (guard) up = ldv(aux);
     V acc = vset(0.0), nacc = vset(0.0);
     auto batch = [&](int e0, auto full) {
         constexpr bool kFull = decltype(full)::value;  // full batch: no bounds checks
@@ -91,17 +80,11 @@ __device__ __forceinline__ void flat_sum(const DevPlan &P, const SumOp &__restri
                 }
                 if (++r == rows) {  // end of target j
                     const V a = finish_target(P, op, pat, lane, j, acc, scale);
-                    V d = a;
-                    if (guard) {
-#pragma unroll
-                        for (int i = 0; i < kW; ++i) d.x[i] = (up.x[i] == 0.0) ? 0.0 : a.x[i];  // TableDivision 0 guard, PotentialTable.cpp:718-734
-                    }
-                    stv(dst + (int64_t)j * kRowDoubles, d);
+                    stv(dst + (int64_t)j * kRowDoubles, a);
                     vadd(nacc, a);
                     acc = vset(0.0);
                     r = 0;
                     ++j;
-                    if (guard) up = ldv(aux + (int64_t)min(j, cols - 1) * kRowDoubles);
                 }
             }
         }
@@ -123,7 +106,6 @@ __device__ __noinline__ void flat_sum_generic(const DevPlan &P, const SumOp &__r
     const Fx fx = op_fx(P, op, pat, lane);
     const int ng = op.ng, stride = ng > 3 ? 8 : 4;
     const int32_t *__restrict__ rec = P.flatc + op.flat_off;
-    const bool guard = FBN_FLAT_GUARD && op.kind == SUM_DISTRIBUTE;
     V nacc = vset(0.0);
     for (int j = 0; j < op.cols; ++j) {
         V acc = vset(0.0);
@@ -137,12 +119,6 @@ __device__ __noinline__ void flat_sum_generic(const DevPlan &P, const SumOp &__r
         }
         V a = finish_target(P, op, pat, lane, j, acc, scale);
         vadd(nacc, a);
-        if (guard) {
-            const V up = ldv(row_ptr(S, op.aux_row + j));
-#pragma unroll
-            for (int i = 0; i < kW; ++i)
-                if (up.x[i] == 0.0) a.x[i] = 0.0;  // TableDivision 0 guard, PotentialTable.cpp:718-734
-        }
         stv(row_ptr(S, op.dst_row + j), a);
     }
     if (op.kind == SUM_COLLECT) {

@@ -461,12 +461,6 @@ __device__ __forceinline__ V store_unit(const DevPlan &P, const SumOp &op, doubl
             const V a = finish_target(P, op, pat, lane, j, acc[c], scale);
             if (op.chunks > 1) {
                 stv(row_ptr(S, P.part_row0 + op.pslot0 + j * op.chunks + ck), a);
-            } else if (op.kind == SUM_DISTRIBUTE) {
-                const V up = ldv(row_ptr(S, op.aux_row + j));
-                V d;
-#pragma unroll
-                for (int i = 0; i < kW; ++i) d.x[i] = (up.x[i] == 0.0) ? 0.0 : a.x[i];  // TableDivision 0 guard, PotentialTable.cpp:718-734
-                stv(row_ptr(S, op.dst_row + j), d);
             } else {
                 stv(row_ptr(S, op.dst_row + j), a);
             }
@@ -532,12 +526,6 @@ __device__ __forceinline__ void fin_item(const DevPlan &P, const FinItem &F, dou
     }
     const double *pp = row_ptr(S, P.part_row0 + F.slot0);
     for (int i = 0; i < F.nslots; ++i) vadd(s, ldv(pp + (int64_t)i * kRowDoubles));
-    if (F.type == FIN_D) {
-        const V up = ldv(row_ptr(S, F.aux_row));
-#pragma unroll
-        for (int i = 0; i < kW; ++i)
-            if (up.x[i] == 0.0) s.x[i] = 0.0;
-    }
     stv(row_ptr(S, F.dst_row), s);
 }
 

@@ -225,8 +225,7 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
         auto is_target = [&](int i) { return std::find(tpos.begin(), tpos.end(), i) != tpos.end(); };
         // uncovered variables: in none of the gathered tables. Target variables of marginal views need nothing (an observed
         // variable is reported as zeros); those of collect AND distribute views are checked once per finished sum, so that a
-        // down ratio is zero wherever the evidence rules its target out even without the 0 guard of TableDivision (the flat
-        // kernel drops that guard, flat_kernel.cu).
+        // down ratio is zero wherever the evidence rules its target out: no kernel applies the 0 guard of TableDivision (plan.h).
         std::vector<int> fold_pos, cmask_pos;
         int64_t nfx = 1;
         if (c >= 0) {
@@ -236,10 +235,7 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
                 for (const GatherSrc &g : gs) covered = covered || g.tab->find(X.vars[i]) >= 0;
                 if (covered) continue;
                 if (!is_target(i)) unc.push_back(i);
-                // checked once per finished sum, not per entry. Distribute views need it only where the kernel has no 0 guard
-                // (team 1: jt_flat_kernel / jt_resident_kernel); the fused and level kernels keep the guard, which zeroes the same
-                // targets (measured on the HEPAR2 shape: the redundant checks were 14 % of the fused kernel's instructions)
-                else if (kind == SUM_COLLECT || (kind == SUM_DISTRIBUTE && team == 1 && !level)) cmask_pos.push_back(i);
+                else if (kind != SUM_MARGINAL) cmask_pos.push_back(i);  // checked once per finished sum, not per entry
             }
             std::stable_sort(unc.begin(), unc.end(), [&](int a, int b) { return X.dims[a] < X.dims[b]; });
             for (int i : unc) {
@@ -443,7 +439,7 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
         if (p != t.root) gs.push_back({&sep[up_sep[p]], dn_row(up_sep[p])});
         SumOp op = make_view(clq[p], p, tpos, gs, inv_rows_of(p), SUM_DISTRIBUTE);
         op.dst_row = dn_row(s);
-        op.aux_row = up_row(s);
+        op.aux_row = up_row(s);   // informational: no kernel applies the 0 guard (plan.h)
         dist_op[c] = (int)P.ops.size();
         P.ops.push_back(op);
         P.parent_entries += clq[p].size;
@@ -546,9 +542,9 @@ std::string build_plan(const fbn_tree_desc &t, int team, HostPlan &P, bool level
             if (chunks > 1)
                 for (int64_t j = 0; j < cols; ++j) {
                     FinItem f = FinItem();
-                    f.type = op.kind == SUM_DISTRIBUTE ? FIN_D : FIN_SUM;
+                    f.type = FIN_SUM;
                     f.dst_row = op.dst_row + (int32_t)j;
-                    f.aux_row = op.kind == SUM_DISTRIBUTE ? op.aux_row + (int32_t)j : 0;
+                    f.aux_row = 0;
                     f.slot0 = pslot0 + (int32_t)(j * chunks);
                     f.nslots = (int32_t)chunks;
                     P.fins.push_back(f);

@@ -10,8 +10,14 @@
 //                         (reference: reset + LoadEvidenceToNodes + CliqueLevelCollection + SeparatorLevelCollectionOptimized)
 //   DISTRIBUTE P -> K     targets = separator K, gathers = up messages of P's OTHER children + P's own down ratio
 //                         (reference: SeparatorLevelDistribution + CliqueLevelDistributionOptimized; the division by K's up
-//                         message is carried out algebraically: K's message is simply left out of the product, the
-//                         reference's 0 guard of TableDivision is kept on the result)
+//                         message is carried out algebraically: K's message is simply left out of the product. The
+//                         reference's 0 guard of TableDivision (PotentialTable.cpp:718-734: ratio = 0 where K's up message
+//                         is 0) is NOT applied: a down ratio is only ever multiplied into entries of K's clique and into
+//                         K's up message itself, and where the up message entry is 0 every one of those is already 0 (a sum
+//                         of non-negative terms), so the guarded and the unguarded ratio give the same finite products;
+//                         targets the evidence itself rules out are zeroed by the per-target check (cmask). The guard cost
+//                         one dependent load per target at the end of every unit: without it ALARM +14 % (flat kernel),
+//                         HEPAR2 shape +12 %, PIGS shape +9 %, MUNIN shape +6 % (B200, round 2))
 //   MARGINAL of variable v targets = {v}, source = the smallest table containing v (a clique: all child messages + its down
 //                         ratio; a separator: up message * down ratio)
 // HBM traffic per case is then the messages (sum of separator sizes) instead of the cliques (round 1: every clique entry
@@ -78,7 +84,7 @@ struct SumOp {
     int64_t perm_off;     // into idx32[]: visiting order of the column blocks, -1 = storage order
     int32_t kind;         // SumKind
     int32_t dst_row;      // scratch row of target 0: up message (root: dummy row) / down ratio / unnormalised marginal
-    int32_t aux_row;      // SUM_DISTRIBUTE: row of entry 0 of the child's up message (0 guard of TableDivision)
+    int32_t aux_row;      // SUM_DISTRIBUTE: row of entry 0 of the child's up message (informational: the 0 guard is not applied)
     int32_t inv_row;      // SUM_COLLECT: scratch row receiving 1/sum(clique)
     int32_t rows, cols;
     int32_t nfold, nfx;   // folded variables, evidence patterns per entry (1 = plain potentials)
@@ -93,9 +99,9 @@ struct SumOp {
     int32_t pad0;
 };
 
-enum FinType : int32_t { FIN_SUM = 0, FIN_NORM = 1, FIN_D = 2 };
+enum FinType : int32_t { FIN_SUM = 0, FIN_NORM = 1 };
 struct FinItem {
-    int32_t type;      // FIN_SUM: dst = sum of partials; FIN_NORM: dst = 1 / sum of the norm shares; FIN_D: dst = aux == 0 ? 0 : sum
+    int32_t type;      // FIN_SUM: dst = sum of partials; FIN_NORM: dst = 1 / sum of the norm shares
     int32_t dst_row;
     int32_t aux_row;
     int32_t slot0;     // first partial slot (FIN_NORM: normslot)

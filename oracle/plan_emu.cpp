@@ -91,8 +91,6 @@ extern "C" int emu_run(const fbn_tree_desc *tree, int team, int64_t n_cases, con
                         }
                         if (op.chunks > 1) {
                             part[op.pslot0 + j * op.chunks + ck] = acc;
-                        } else if (op.kind == SUM_DISTRIBUTE) {
-                            S[op.dst_row + j] = (!use_flat && S[op.aux_row + j] == 0.0) ? 0.0 : acc;  // TableDivision 0 guard (the flat kernel has none)
                         } else {
                             S[op.dst_row + j] = acc;
                         }
@@ -108,7 +106,6 @@ extern "C" int emu_run(const fbn_tree_desc *tree, int team, int64_t n_cases, con
                     continue;
                 }
                 for (int i = 0; i < F.nslots; ++i) s += part[F.slot0 + i];
-                if (F.type == FIN_D && S[F.aux_row] == 0.0) s = 0.0;
                 S[F.dst_row] = s;
             }
         }
