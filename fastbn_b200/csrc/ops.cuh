@@ -454,17 +454,38 @@ template <int CB>
 __device__ __forceinline__ V store_unit(const DevPlan &P, const SumOp &op, double *S, const uint8_t *pat, int lane, int j0, int nc, int ck,
                                         const V &scale, const V (&acc)[CB]) {
     V nacc = vset(0.0);
+    // the op's scale, then the evidence checks of uncovered target variables (finish_target), variable by variable: a case's
+    // pattern bytes of a checked variable are read once per unit, not once per target
+    V a[CB];
+#pragma unroll
+    for (int c = 0; c < CB; ++c) {
+        a[c] = acc[c];
+        vmul(a[c], scale);
+    }
+    const int32_t *__restrict__ cmk = P.idx32 + op.cmask_off;
+    for (int k = 0; k < op.ncmask; ++k) {
+        const int v = __ldg(cmk + k);
+        int pv[kW];
+#pragma unroll
+        for (int i = 0; i < kW; ++i) pv[i] = pat[v * kTileCases + lane * kW + i];
+#pragma unroll
+        for (int c = 0; c < CB; ++c) {
+            const int want = __ldg(cmk + op.ncmask + min(j0 + c, op.cols - 1) * op.ncmask + k);
+#pragma unroll
+            for (int i = 0; i < kW; ++i)
+                if (pv[i] != 0 && pv[i] != want) a[c].x[i] = 0.0;
+        }
+    }
 #pragma unroll
     for (int c = 0; c < CB; ++c)
         if (c < nc) {
             const int j = j0 + c;
-            const V a = finish_target(P, op, pat, lane, j, acc[c], scale);
             if (op.chunks > 1) {
-                stv(row_ptr(S, P.part_row0 + op.pslot0 + j * op.chunks + ck), a);
+                stv(row_ptr(S, P.part_row0 + op.pslot0 + j * op.chunks + ck), a[c]);
             } else {
-                stv(row_ptr(S, op.dst_row + j), a);
+                stv(row_ptr(S, op.dst_row + j), a[c]);
             }
-            vadd(nacc, a);
+            vadd(nacc, a[c]);
         }
     return nacc;
 }
