@@ -13,6 +13,9 @@
 
 namespace fbn {
 
+#ifndef FBN_POT_BCAST
+#define FBN_POT_BCAST 1
+#endif
 // unroll factor of the single-register-set row loop of the CB = 2 kernels
 #ifndef FBN_SUM_UNROLL_CB2
 #define FBN_SUM_UNROLL_CB2 2
@@ -203,6 +206,9 @@ __device__ __forceinline__ void sum_rows(const DevPlan &P, const SumOp &op, cons
                                          uint32_t next_bytes) {
     constexpr bool FOLD = POT == 2;
     constexpr bool STAGE = POT == 1 && CB >= 2 && TMA;
+    // plain potentials without staging: every lane loads the row's CB values itself (same address in all lanes: one L1 broadcast
+    // per 16 bytes, requested with the row's gathers) instead of one coalesced load per 32 / CB rows + two shuffles per value
+    constexpr bool BCAST = POT == 1 && !STAGE && CB >= 2 && FBN_POT_BCAST;
     constexpr int NGC = NG > 0 ? NG : 1;
     constexpr int NU = (UMASK & 1) + ((UMASK >> 1) & 1) + ((UMASK >> 2) & 1) + ((UMASK >> 3) & 1);
     constexpr int kLoads = (NG > 0 ? (NG - NU) * CB + NU : 0) * kW + (POT == 2 ? CB * kW / 2 : 0);  // 16-byte units per row
@@ -215,7 +221,7 @@ __device__ __forceinline__ void sum_rows(const DevPlan &P, const SumOp &op, cons
     // POT 1, cb 1: ONE coalesced load serves 32 rows, the row loop picks its value by shuffle
     constexpr int RPL = 32 / CB;
     const double *potl = pot + (int64_t)(j0 / CB) * op.rows * CB * (POT == 2 ? op.nfx : 1);   // the unit's block of potX (unit-major)
-    double potv = 1.0, potv_next = (POT == 1 && !STAGE) ? __ldg(potl + min((int64_t)r0 * CB + lane, (int64_t)r1 * CB - 1)) : 1.0;
+    double potv = 1.0, potv_next = (POT == 1 && !STAGE && !BCAST) ? __ldg(potl + min((int64_t)r0 * CB + lane, (int64_t)r1 * CB - 1)) : 1.0;
     // POT 1, cb >= 2: blocks of `sb` rows come in through shared memory (PotStage above); the copy of rows [r0, r0 + sb) was
     // started by the caller
     const int sb = STAGE ? (int)(st.buf_bytes / (CB * 8)) : 0;
@@ -235,6 +241,7 @@ __device__ __forceinline__ void sum_rows(const DevPlan &P, const SumOp &op, cons
     struct Set {
         V m[NGC][CB];
         double pv[POT == 2 ? CB : 1][kW];
+        double pc[BCAST ? CB : 1];
     };
     auto load_parts = [&](int rr, int32_t (&rp)[NGC]) {
         if (NG > 0) {
@@ -250,6 +257,15 @@ __device__ __forceinline__ void sum_rows(const DevPlan &P, const SumOp &op, cons
             for (int c = 0; c < CB; ++c)
 #pragma unroll
                 for (int i = 0; i < kW; ++i) s.pv[FOLD ? c : 0][i] = __ldg(q + c * nfx + fx.x[i]);
+        }
+        if (BCAST) {
+            const double2 *q = reinterpret_cast<const double2 *>(potl + (int64_t)min(rr, r1 - 1) * CB);
+#pragma unroll
+            for (int c = 0; c < CB; c += 2) {
+                const double2 t = __ldg(q + c / 2);
+                s.pc[BCAST ? c : 0] = t.x;
+                s.pc[BCAST ? c + 1 : 0] = t.y;
+            }
         }
         if (NG > 0) {
 #pragma unroll
@@ -279,6 +295,9 @@ __device__ __forceinline__ void sum_rows(const DevPlan &P, const SumOp &op, cons
                 pc[c] = t.x;
                 pc[c + (CB > 1 ? 1 : 0)] = t.y;
             }
+        } else if (BCAST) {
+#pragma unroll
+            for (int c = 0; c < CB; ++c) pc[c] = s.pc[BCAST ? c : 0];
         } else if (POT == 1) {
             const int rg = (r - r0) & (RPL - 1);  // row inside its group of RPL
             if (rg == 0) {
