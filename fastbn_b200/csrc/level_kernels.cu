@@ -16,6 +16,10 @@
 #include "ops.cuh"
 #include "plan.h"
 
+#ifndef FBN_LEVEL_TMA
+#define FBN_LEVEL_TMA 1   // potentials of a unit through shared memory (cp.async.bulk + mbarrier); 0: broadcast loads like the fused kernels
+#endif
+
 namespace fbn {
 
 #ifndef FBN_LVL_OCC
@@ -59,7 +63,7 @@ __global__ void __launch_bounds__(kLevelWarps * 32, FBN_LVL_OCC) lvl_sum_kernel(
         const SumOp &__restrict__ op = P.ops[P.oplist[oi]];
         int start = (gw - op.rot % GW) % GW;
         if (start < 0) start += GW;
-        const V nacc = sum_units<CB, true>(P, op, S, pat, lane, start, GW, st);
+        const V nacc = sum_units<CB, FBN_LEVEL_TMA != 0>(P, op, S, pat, lane, start, GW, st);
         if (op.kind == SUM_COLLECT) {  // this CTA's share of sum(clique): one share row per (collect op, CTA)
 #pragma unroll
             for (int i = 0; i < kW; ++i) red[warp][lane * kW + i] = nacc.x[i];
