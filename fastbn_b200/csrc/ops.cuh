@@ -316,22 +316,37 @@ __device__ __forceinline__ void sum_rows(const DevPlan &P, const SumOp &op, cons
             for (int g = 0; g < NG; ++g)
                 if ((UMASK >> g) & 1) vmul(u, s.m[g][0]);
         }
+        if constexpr (NG < 0) {
+            // more than four gathers per entry (cliques with more than three or four neighbours): gather by gather, one index load
+            // per row and one per target, 128-bit row loads (both cases of a lane at once), four loads in flight
+            V w[CB];
 #pragma unroll
-        for (int i = 0; i < kW; ++i) {
+            for (int c = 0; c < CB; ++c)
 #pragma unroll
-            for (int c = 0; c < CB; ++c) {
-                double v = (FOLD ? s.pv[FOLD ? c : 0][i] : pc[c]) * u.x[i];
-                if (NG > 0) {
+                for (int i = 0; i < kW; ++i) w[c].x[i] = (FOLD ? s.pv[FOLD ? c : 0][i] : pc[c]);
+            for (int g = 0; g < ng; ++g) {
+                const int32_t rpg = __ldg(rowpart + (int64_t)r * ng + g);
+                V m[CB];
 #pragma unroll
-                    for (int g = 0; g < NG; ++g)
-                        if (!((UMASK >> g) & 1)) v *= s.m[g][c].x[i];
-                } else if (NG < 0) {
-                    for (int g = 0; g < ng; ++g) {
-                        const int32_t row = __ldg(rowpart + (int64_t)r * ng + g) + __ldg(colpart + (int64_t)jc[c] * ng + g);
-                        v *= row_ptr(S, row)[i];
+                for (int c = 0; c < CB; ++c) m[c] = ldv(row_ptr(S, rpg + __ldg(colpart + (int64_t)jc[c] * ng + g)));
+#pragma unroll
+                for (int c = 0; c < CB; ++c) vmul(w[c], m[c]);
+            }
+#pragma unroll
+            for (int c = 0; c < CB; ++c) vadd(acc[c], w[c]);
+        } else {
+#pragma unroll
+            for (int i = 0; i < kW; ++i) {
+#pragma unroll
+                for (int c = 0; c < CB; ++c) {
+                    double v = (FOLD ? s.pv[FOLD ? c : 0][i] : pc[c]) * u.x[i];
+                    if (NG > 0) {
+#pragma unroll
+                        for (int g = 0; g < NG; ++g)
+                            if (!((UMASK >> g) & 1)) v *= s.m[g][c].x[i];
                     }
+                    acc[c].x[i] += v;
                 }
-                acc[c].x[i] += v;
             }
         }
     };
