@@ -13,6 +13,9 @@
 
 namespace fbn {
 
+#ifndef FBN_TWOSET_MAX
+#define FBN_TWOSET_MAX 16   // 16-byte loads per lane and row up to which the row loop keeps two register sets (B200: 12 -> 16 HEPAR2 shape +5 %, MUNIN shape +4 %, PIGS shape -1 %; 24: spills, -3..-6 %)
+#endif
 #ifndef FBN_POT_BCAST
 #define FBN_POT_BCAST 1
 #endif
@@ -212,7 +215,7 @@ __device__ __forceinline__ void sum_rows(const DevPlan &P, const SumOp &op, cons
     constexpr int NGC = NG > 0 ? NG : 1;
     constexpr int NU = (UMASK & 1) + ((UMASK >> 1) & 1) + ((UMASK >> 2) & 1) + ((UMASK >> 3) & 1);
     constexpr int kLoads = (NG > 0 ? (NG - NU) * CB + NU : 0) * kW + (POT == 2 ? CB * kW / 2 : 0);  // 16-byte units per row
-    constexpr bool kTwoSets = NG > 0 && CB >= 4 && kLoads <= 12;
+    constexpr bool kTwoSets = NG > 0 && CB >= 4 && kLoads <= FBN_TWOSET_MAX;
     const int ng = NG >= 0 ? NG : op.ng, cols = op.cols;
     constexpr bool has_pot = POT != 0;
     const double *__restrict__ pot = P.pot + (has_pot ? op.pot_off : 0);
