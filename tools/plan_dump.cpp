@@ -100,3 +100,16 @@ extern "C" int gather_stats(const fbn_tree_desc *tree) {
            entries, potless, nofold, both, rowonly, colonly, none, hoisted);
     return 0;
 }
+
+// view entries of a fused plan by gathers per entry
+extern "C" int ng_hist(const fbn_tree_desc *tree, int team) {
+    fbn::HostPlan h;
+    std::string err = fbn::build_plan(*tree, team, h, false);
+    if (!err.empty()) { fprintf(stderr, "%s\n", err.c_str()); return 1; }
+    long long e[10] = {0}, tot = 0;
+    for (const fbn::SumOp &op : h.ops) { e[std::min(op.ng, 9)] += (long long)op.rows * op.cols; tot += (long long)op.rows * op.cols; }
+    printf("view entries by gathers per entry:");
+    for (int g = 0; g < 10; ++g) if (e[g]) printf("  ng %d: %.1f%%", g, 100.0 * e[g] / tot);
+    printf("\n");
+    return 0;
+}
