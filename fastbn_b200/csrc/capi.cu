@@ -262,7 +262,7 @@ extern "C" int fbn_plan_create(const fbn_tree_desc *tree, const fbn_plan_options
             p->rd.n_lams = (int32_t)p->rp.lams.size();
             p->rd.clk = nullptr;
             if (getenv("FBN_RES_CLOCK")) {   // developer knob: cycles per block of CTA 0, printed when the plan is destroyed
-                std::vector<long long> z(4 * 2048 + 4 + 64, 0);
+                std::vector<long long> z(8300 + 32 * 32, 0);
                 const long long *dz = nullptr;
                 if ((rc = upload(p, z, &dz)) != FBN_OK) { fbn_plan_destroy(p); return rc; }
                 p->rd.clk = const_cast<long long *>(dz);
@@ -356,6 +356,17 @@ extern "C" void fbn_plan_destroy(fbn_plan *p) {
     if (p->resident && p->rd.clk) {
         std::vector<long long> c(4 * 2048);
         const int nb = p->rp.n_blocks;
+        {   // -DFBN_RES_CLOCK_BUILD=2: mean cycles per warp and block of CTA 0
+            std::vector<long long> w(1 + 32 * 32);
+            if (cudaMemcpy(w.data(), p->rd.clk + 8299, w.size() * 8, cudaMemcpyDeviceToHost) == cudaSuccess && w[0] > 0) {
+                fprintf(stderr, "FBN_RES_CLOCK per warp (CTA 0, mean over %lld tiles): cycles from the block's constants to the end of the warp's items\n", w[0]);
+                for (int b = 0; b < nb && b < 32; ++b) {
+                    fprintf(stderr, "  block %2d:", b);
+                    for (int k = 0; k < p->rp.warps; ++k) fprintf(stderr, " %5.0f", (double)w[1 + (size_t)b * 32 + k] / (double)w[0]);
+                    fprintf(stderr, "\n");
+                }
+            }
+        }
         if (cudaMemcpy(c.data(), p->rd.clk, c.size() * 8, cudaMemcpyDeviceToHost) == cudaSuccess && c[4 * (size_t)nb] != 0) {
             // tiles 1.. of CTA 0 (the first one includes the start-up), thread 0: cycles for requesting the next block + waiting
             // for this one, for warp 0's items, at the CTA barrier

@@ -22,7 +22,7 @@ namespace fbn {
 #define FBN_RES_CLOCK_BUILD 0   // developer builds (tools/build_variant.sh ... -DFBN_RES_CLOCK_BUILD=1): FBN_RES_CLOCK=1 records cycles per block
 #endif
 constexpr bool kResClock = FBN_RES_CLOCK_BUILD != 0;
-#if FBN_RES_CLOCK_BUILD
+#if FBN_RES_CLOCK_BUILD == 1
 // developer build: cycles of thread 0 of CTA 0 per segment of a phase (summed over all phases and tiles)
 __shared__ long long s_clk_t, s_clk_sum[16], s_clk_cnt[16];
 #define RES_STAMP(k)                                                     \
@@ -350,7 +350,7 @@ __global__ void __launch_bounds__(MAXT * 32, 1) jt_resident_kernel(const ResDev 
     const uint32_t pat_words = (L.pat1 - L.pat0) / 4;
     for (uint32_t i = threadIdx.x; i < 2 * pat_words; i += blockDim.x) reinterpret_cast<uint32_t *>(sm + L.pat0)[i] = 0u;
     const uint32_t bars = sbase + L.bars;
-#if FBN_RES_CLOCK_BUILD
+#if FBN_RES_CLOCK_BUILD == 1
     if (threadIdx.x == 0) {
         for (int k = 0; k < 16; ++k) { s_clk_sum[k] = 0; s_clk_cnt[k] = 0; }
         s_clk_t = clock64();
@@ -390,6 +390,9 @@ __global__ void __launch_bounds__(MAXT * 32, 1) jt_resident_kernel(const ResDev 
             block_wait(bars + 8 * (g & 1), (g >> 1) & 1);
             RES_STAMP(1);
             if (kResClock && R.clk && blockIdx.x == 0 && threadIdx.x == 0 && g < 2048) R.clk[4 * g + 1] = clock64();
+#if FBN_RES_CLOCK_BUILD == 2   // -DFBN_RES_CLOCK_BUILD=2: cycles every warp of CTA 0 needs for its items, per block (summed over tiles)
+            const long long w_t0 = clock64();
+#endif
             const uint32_t blk = sbase + ((g & 1) ? L.buf1 : L.buf0);
             const uint4 hdr = lds128u(blk);   // n_items, -, items_off, bytes
             // the last block sums nothing: the next tile's lambda rows can be written (its patterns came in an earlier block)
@@ -421,12 +424,16 @@ __global__ void __launch_bounds__(MAXT * 32, 1) jt_resident_kernel(const ResDev 
                 }
             }
             if (kResClock && R.clk && blockIdx.x == 0 && threadIdx.x == 0 && g < 2048) R.clk[4 * g + 2] = clock64();
+#if FBN_RES_CLOCK_BUILD == 2
+            if (R.clk && blockIdx.x == 0 && lane == 0 && b < 32) atomicAdd(reinterpret_cast<unsigned long long *>(R.clk) + 8300 + b * 32 + warp, (unsigned long long)(clock64() - w_t0));
+            if (R.clk && blockIdx.x == 0 && threadIdx.x == 0 && b == 0) atomicAdd(reinterpret_cast<unsigned long long *>(R.clk) + 8299, 1ull);
+#endif
             RES_STAMP(7);
             __syncthreads();
             RES_STAMP(8);
         }
     }
-#if FBN_RES_CLOCK_BUILD
+#if FBN_RES_CLOCK_BUILD == 1
     if (R.clk && blockIdx.x == 0 && threadIdx.x == 0)
         for (int k = 0; k < 16; ++k) { R.clk[8100 + k] = s_clk_sum[k]; R.clk[8120 + k] = s_clk_cnt[k]; }
 #endif
