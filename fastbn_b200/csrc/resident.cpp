@@ -297,6 +297,11 @@ void build_resident(const HostPlan &P, int warps, int64_t smem_limit, ResidentPl
                         it.dst_off = state_off(op.dst_row) + (uint32_t)q.j0 * (uint32_t)kResRowBytes;
                         it.desc_off = desc_off[q.op];
                         it.j0 = (uint32_t)q.j0;
+                        it.want_off = op.ncmask ? tab_off[q.op] + (uint32_t)q.j0 * (uint32_t)op.ncmask * 4u : 0u;
+                        it.nfold_ncm = (uint32_t)op.nfold | ((uint32_t)op.ncmask << 8);
+                        if (op.nfold > 0) { it.fold_var0 = (uint32_t)P.idx32[(size_t)op.fold_off]; it.fold_stride0 = (uint32_t)P.idx32[(size_t)op.fold_off + 1] * 8u; }
+                        if (op.nfold > 1) { it.fold_var1 = (uint32_t)P.idx32[(size_t)op.fold_off + 2]; it.fold_stride1 = (uint32_t)P.idx32[(size_t)op.fold_off + 3] * 8u; }
+                        for (int k = 0; k < kResMaxChecks; ++k) it.chk[k] = op.ncmask ? (uint32_t)P.idx32[(size_t)(op.cmask_off + std::min(k, op.ncmask - 1))] : 0u;
                     } else if (q.kind == RES_OUT) {
                         const VarInfo vi = P.vars[(size_t)q.op];
                         it.kind_ng = RES_OUT;

@@ -31,7 +31,7 @@ enum ResItemKind : uint32_t { RES_SUM = 0, RES_OUT = 1, RES_EVID = 2, RES_SUMC =
 // Block of one phase (uint32 words; all *_off are BYTE offsets from the block start unless they say "state"):
 //   [0] n_items  [1] 0  [2] items_off  [3] block_bytes
 //   [4 .. 4 + warps]  warp_begin[w]: first item of warp w (items of a warp are adjacent), warp_begin[warps] = n_items
-//   items    : ResItem (32 B each)
+//   items    : ResItem (64 B each)
 //   descs    : per op {nfold, ncm, want_off, 0} + nfold x {variable, pattern stride in BYTES} + ncm checked target variables,
 //              padded to 16 bytes; want_off -> cols x ncm words: the pattern byte (1 + state) target j has of checked variable k
 //   records  : per entry, target-major: int4 {pot_off, state offsets of gathers 0..2} (+ int4 {gathers 3..6} when the op has
@@ -45,8 +45,17 @@ struct ResItem {
     uint32_t dst_off;    // SUM: state offset of the first target. OUT: state offset of the unnormalised marginal of state 0
     uint32_t desc_off;   // SUM: the op's descriptor
     uint32_t j0;         // SUM: first target of the piece
-    uint32_t pad1;
+    uint32_t want_off;   // SUM with checks: the want words of target j0 (ncm per target), else 0
+    // what the kernel needs of the descriptor before its first record, so that an item's set-up is ONE round of shared-memory
+    // loads (item, then pattern bytes) instead of a chain of five (item -> descriptor -> fold pair -> pattern byte, twice):
+    uint32_t nfold_ncm;     // folded variables | checked variables << 8
+    uint32_t fold_var0;     // the first two folded variables and their strides in BYTES (stride 0: none); ops that fold more
+    uint32_t fold_stride0;  // than two go through the descriptor
+    uint32_t fold_var1;
+    uint32_t fold_stride1;
+    uint32_t chk[3];        // checked target variables; unused slots repeat a valid variable (their loads are unconditional)
 };
+static_assert(sizeof(ResItem) == 64, "ResItem is four 16-byte words");
 
 constexpr int kResMaxChecks = 3;   // checked target variables per op the kernel keeps in registers
 constexpr int kResRowBytes = kRowDoubles * 8;   // bytes of one state row (64 cases)

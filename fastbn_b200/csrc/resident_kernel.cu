@@ -165,29 +165,30 @@ __device__ __noinline__ uint2 res_fold(uint32_t blk, uint32_t desc, uint32_t pat
 // a CTA run different kinds at the same time (a first version with one fully unrolled body per (gathers, remainder, checks)
 // was 380 KB of SASS and lost 13 % of the warp time to instruction fetches).
 template <int NG, int BATCH>
-__device__ __noinline__ void res_sum(uint32_t blk, const uint4 a, const uint4 b4, uint32_t Sb, uint32_t patl, bool cm) {
+__device__ __noinline__ void res_sum(uint32_t blk, const uint4 a, const uint4 b4, const uint4 c4, const uint4 d4, uint32_t Sb, uint32_t patl) {
     constexpr uint32_t kRec = NG > 3 ? 32u : 16u;
-    const uint32_t rows = a.w, desc = blk + b4.y;
+    const uint32_t rows = a.w;
     uint32_t n = a.z * rows, dst = Sb + b4.x;
     RES_STAMP(3);
-    const uint2 pots = res_fold(blk, desc, patl);
+    // set-up from the item alone (resident.h): the pattern bytes of the first two folded variables and of the (at most
+    // kResMaxChecks) checked target variables are requested together; unused slots name a valid variable and are masked
+    const uint32_t nfold = c4.x & 255u, ncm = c4.x >> 8;
+    const uint32_t f0 = lds16(patl + c4.y * kTileCases), f1 = lds16(patl + c4.w * kTileCases);
+    const uint32_t k0 = lds16(patl + d4.y * kTileCases), k1 = lds16(patl + d4.z * kTileCases), k2 = lds16(patl + d4.w * kTileCases);
+    // this lane's pattern slots of the op's potentials (one per case): block base + sum over the folded variables of pattern x stride
+    uint32_t pot0 = blk + (f0 & 255u) * c4.z + (f1 & 255u) * d4.x, pot1 = blk + (f0 >> 8) * c4.z + (f1 >> 8) * d4.x;
+    if (nfold > 2) {
+        const uint2 pots = res_fold(blk, blk + b4.y, patl);
+        pot0 = pots.x; pot1 = pots.y;
+    }
     RES_STAMP(4);
-    const uint32_t pot0 = pots.x, pot1 = pots.y;
     // (measured and rejected: one potential load for both cases when the view has no folded variable, 4 of 5 ALARM entries:
     // the warp-uniform branch costs more than the load, 256 against 268 M cases/s)
     uint32_t rec = blk + a.y, r = 0;
-    // checked target variables (at most kResMaxChecks): this lane's two pattern bytes of each, read once per item; per finished
-    // target the byte the target wants (a word per target and variable); cw = 0: no checks
-    uint32_t cw = 0, ncm = 0, c0 = 0, c1 = 0, c2 = 0;
-    if (cm) {
-        const uint4 h = lds128u(desc);   // nfold, ncm, want_off
-        ncm = h.y;
-        const uint32_t cv = desc + 16 + 8 * h.x;
-        cw = blk + h.z + b4.z * ncm * 4;
-        c0 = lds16(patl + lds32(cv) * kTileCases);
-        if (ncm > 1) c1 = lds16(patl + lds32(cv + 4) * kTileCases);
-        if (ncm > 2) c2 = lds16(patl + lds32(cv + 8) * kTileCases);
-    }
+    // checked target variables: this lane's two pattern bytes of each, read once per item; per finished target the byte the
+    // target wants (a word per target and variable); cw = 0: no checks
+    uint32_t cw = ncm ? blk + b4.w : 0u;
+    const uint32_t c0 = ncm > 0 ? k0 : 0u, c1 = ncm > 1 ? k1 : 0u, c2 = ncm > 2 ? k2 : 0u;
     RES_STAMP(5);
     auto check = [&](uint32_t c, uint32_t want, V2 &x) {
         const uint32_t q0 = c & 255u, q1 = c >> 8;
@@ -401,18 +402,18 @@ __global__ void __launch_bounds__(MAXT * 32, 1) jt_resident_kernel(const ResDev 
             // (measured and rejected: the warps taking the items from a queue, an atomic counter in shared memory, instead of the
             // planner's static lists: 228-238 M ALARM cases/s against 258-268 M, the counter serialises the warps at every block start)
             for (uint32_t i = i0; i < i1; ++i) {
-                const uint32_t ia = blk + hdr.z + i * 32;
+                const uint32_t ia = blk + hdr.z + i * (uint32_t)sizeof(ResItem);
                 RES_STAMP(2);
-                const uint4 a = lds128u(ia), b4 = lds128u(ia + 16);
+                const uint4 a = lds128u(ia), b4 = lds128u(ia + 16), c4 = lds128u(ia + 32), d4 = lds128u(ia + 48);
                 const uint32_t kind = a.x & 255u, ng = a.x >> 8;
                 if (kind == RES_SUM || kind == RES_SUMC) {
                     const bool cm = kind == RES_SUMC;   // with per-target evidence checks
                     switch (ng) {
-                        case 0: res_sum<0, ResBatch<0, MAXT>::value>(blk, a, b4, Sb, patl, cm); break;
-                        case 1: res_sum<1, ResBatch<1, MAXT>::value>(blk, a, b4, Sb, patl, cm); break;
-                        case 2: res_sum<2, ResBatch<2, MAXT>::value>(blk, a, b4, Sb, patl, cm); break;
-                        case 3: res_sum<3, ResBatch<3, MAXT>::value>(blk, a, b4, Sb, patl, cm); break;
-                        case 4: res_sum<4, ResBatch<4, MAXT>::value>(blk, a, b4, Sb, patl, cm); break;
+                        case 0: res_sum<0, ResBatch<0, MAXT>::value>(blk, a, b4, c4, d4, Sb, patl); break;
+                        case 1: res_sum<1, ResBatch<1, MAXT>::value>(blk, a, b4, c4, d4, Sb, patl); break;
+                        case 2: res_sum<2, ResBatch<2, MAXT>::value>(blk, a, b4, c4, d4, Sb, patl); break;
+                        case 3: res_sum<3, ResBatch<3, MAXT>::value>(blk, a, b4, c4, d4, Sb, patl); break;
+                        case 4: res_sum<4, ResBatch<4, MAXT>::value>(blk, a, b4, c4, d4, Sb, patl); break;
                         default: res_sum_generic(blk, a, b4, Sb, patl, ng, cm); break;
                     }
                 } else if (kind == RES_OUT) {

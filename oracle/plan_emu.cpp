@@ -192,9 +192,21 @@ extern "C" int emu_run_resident(const fbn_tree_desc *tree, int warps, int64_t sm
                         continue;
                     }
                     const uint32_t *fd = reinterpret_cast<const uint32_t *>(bytes + I.desc_off);
+                    // the item repeats what the kernel needs of the descriptor (resident.h): both must say the same, and the
+                    // emulator reads what the kernel reads (the item, unless the op folds more than two variables)
+                    const uint32_t ncm = fd[1], *cm = fd + 4 + 2 * fd[0];
+                    if ((I.nfold_ncm & 255u) != fd[0] || (I.nfold_ncm >> 8) != ncm) { g_err = "item and descriptor disagree on the counts"; return 8; }
+                    const uint32_t ifv[2] = {I.fold_var0, I.fold_var1}, ifs[2] = {I.fold_stride0, I.fold_stride1};
+                    for (uint32_t k = 0; k < 2; ++k) {
+                        if (k < fd[0] ? (ifv[k] != fd[4 + 2 * k] || ifs[k] != fd[5 + 2 * k]) : (ifs[k] != 0 || ifv[k] >= (uint32_t)P.n_vars)) { g_err = "item and descriptor disagree on the folded variables"; return 8; }
+                    }
+                    for (uint32_t k = 0; k < (uint32_t)kResMaxChecks; ++k)
+                        if (k < ncm ? I.chk[k] != cm[k] : I.chk[k] >= (uint32_t)P.n_vars) { g_err = "item and descriptor disagree on the checked variables"; return 8; }
+                    if (I.want_off != (ncm ? fd[2] + I.j0 * ncm * 4u : 0u)) { g_err = "item and descriptor disagree on the want words"; return 8; }
                     uint32_t fx = 0;
-                    for (uint32_t k = 0; k < fd[0]; ++k) fx += (uint32_t)pat[fd[4 + 2 * k]] * fd[5 + 2 * k];
-                    const uint32_t ncm = fd[1], *cm = fd + 4 + 2 * fd[0], *want = reinterpret_cast<const uint32_t *>(bytes + fd[2]);
+                    if (fd[0] <= 2) fx = (uint32_t)pat[I.fold_var0] * I.fold_stride0 + (uint32_t)pat[I.fold_var1] * I.fold_stride1;
+                    else for (uint32_t k = 0; k < fd[0]; ++k) fx += (uint32_t)pat[fd[4 + 2 * k]] * fd[5 + 2 * k];
+                    const uint32_t *want = reinterpret_cast<const uint32_t *>(bytes + I.want_off) - (size_t)I.j0 * ncm;   // indexed by the op's target below
                     if ((ncm != 0) != (kind == RES_SUMC)) { g_err = "item kind does not match the op's checks"; return 7; }
                     const uint32_t stride = ng > 3 ? 8 : 4;
                     const uint32_t *rec = reinterpret_cast<const uint32_t *>(bytes + I.rec_off);
@@ -208,7 +220,7 @@ extern "C" int emu_run_resident(const fbn_tree_desc *tree, int warps, int64_t sm
                             acc += v;
                         }
                         for (uint32_t k = 0; k < ncm; ++k) {   // checked target variables: zero where the case observed another state
-                            const int pv = pat[cm[k]];
+                            const int pv = pat[I.chk[k]];
                             if (pv != 0 && pv != (int)want[(size_t)(I.j0 + j) * ncm + k]) acc = 0.0;
                         }
                         W[I.dst_off / rowb + j] = acc;
