@@ -42,7 +42,7 @@ int fbn_set_error(int code, const std::string &msg) { return fail(code, msg); } 
 
 // Revision of the kernels' memory behaviour. bench.py attaches an ncu traffic figure (profiles/traffic.json) to a run only
 // when it was captured at the same revision: bump on every change that alters what the kernels read or write.
-static const int kKernelRev = 7;
+static const int kKernelRev = 8;
 #define CK(call)                                                                                       \
     do {                                                                                               \
         cudaError_t e__ = (call);                                                                      \
