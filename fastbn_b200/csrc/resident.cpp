@@ -290,7 +290,7 @@ void build_resident(const HostPlan &P, int warps, int64_t smem_limit, ResidentPl
                     ResItem it = ResItem();
                     if (q.kind == RES_SUM) {
                         const SumOp &op = P.ops[(size_t)q.op];
-                        it.kind_ng = (op.ncmask ? RES_SUMC : RES_SUM) | ((uint32_t)op.ng << 8);
+                        it.kind_ng = (op.ncmask ? RES_SUMC : RES_SUM) | ((uint32_t)op.ng << 8) | (1u << (16 + std::min(op.ng, 5)));   // bits 16..21: the kernel body (by gathers per entry)
                         it.rec_off = rec_off[q.op] + (uint32_t)q.j0 * (uint32_t)op.rows * (op.ng > 3 ? 32u : 16u);
                         it.n_targets = (uint32_t)(q.j1 - q.j0);
                         it.rows = (uint32_t)op.rows;

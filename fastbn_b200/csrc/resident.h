@@ -38,7 +38,7 @@ enum ResItemKind : uint32_t { RES_SUM = 0, RES_OUT = 1, RES_EVID = 2, RES_SUMC =
 //              more than 3 gathers)
 //   pots     : doubles (nfx per entry), 16-byte aligned per op
 struct ResItem {
-    uint32_t kind_ng;    // kind | ng << 8
+    uint32_t kind_ng;    // kind | ng << 8 | 1 << (16 + min(ng, 5)) (SUM items: the bit names the kernel body)
     uint32_t rec_off;    // SUM: first record.                     OUT: variable
     uint32_t n_targets;  // SUM: targets of the piece.             OUT: dim
     uint32_t rows;       // SUM: records per target.               OUT: posterior column of state 0 (VarInfo::off)

@@ -405,17 +405,16 @@ __global__ void __launch_bounds__(MAXT * 32, 1) jt_resident_kernel(const ResDev 
                 const uint32_t ia = blk + hdr.z + i * (uint32_t)sizeof(ResItem);
                 RES_STAMP(2);
                 const uint4 a = lds128u(ia), b4 = lds128u(ia + 16), c4 = lds128u(ia + 32), d4 = lds128u(ia + 48);
-                const uint32_t kind = a.x & 255u, ng = a.x >> 8;
+                const uint32_t kind = a.x & 255u, ng = (a.x >> 8) & 255u;
                 if (kind == RES_SUM || kind == RES_SUMC) {
-                    const bool cm = kind == RES_SUMC;   // with per-target evidence checks
-                    switch (ng) {
-                        case 0: res_sum<0, ResBatch<0, MAXT>::value>(blk, a, b4, c4, d4, Sb, patl); break;
-                        case 1: res_sum<1, ResBatch<1, MAXT>::value>(blk, a, b4, c4, d4, Sb, patl); break;
-                        case 2: res_sum<2, ResBatch<2, MAXT>::value>(blk, a, b4, c4, d4, Sb, patl); break;
-                        case 3: res_sum<3, ResBatch<3, MAXT>::value>(blk, a, b4, c4, d4, Sb, patl); break;
-                        case 4: res_sum<4, ResBatch<4, MAXT>::value>(blk, a, b4, c4, d4, Sb, patl); break;
-                        default: res_sum_generic(blk, a, b4, Sb, patl, ng, cm); break;
-                    }
+                    // bit 16 + min(ng, 5) of the item's first word names the body: a chain of warp-uniform bit tests, most
+                    // frequent first (a switch on ng becomes a jump table: a constant load and an indirect branch per item)
+                    if (a.x & (1u << 17)) res_sum<1, ResBatch<1, MAXT>::value>(blk, a, b4, c4, d4, Sb, patl);
+                    else if (a.x & (1u << 18)) res_sum<2, ResBatch<2, MAXT>::value>(blk, a, b4, c4, d4, Sb, patl);
+                    else if (a.x & (1u << 16)) res_sum<0, ResBatch<0, MAXT>::value>(blk, a, b4, c4, d4, Sb, patl);
+                    else if (a.x & (1u << 19)) res_sum<3, ResBatch<3, MAXT>::value>(blk, a, b4, c4, d4, Sb, patl);
+                    else if (a.x & (1u << 20)) res_sum<4, ResBatch<4, MAXT>::value>(blk, a, b4, c4, d4, Sb, patl);
+                    else res_sum_generic(blk, a, b4, Sb, patl, ng, kind == RES_SUMC);
                 } else if (kind == RES_OUT) {
                     res_out(R, a, b4, Sb, patl, tile, n_cases, lane, labels, post);
                 } else if (next_tile < n_tiles) {   // RES_EVID: the next tile's patterns into the other pattern buffer

@@ -172,9 +172,10 @@ extern "C" int emu_run_resident(const fbn_tree_desc *tree, int warps, int64_t sm
             for (int w = 0; w < warps; ++w)
                 for (uint32_t it = blk[4 + w]; it < blk[4 + w + 1]; ++it) {
                     const ResItem &I = items[it];
-                    const uint32_t kind = I.kind_ng & 255u, ng = I.kind_ng >> 8;
+                    const uint32_t kind = I.kind_ng & 255u, ng = (I.kind_ng >> 8) & 255u;
                     if (kind == RES_EVID) { if (cs == 0) ++n_evid_items; continue; }
                     if (kind != RES_OUT && kind != RES_SUM && kind != RES_SUMC) { g_err = "unknown item kind"; return 6; }
+                    if (kind != RES_OUT && (I.kind_ng >> 16) != (1u << (ng < 5 ? ng : 5))) { g_err = "item without its body bit"; return 6; }
                     if (kind == RES_OUT) {
                         const int v = (int)I.rec_off, dim = (int)I.n_targets, off = (int)I.rows;
                         const double *mg = &S[I.dst_off / rowb];

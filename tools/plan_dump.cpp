@@ -76,7 +76,7 @@ extern "C" int resident_dump(const fbn_tree_desc *tree, int warps, int verbose) 
             for (int w = 0; w < warps; ++w) {
                 double c = 0;
                 for (uint32_t i = blk[4 + w]; i < blk[4 + w + 1]; ++i) {
-                    const uint32_t kind = items[i].kind_ng & 255, ng = items[i].kind_ng >> 8;
+                    const uint32_t kind = items[i].kind_ng & 255, ng = (items[i].kind_ng >> 8) & 255;
                     if (kind == fbn::RES_SUM || kind == fbn::RES_SUMC) {
                         const uint32_t *d = blk + items[i].desc_off / 4;
                         c += 100.0 + 12.0 * d[0] + 6.0 * d[1] + items[i].n_targets * (8.0 + 10.0 * d[1] + (10.0 + 5.0 * ng + (ng > 3 ? 1.0 : 0.0)) * items[i].rows);
