@@ -227,9 +227,12 @@ __device__ __noinline__ void res_sum(uint32_t blk, const uint4 a, const uint4 b4
             acc.x += v0; acc.y += v1;
             if (++r == rows) {   // end of target j
                 if (cw) {
-                    check(c0, lds32(cw), acc);
-                    if (ncm > 1) check(c1, lds32(cw + 4), acc);
-                    if (ncm > 2) check(c2, lds32(cw + 8), acc);
+                    // all three slots, no branches: an unused slot holds pattern 0 (nothing observed), the words read past the
+                    // target's ncm are the next target's (or the bytes after the table: still this CTA's shared memory)
+                    const uint32_t w0 = lds32(cw), w1 = lds32(cw + 4), w2 = lds32(cw + 8);
+                    check(c0, w0, acc);
+                    check(c1, w1, acc);
+                    check(c2, w2, acc);
                     cw += 4 * ncm;
                 }
                 sts128(dst, acc);
