@@ -36,7 +36,7 @@ double sum_piece_cost(const SumOp &op, int targets) {
     return setup + targets * (per_target + per_entry * op.rows);
 }
 double out_cost(int dim) { return 180.0 + 20.0 * dim; }
-constexpr double kEvidCost = 1200.0;
+const double kEvidCost = getenv("FBN_RES_EVID_COST") ? atof(getenv("FBN_RES_EVID_COST")) : 1200.0;   // developer knob for sweeps
 
 }  // namespace
 

@@ -97,16 +97,17 @@ __device__ __forceinline__ void res_load_patterns(const ResDev &R, uint32_t pat_
     if (c0 >= n_cases) return;
     const int64_t k0 = ev_off[c0] - ev_base, kmid = ev_off[c0 + 1] - ev_base;
     const int64_t k1 = c0 + 1 < n_cases ? ev_off[c0 + 2] - ev_base : kmid;
-    for (int64_t k = k0; k < k1; k += 4) {
-        int vv[4], ww[4];
+    constexpr int kEvBatch = 8;   // (variable, value) pairs requested together: the item's time is global-memory round trips
+    for (int64_t k = k0; k < k1; k += kEvBatch) {
+        int vv[kEvBatch], ww[kEvBatch];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
+        for (int u = 0; u < kEvBatch; ++u) {
             const int64_t kk = min(k + u, k1 - 1);
             vv[u] = __ldg(ev_vars + kk);
             ww[u] = __ldg(ev_vals + kk);
         }
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
+        for (int u = 0; u < kEvBatch; ++u) {
             if (k + u >= k1) break;
             const int v = vv[u], val = ww[u];
             if (v < 0 || v >= R.n_vars) continue;   // src/JunctionTree.cpp:326-331
