@@ -385,10 +385,10 @@ extern "C" void fbn_plan_destroy(fbn_plan *p) {
             }
             fprintf(stderr, "  tile: %.0f cycles\n", tot);
             static const char *seg[] = {"barrier->before wait", "wait for block", "header + list", "item load + dispatch", "fold", "check setup", "record loop",
-                                        "items done", "CTA barrier"};
+                                        "items done", "CTA barrier", "OUT: item load + dispatch", "OUT: pattern + sum of the states", "OUT: reciprocal, posteriors, argmax"};
             std::vector<long long> sc(40);
             if (cudaMemcpy(sc.data(), p->rd.clk + 8100, 40 * 8, cudaMemcpyDeviceToHost) == cudaSuccess)
-                for (int k = 0; k < 9; ++k)
+                for (int k = 0; k < 12; ++k)
                     if (sc[20 + k]) fprintf(stderr, "  segment %-22s: %8.0f cycles mean x %lld\n", seg[k], (double)sc[k] / sc[20 + k], sc[20 + k]);
         }
     }

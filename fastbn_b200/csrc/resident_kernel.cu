@@ -309,6 +309,7 @@ __device__ __noinline__ void res_sum_generic(uint32_t blk, const uint4 a, const 
 __device__ __noinline__ void res_out(const ResDev &R, const uint4 a, const uint4 b4, uint32_t Sb, uint32_t patl, int64_t tile, int64_t n_cases,
                                         int lane, int32_t *__restrict__ labels, double *__restrict__ post) {
     const uint32_t v = a.y, dim = a.z, off = a.w, mg = Sb + b4.x;   // ResItem: variable, dim, posterior column, marginal rows
+    RES_STAMP(9);
     const uint32_t pp = lds16(patl + v * kTileCases);
     const bool obs0 = (pp & 255u) != 0, obs1 = (pp >> 8) != 0;
     const int64_t c0 = tile * kTileCases + lane * 2;
@@ -320,6 +321,7 @@ __device__ __noinline__ void res_out(const ResDev &R, const uint4 a, const uint4
     }
     // one division per case, then products (a division per state costs ~35 instructions; x * (1 / s) is within one ulp of x / s).
     // 0 / 0 (evidence with probability zero) must stay NaN as in the reference: 1 / 0 = inf, 0 * inf = NaN
+    RES_STAMP(10);
     const double r0 = 1.0 / s0, r1 = 1.0 / s1;
     double best0 = 0.0, best1 = 0.0;
     int arg0 = -1, arg1 = -1;
@@ -333,6 +335,7 @@ __device__ __noinline__ void res_out(const ResDev &R, const uint4 a, const uint4
         if (pr0 > best0) { best0 = pr0; arg0 = (int)d; }
         if (pr1 > best1) { best1 = pr1; arg1 = (int)d; }
     }
+    RES_STAMP(11);
     if ((int)v == R.query_var && labels) {
         if (ok0) labels[c0] = arg0;
         if (ok1) labels[c0 + 1] = arg1;
