@@ -108,3 +108,43 @@ def test_cuda_path_agrees_with_joint_enumeration(tmp_path, spec):
         labels, post, _ = p.run(ev_off, ev_vars, ev_vals)
         p.close()
         assert np.max(np.abs(post - want)) <= 1e-12, kw
+
+
+def star_case(tmp_path, n_cases=64, seed=3):
+    """Two cliques whose three binary parents appear nowhere else: the collect view of each folds THREE variables into its pattern
+    tables (4^3 = 64 patterns per entry, the default cap) — the resident kernel then reads the fold list from the op's
+    descriptor instead of the two pairs an item carries (csrc/resident.h)."""
+    rng = np.random.default_rng(seed)
+    var_dims = np.array([2, 2, 2, 3, 2, 3, 2, 2, 2, 2], np.int32)
+    parents = [[], [], [], [0, 1, 2], [3], [4], [], [], [5, 6, 7], [8]]
+    cpts = []
+    for i, pa in enumerate(parents):
+        ncfg = int(np.prod(var_dims[pa])) if pa else 1
+        cpts.append(np.round(rng.dirichlet(np.ones(int(var_dims[i])), size=ncfg).T, 4))
+    xml = str(tmp_path / "star.xml")
+    synth.write_xmlbif(xml, var_dims, parents, cpts)
+    m = hostapi.HostModel(xml)
+    tree = m.tree()
+    m.close()
+    n = len(var_dims)
+    counts = rng.integers(0, 7, n_cases)
+    counts[0] = 0
+    ev_off = np.concatenate([[0], np.cumsum(counts)]).astype(np.int64)
+    ev_vars = np.concatenate([np.sort(rng.choice(n, k, replace=False)) for k in counts] + [np.zeros(0, np.int64)]).astype(np.int32)
+    ev_vals = np.array([rng.integers(0, var_dims[v]) for v in ev_vars], np.int32)
+    want = brute_posteriors(joint_table(var_dims, parents, cpts), var_dims, ev_off, ev_vars, ev_vals)
+    return tree, ev_off, ev_vars, ev_vals, want
+
+
+def test_three_folded_variables_against_joint_enumeration(tmp_path):
+    tree, ev_off, ev_vars, ev_vals, want = star_case(tmp_path)
+    o = jtoracle.Oracle(tree)
+    post, lab = o.run_batch(ev_off, ev_vars, ev_vals)
+    o.close()
+    ok = ~np.isnan(want)   # evidence of probability zero: NaN on both sides
+    assert np.array_equal(np.isnan(post), np.isnan(want)) and np.max(np.abs(post[ok] - want[ok])) <= 1e-12
+    for team in (1, 4, -8):
+        post2, lab2, _ = emu.run(tree, team, ev_off, ev_vars, ev_vals)
+        assert np.array_equal(np.isnan(post2), np.isnan(want)) and np.max(np.abs(post2[ok] - want[ok])) <= 1e-12 and np.array_equal(lab2, lab)
+    post2, lab2, info = emu.run_resident(tree, 16, ev_off, ev_vars, ev_vals)
+    assert np.array_equal(np.isnan(post2), np.isnan(want)) and np.max(np.abs(post2[ok] - want[ok])) <= 1e-12 and np.array_equal(lab2, lab)
